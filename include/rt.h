@@ -1,0 +1,196 @@
+/*
+ * rt.h -- C ABI of the B200-native per-pixel ray-tracing hot path.
+ *
+ * Drop-in boundary for JustinPrivitera/Real_Time_Ray_Tracer: these entry points replace
+ * the OpenGL compute dispatch of the reference (citations relative to /root/reference):
+ *
+ *   reference                                              this ABI
+ *   ------------------------------------------------------ ---------------------------
+ *   glBufferData(sizeof(ssbo_data))   src/main.cpp:476-480  rt_create
+ *   loadShapeBuffer + SSBO upload     src/main.cpp:395-469,  rt_upload_scene
+ *                                     598-602
+ *   compute_one_shader: uniforms, glDispatchCompute(W,H,1), rt_render_frame
+ *     barrier                         src/main.cpp:580-620
+ *   compute_two_shaders, 2nd dispatch src/main.cpp:649-656  rt_postprocess
+ *   SSBO read-back                    src/main.cpp:613-617  rt_download
+ *   (nothing: errors printed/ignored) src/GLSL.cpp:39-47    rt_last_error, int status
+ *
+ * Plain C types only.  Every function returns RT_OK (0) or a negative RT_E* code and never
+ * calls exit().  The library has no CPU fallback: without a CUDA device rt_create fails with
+ * RT_ENODEVICE.  A context is used by one thread at a time; contexts are independent.
+ */
+#ifndef RT_H
+#define RT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* compile-time limits (reference: NUM_SHAPES 10 src/main.cpp:34; AA 4 :31) */
+#define RT_MAX_SHAPES 10
+#define RT_MAX_AA 16
+#define RT_MAX_FRAMES 16
+
+enum {
+    RT_OK = 0,
+    RT_EINVAL = -1,    /* bad argument */
+    RT_ENODEVICE = -2, /* no usable CUDA device */
+    RT_ENOMEM = -3,    /* device or host allocation failed */
+    RT_ECUDA = -4,     /* a CUDA call failed; see rt_last_error */
+    RT_ESTATE = -5     /* call out of order (e.g. rt_postprocess before a mode-1 frame) */
+};
+
+/* lighting modes, Application::compute() src/main.cpp:553-578 */
+enum {
+    RT_MODE_AO_PP = 1, /* aop_compute.glsl, then rt_postprocess = aop_postprocessing.glsl */
+    RT_MODE_AO = 2,    /* ao_compute.glsl */
+    RT_MODE_PHONG = 3, /* p_compute.glsl */
+    RT_MODE_HYBRID = 4 /* h_compute.glsl */
+};
+
+/* neighbour semantics at the image border of the post-processing pass
+ * (aop_postprocessing.glsl:81 `x < WIDTH`, :150 `y - 1 > 0` on a uint) */
+enum {
+    RT_EDGE_FLAT32 = 0, /* literal: 32-bit flat index into the contiguous ssbo_data struct */
+    RT_EDGE_CLEAN = 1   /* intended: x + 1 < WIDTH, y > 0 */
+};
+
+/* buffers of rt_download / rt_upload / rt_device_ptr */
+enum {
+    RT_BUF_COLOR = 0,     /* pixels[slot]          float4 per pixel */
+    RT_BUF_NORMAL = 1,    /* normals_buffer[slot]  float4 per pixel */
+    RT_BUF_DEPTH = 2,     /* depth_buffer[slot]    float4 per pixel (x,y stored; z = 0; w stored) */
+    RT_BUF_HIT_INDEX = 3, /* int32 per pixel: shape index of the un-jittered primary hit, -1 = miss
+                             (the shader local `ind`, ao_compute.glsl:180; last frame only) */
+    RT_BUF_IMAGE = 4,     /* img_output of the last frame, float4 per pixel */
+    RT_BUF_RAW_COLOR = 5, /* mode 1: aop_compute output before post-processing (last frame) */
+    RT_BUF_DEPTH_XY = 6,  /* device-side plane: float2 per pixel (rt_device_ptr only) */
+    RT_BUF_DEPTH_W = 7    /* device-side plane: float per pixel (rt_device_ptr only) */
+};
+
+/* host layouts of rt_download / rt_upload */
+enum {
+    RT_LAYOUT_ROW_MAJOR = 0, /* [rows][W], x fastest, y = 0 at the bottom (like `tex`) */
+    RT_LAYOUT_REFERENCE = 1  /* [W][rows], y fastest: ssbo_data's pixels[f][x][y], src/main.cpp:81-84 */
+};
+
+typedef struct rt_vec4 { float x, y, z, w; } rt_vec4;
+
+/* the seven leading vec4 of ssbo_data / shader_data, same order (src/main.cpp:52-58).
+ * mode.y = ring slot, mode.z = number of shapes (src/main.cpp:584-585). */
+typedef struct rt_uniforms {
+    rt_vec4 mode;
+    rt_vec4 horizontal;
+    rt_vec4 vertical;
+    rt_vec4 llc_minus_campos;
+    rt_vec4 camera_location;
+    rt_vec4 light_pos;
+    rt_vec4 background;
+} rt_uniforms;
+
+/* one record of simple_shapes[NUM_SHAPES][5] (src/main.cpp:59-77):
+ *   sphere: v[0]=(center,radius) v[1].w=emissive v[3].w=reflectivity v[4]=(color,1)
+ *   plane:  v[0]=(normal,dist)   v[1].w=emissive v[3]=(p0,reflectivity) v[4]=(color,5)
+ *   rectangle (id 3) is accepted and, like in the shaders, never intersected. */
+typedef struct rt_shape { rt_vec4 v[5]; } rt_shape;
+
+/* the reference's #defines (src/main.cpp:29-36, every shader :7-13) made run-time */
+typedef struct rt_config {
+    int32_t width;           /* WIDTH  of the whole image */
+    int32_t height;          /* HEIGHT of the whole image */
+    int32_t aa;              /* AA, 1..RT_MAX_AA */
+    int32_t recursion_depth; /* RECURSION_DEPTH, 20 */
+    int32_t num_frames;      /* NUM_FRAMES, 8; <= RT_MAX_FRAMES */
+    int32_t edge_mode;       /* RT_EDGE_* */
+    int32_t device;          /* CUDA device ordinal */
+    int32_t band_y0;         /* first image row owned by this context */
+    int32_t band_rows;       /* rows owned; 0 = height - band_y0 (whole image when band_y0 = 0) */
+    int32_t band_index;      /* position of this band in the frame, 0 .. band_count-1 */
+    int32_t band_count;      /* number of bands the frame is split into (1 = no halo exchange) */
+    int32_t reserved[5];     /* must be 0 */
+} rt_config;
+
+/* ray / work counters accumulated since rt_reset_stats; "ray" = one closest-hit traversal of the
+ * object table or one shadow traversal */
+typedef struct rt_stats {
+    uint64_t rays_closest;
+    uint64_t rays_shadow;
+    uint64_t primary;
+    uint64_t jittered;
+    uint64_t seg_nonterminal;
+    uint64_t seg_terminal;
+    uint64_t shaded;
+    uint64_t reflective;
+    uint64_t pixels;
+    uint64_t pp_nonbackground;
+    uint64_t pp_hist_evaluated;
+    uint64_t pp_hist_accepted;
+    double ms_trace_last; /* device time of the last trace kernel (CUDA events), 0 if timing off */
+    double ms_post_last;  /* device time of the last post-processing kernel */
+} rt_stats;
+
+/* where the halo records of a row band live on the device (band_count > 1 or FLAT32).
+ * A record row is W x {float4 color, float4 normal, float2 depth_xy} stored as three consecutive
+ * arrays: bytes = W * 40.  After a mode-1 rt_render_frame, rt_halo_pack fills send_lo (this band's
+ * bottom row) and send_hi (this band's top row; on the LAST band under FLAT32 the wrapped row that
+ * `[f][x][-1]` reads).  The caller moves send_hi -> recv_lo of band (i+1) % count and
+ * send_lo -> recv_hi of band i-1 (NCCL, cudaMemcpyPeer, ...), then calls rt_postprocess. */
+typedef struct rt_halo_info {
+    void *send_lo, *send_hi, *recv_lo, *recv_hi;
+    size_t row_bytes;
+} rt_halo_info;
+
+typedef struct rt_ctx rt_ctx;
+
+int rt_abi_version(void);
+int rt_device_count(void);
+
+int rt_create(const rt_config *cfg, rt_ctx **out);
+void rt_destroy(rt_ctx *ctx);
+const char *rt_last_error(const rt_ctx *ctx); /* ctx may be NULL: last error of rt_create */
+
+/* run on this CUDA stream (a cudaStream_t; NULL = the context's own stream) */
+int rt_set_stream(rt_ctx *ctx, void *cuda_stream);
+int rt_synchronize(rt_ctx *ctx);
+/* per-kernel CUDA-event timing into rt_stats.ms_* (off by default: it adds two event records) */
+int rt_set_timing(rt_ctx *ctx, int enabled);
+
+/* copies n_shapes records; the device table is rebuilt before the next frame */
+int rt_upload_scene(rt_ctx *ctx, const rt_shape *shapes, int n_shapes);
+
+/* one trace dispatch into ring slot (int)u->mode.y.  rand_buffer: 8*aa floats = vec4[2*aa]
+ * (modes 1,2; may be NULL for 3,4).  Asynchronous on the context's stream. */
+int rt_render_frame(rt_ctx *ctx, int lighting_mode, const rt_uniforms *u, const float *rand_buffer);
+
+/* mode 1, second pass, on the slot just rendered */
+int rt_halo_pack(rt_ctx *ctx);
+int rt_get_halo(rt_ctx *ctx, rt_halo_info *out);
+int rt_postprocess(rt_ctx *ctx);
+
+/* synchronising copies between this band's device buffers and host memory; bytes must equal
+ * band_rows * width * element size (16, or 4 for RT_BUF_HIT_INDEX) */
+int rt_download(rt_ctx *ctx, int buffer, int slot, int layout, void *host, size_t bytes);
+int rt_upload(rt_ctx *ctx, int buffer, int slot, int layout, const void *host, size_t bytes);
+/* asynchronous row-major download into pinned host memory on the context's stream */
+int rt_download_async(rt_ctx *ctx, int buffer, int slot, void *pinned_host, size_t bytes);
+/* raw device pointer of a row-major plane of this band (for NCCL / framework interop) */
+int rt_device_ptr(rt_ctx *ctx, int buffer, int slot, void **out_ptr, size_t *out_bytes);
+
+int rt_get_stats(rt_ctx *ctx, rt_stats *out); /* synchronises */
+int rt_reset_stats(rt_ctx *ctx);
+
+/* diagnostics used by the parity tests and the benchmark */
+/* element-wise built-ins on the device: kind 0 sin(a), 1 pow(a,b), 2 random(vec2(a,b)) */
+int rt_debug_eval_math(int device, int kind, const float *a, const float *b, float *out, size_t n);
+/* dependent-free FFMA microbenchmark: measured FP32 FMA throughput of the device in TFLOP/s */
+int rt_measure_fp32_peak(int device, double *tflops_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_H */

@@ -1,0 +1,517 @@
+// rt_capi.cu -- the C ABI of include/rt.h over the sm_100a kernels.
+//
+// Replaces the dispatch boundary of the reference: Application::compute_one_shader /
+// compute_two_shaders (src/main.cpp:580-671) and the SSBO create/upload/read-back around them
+// (src/main.cpp:476-480, 598-602, 613-617).  No CPU fallback: every entry point needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "rt_kernels.cuh"
+
+using namespace rt;
+
+struct rt_ctx {
+    rt_config cfg{};
+    int rows = 0;
+    size_t npix = 0; // rows * width
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    // ring planes, each [NF][rows*W]
+    float4 *ring_color = nullptr, *ring_normal = nullptr;
+    float2 *ring_depth_xy = nullptr;
+    float *ring_depth_w = nullptr;
+    float4 *raw = nullptr; // mode-1 trace output of the current frame
+    int *hit = nullptr;
+    void *halo[4] = { nullptr, nullptr, nullptr, nullptr }; // send_lo, send_hi, recv_lo, recv_hi
+    void *staging = nullptr; // npix * 16 bytes, layout conversions
+    unsigned long long *stats = nullptr;
+    unsigned long long *stats_host = nullptr; // pinned
+    DevShape shapes[RT_MAX_SHAPES]{};
+    int nshapes = 0;
+    FrameParams fp{};
+    int last_mode = 0, last_slot = 0;
+    bool frame_pending_post = false, halo_packed = false;
+    float4 rand_last{};
+    bool timing = false;
+    cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
+    bool ev_trace_valid = false, ev_post_valid = false;
+    std::string err;
+};
+
+static thread_local std::string g_create_err;
+
+static int fail(rt_ctx *c, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_err = buf;
+    return code;
+}
+
+#define CU(c, call)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess)                                                                        \
+            return fail((c), RT_ECUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" {
+
+int rt_abi_version(void) { return RT_ABI_VERSION; }
+
+int rt_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+static void free_all(rt_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
+    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats);
+    for (void *h : c->halo) cudaFree(h);
+    if (c->stats_host) cudaFreeHost(c->stats_host);
+    for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+int rt_create(const rt_config *cfg, rt_ctx **out)
+{
+    if (!cfg || !out) return fail(nullptr, RT_EINVAL, "rt_create: null argument");
+    *out = nullptr;
+    if (cfg->width <= 0 || cfg->height <= 0) return fail(nullptr, RT_EINVAL, "rt_create: width/height must be > 0");
+    if (cfg->aa < 1 || cfg->aa > RT_MAX_AA) return fail(nullptr, RT_EINVAL, "rt_create: aa must be 1..%d", RT_MAX_AA);
+    if (cfg->recursion_depth < 1 || cfg->recursion_depth > 1000) return fail(nullptr, RT_EINVAL, "rt_create: bad recursion_depth");
+    if (cfg->num_frames < 1 || cfg->num_frames > RT_MAX_FRAMES) return fail(nullptr, RT_EINVAL, "rt_create: num_frames must be 1..%d", RT_MAX_FRAMES);
+    if (cfg->edge_mode != RT_EDGE_FLAT32 && cfg->edge_mode != RT_EDGE_CLEAN) return fail(nullptr, RT_EINVAL, "rt_create: bad edge_mode");
+    for (int r : cfg->reserved) if (r != 0) return fail(nullptr, RT_EINVAL, "rt_create: reserved fields must be 0");
+    int rows = cfg->band_rows ? cfg->band_rows : cfg->height - cfg->band_y0;
+    if (cfg->band_y0 < 0 || rows <= 0 || cfg->band_y0 + rows > cfg->height) return fail(nullptr, RT_EINVAL, "rt_create: band outside the image");
+    int bcount = cfg->band_count ? cfg->band_count : 1;
+    if (cfg->band_index < 0 || cfg->band_index >= bcount) return fail(nullptr, RT_EINVAL, "rt_create: bad band_index");
+    if (bcount == 1 && rows != cfg->height) return fail(nullptr, RT_EINVAL, "rt_create: a partial band needs band_count > 1");
+    if ((long long)cfg->width * cfg->height * cfg->num_frames >= (1ll << 31)) return fail(nullptr, RT_EINVAL, "rt_create: W*H*num_frames must fit 31 bits");
+
+    int ndev = rt_device_count();
+    if (ndev <= 0) return fail(nullptr, RT_ENODEVICE, "rt_create: no CUDA device (this library has no CPU path)");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, RT_ENODEVICE, "rt_create: device %d of %d", cfg->device, ndev);
+
+    rt_ctx *c = new (std::nothrow) rt_ctx();
+    if (!c) return fail(nullptr, RT_ENOMEM, "rt_create: host allocation failed");
+    c->cfg = *cfg;
+    c->cfg.band_rows = rows;
+    c->cfg.band_count = bcount;
+    c->rows = rows;
+    c->npix = (size_t)rows * cfg->width;
+    const size_t ring = c->npix * cfg->num_frames;
+    cudaError_t e = cudaSetDevice(cfg->device);
+    auto alloc0 = [&](void **p, size_t bytes) {
+        if (e != cudaSuccess) return;
+        e = cudaMalloc(p, bytes);
+        if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
+    };
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    c->stream = c->own_stream;
+    // value-initialised like the reference's ssbo_CPUMEM (src/main.cpp:810): the ring starts at zero
+    alloc0((void **)&c->ring_color, ring * sizeof(float4));
+    alloc0((void **)&c->ring_normal, ring * sizeof(float4));
+    alloc0((void **)&c->ring_depth_xy, ring * sizeof(float2));
+    alloc0((void **)&c->ring_depth_w, ring * sizeof(float));
+    alloc0((void **)&c->raw, c->npix * sizeof(float4));
+    alloc0((void **)&c->hit, c->npix * sizeof(int));
+    alloc0(&c->staging, c->npix * sizeof(float4));
+    alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
+    for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width));
+    if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
+    for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        int code = (e == cudaErrorMemoryAllocation) ? RT_ENOMEM : RT_ECUDA;
+        fail(nullptr, code, "rt_create: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        free_all(c);
+        return code;
+    }
+    *out = c;
+    return RT_OK;
+}
+
+void rt_destroy(rt_ctx *ctx) { free_all(ctx); }
+
+int rt_set_stream(rt_ctx *c, void *cuda_stream)
+{
+    if (!c) return RT_EINVAL;
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return RT_OK;
+}
+
+int rt_synchronize(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_set_timing(rt_ctx *c, int enabled)
+{
+    if (!c) return RT_EINVAL;
+    c->timing = enabled != 0;
+    c->ev_trace_valid = c->ev_post_valid = false;
+    return RT_OK;
+}
+
+// loadShapeBuffer's records (src/main.cpp:395-469) -> device table
+int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
+{
+    if (!c) return RT_EINVAL;
+    if (n < 0 || n > RT_MAX_SHAPES) return fail(c, RT_EINVAL, "rt_upload_scene: n_shapes %d outside 0..%d", n, RT_MAX_SHAPES);
+    if (n > 0 && !shapes) return fail(c, RT_EINVAL, "rt_upload_scene: null shapes");
+    for (int i = 0; i < n; i++) {
+        const rt_vec4 *v = shapes[i].v;
+        DevShape d{};
+        d.s0 = make_float4(v[0].x, v[0].y, v[0].z, v[0].w);
+        d.s3 = make_float4(v[3].x, v[3].y, v[3].z, v[3].w);
+        d.col = make_float4(v[4].x, v[4].y, v[4].z, v[4].w);
+        d.emissive = v[1].w;
+        volatile float r = v[0].w; // binary32 product, as `radius * radius` in the shader
+        volatile float r2 = r * r;
+        d.r2 = r2;
+        d.id = (int)v[4].w;
+        c->shapes[i] = d;
+    }
+    c->nshapes = n;
+    return RT_OK;
+}
+
+static inline float3 f3(const rt_vec4 &v) { return make_float3(v.x, v.y, v.z); }
+
+int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand_buffer)
+{
+    if (!c) return RT_EINVAL;
+    if (!u) return fail(c, RT_EINVAL, "rt_render_frame: null uniforms");
+    if (mode < RT_MODE_AO_PP || mode > RT_MODE_HYBRID) return fail(c, RT_EINVAL, "rt_render_frame: lighting mode %d not implemented", mode);
+    const int slot = (int)u->mode.y;
+    const int nobj = (int)u->mode.z;
+    if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "rt_render_frame: ring slot %d outside 0..%d", slot, c->cfg.num_frames - 1);
+    if (nobj < 0 || nobj > c->nshapes) return fail(c, RT_EINVAL, "rt_render_frame: mode.z = %d but %d shapes uploaded", nobj, c->nshapes);
+    const bool ao = (mode == RT_MODE_AO_PP || mode == RT_MODE_AO);
+    if (ao && !rand_buffer) return fail(c, RT_EINVAL, "rt_render_frame: AO modes need a rand_buffer");
+    CU(c, cudaSetDevice(c->cfg.device));
+
+    FrameParams &p = c->fp;
+    p.W = c->cfg.width; p.H = c->cfg.height; p.AA = c->cfg.aa; p.RD = c->cfg.recursion_depth; p.NF = c->cfg.num_frames;
+    p.y0 = c->cfg.band_y0; p.rows = c->rows;
+    p.slot = slot; p.nshapes = nobj; p.edge_mode = c->cfg.edge_mode; p.mode = mode;
+    p.band_index = c->cfg.band_index; p.band_count = c->cfg.band_count;
+    p.llc = f3(u->llc_minus_campos); p.horiz = f3(u->horizontal); p.vert = f3(u->vertical);
+    p.cam = f3(u->camera_location); p.light = f3(u->light_pos);
+    p.bg = make_float4(u->background.x, u->background.y, u->background.z, u->background.w);
+    memcpy(p.shapes, c->shapes, sizeof p.shapes);
+    if (rand_buffer) {
+        memcpy(p.rand, rand_buffer, (size_t)c->cfg.aa * 2 * sizeof(float4));
+        c->rand_last = p.rand[2 * c->cfg.aa - 1];
+    }
+
+    TraceOut o{};
+    const size_t off = (size_t)slot * c->npix;
+    o.color = (mode == RT_MODE_AO_PP) ? c->raw : c->ring_color + off;
+    o.normal = c->ring_normal + off;
+    o.depth_xy = c->ring_depth_xy + off;
+    o.depth_w = c->ring_depth_w + off;
+    o.hit = c->hit;
+    o.stats = c->stats;
+    if (c->timing) CU(c, cudaEventRecord(c->ev[0], c->stream));
+    CU(c, launch_trace(p, o, c->stream));
+    if (c->timing) { CU(c, cudaEventRecord(c->ev[1], c->stream)); c->ev_trace_valid = true; }
+    c->last_mode = mode;
+    c->last_slot = slot;
+    c->frame_pending_post = (mode == RT_MODE_AO_PP);
+    c->halo_packed = false;
+    return RT_OK;
+}
+
+static void fill_post(rt_ctx *c, PostParams &q)
+{
+    q.W = c->cfg.width; q.H = c->cfg.height; q.AA = c->cfg.aa; q.NF = c->cfg.num_frames;
+    q.y0 = c->cfg.band_y0; q.rows = c->rows;
+    q.slot = c->last_slot; q.edge_mode = c->cfg.edge_mode;
+    q.band_index = c->cfg.band_index; q.band_count = c->cfg.band_count;
+    q.raw = c->raw; q.ring_color = c->ring_color; q.ring_normal = c->ring_normal;
+    q.ring_depth_xy = c->ring_depth_xy; q.ring_depth_w = c->ring_depth_w;
+    q.send_lo = c->halo[0]; q.send_hi = c->halo[1];
+    q.halo_lo = c->halo[2]; q.halo_hi = c->halo[3];
+    q.rand_last = c->rand_last;
+    q.stats = c->stats;
+}
+
+int rt_halo_pack(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    if (!c->frame_pending_post) return fail(c, RT_ESTATE, "rt_halo_pack: no mode-1 frame waiting for post-processing");
+    CU(c, cudaSetDevice(c->cfg.device));
+    PostParams q{};
+    fill_post(c, q);
+    if (c->cfg.band_count == 1) {
+        // the wrapped row goes straight into this band's own lower halo
+        q.send_lo = nullptr;
+        q.send_hi = c->halo[2];
+    }
+    CU(c, launch_halo_pack(q, c->stream));
+    c->halo_packed = true;
+    return RT_OK;
+}
+
+int rt_get_halo(rt_ctx *c, rt_halo_info *out)
+{
+    if (!c || !out) return RT_EINVAL;
+    out->send_lo = c->halo[0]; out->send_hi = c->halo[1];
+    out->recv_lo = c->halo[2]; out->recv_hi = c->halo[3];
+    out->row_bytes = halo_row_bytes(c->cfg.width);
+    return RT_OK;
+}
+
+int rt_postprocess(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    if (!c->frame_pending_post) return fail(c, RT_ESTATE, "rt_postprocess: the last frame was not rendered in mode 1");
+    CU(c, cudaSetDevice(c->cfg.device));
+    if (c->timing) CU(c, cudaEventRecord(c->ev[2], c->stream));
+    if (!c->halo_packed) {
+        if (c->cfg.band_count > 1) return fail(c, RT_ESTATE, "rt_postprocess: call rt_halo_pack and exchange the halo rows first");
+        if (c->cfg.edge_mode == RT_EDGE_FLAT32) {
+            int rc = rt_halo_pack(c);
+            if (rc != RT_OK) return rc;
+        }
+    }
+    PostParams q{};
+    fill_post(c, q);
+    CU(c, launch_postprocess(q, c->stream));
+    if (c->timing) { CU(c, cudaEventRecord(c->ev[3], c->stream)); c->ev_post_valid = true; }
+    c->frame_pending_post = false;
+    return RT_OK;
+}
+
+// ---- buffers ---------------------------------------------------------------------------------
+static int plane_ptr(rt_ctx *c, int buffer, int slot, void **ptr, size_t *elem)
+{
+    const bool ringed = (buffer == RT_BUF_COLOR || buffer == RT_BUF_NORMAL || buffer == RT_BUF_DEPTH ||
+                         buffer == RT_BUF_DEPTH_XY || buffer == RT_BUF_DEPTH_W);
+    if (ringed && (slot < 0 || slot >= c->cfg.num_frames)) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
+    const size_t off = ringed ? (size_t)slot * c->npix : 0;
+    switch (buffer) {
+    case RT_BUF_COLOR: *ptr = c->ring_color + off; *elem = 16; return RT_OK;
+    case RT_BUF_NORMAL: *ptr = c->ring_normal + off; *elem = 16; return RT_OK;
+    case RT_BUF_DEPTH_XY: *ptr = c->ring_depth_xy + off; *elem = 8; return RT_OK;
+    case RT_BUF_DEPTH_W: *ptr = c->ring_depth_w + off; *elem = 4; return RT_OK;
+    case RT_BUF_HIT_INDEX: *ptr = c->hit; *elem = 4; return RT_OK;
+    case RT_BUF_RAW_COLOR: *ptr = c->raw; *elem = 16; return RT_OK;
+    case RT_BUF_IMAGE: // img_output == pixels[slot of the last frame] (ao_compute.glsl:338-339)
+        *ptr = c->ring_color + (size_t)c->last_slot * c->npix; *elem = 16; return RT_OK;
+    default: return fail(c, RT_EINVAL, "unknown buffer %d", buffer);
+    }
+}
+
+int rt_device_ptr(rt_ctx *c, int buffer, int slot, void **out_ptr, size_t *out_bytes)
+{
+    if (!c || !out_ptr) return RT_EINVAL;
+    if (buffer == RT_BUF_DEPTH) return fail(c, RT_EINVAL, "rt_device_ptr: depth is stored as RT_BUF_DEPTH_XY + RT_BUF_DEPTH_W planes");
+    size_t elem = 0;
+    int rc = plane_ptr(c, buffer, slot, out_ptr, &elem);
+    if (rc == RT_OK && out_bytes) *out_bytes = elem * c->npix;
+    return rc;
+}
+
+int rt_download(rt_ctx *c, int buffer, int slot, int layout, void *host, size_t bytes)
+{
+    if (!c || !host) return RT_EINVAL;
+    if (layout != RT_LAYOUT_ROW_MAJOR && layout != RT_LAYOUT_REFERENCE) return fail(c, RT_EINVAL, "rt_download: bad layout");
+    CU(c, cudaSetDevice(c->cfg.device));
+    const void *src = nullptr;
+    size_t elem = 16;
+    if (buffer == RT_BUF_DEPTH) {
+        if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
+        if (bytes != c->npix * 16) return fail(c, RT_EINVAL, "rt_download: expected %zu bytes, got %zu", c->npix * 16, bytes);
+        const size_t off = (size_t)slot * c->npix;
+        if (layout == RT_LAYOUT_ROW_MAJOR) {
+            CU(c, launch_expand_depth(c->ring_depth_xy + off, c->ring_depth_w + off, (float4 *)c->staging, c->npix, c->stream));
+            src = c->staging;
+        } else {
+            // expand into raw's spare? no: use a temporary so staging can hold the transpose
+            float4 *tmp = nullptr;
+            CU(c, cudaMalloc((void **)&tmp, c->npix * 16));
+            cudaError_t e = launch_expand_depth(c->ring_depth_xy + off, c->ring_depth_w + off, tmp, c->npix, c->stream);
+            if (e == cudaSuccess) e = launch_transpose(tmp, c->staging, c->cfg.width, c->rows, 16, true, c->stream);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(host, c->staging, bytes, cudaMemcpyDeviceToHost, c->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+            cudaFree(tmp);
+            CU(c, e);
+            return RT_OK;
+        }
+    } else {
+        void *p = nullptr;
+        int rc = plane_ptr(c, buffer, slot, &p, &elem);
+        if (rc != RT_OK) return rc;
+        if (elem == 8) return fail(c, RT_EINVAL, "rt_download: use RT_BUF_DEPTH");
+        if (bytes != c->npix * elem) return fail(c, RT_EINVAL, "rt_download: expected %zu bytes, got %zu", c->npix * elem, bytes);
+        src = p;
+        if (layout == RT_LAYOUT_REFERENCE) {
+            CU(c, launch_transpose(p, c->staging, c->cfg.width, c->rows, (int)elem, true, c->stream));
+            src = c->staging;
+        }
+    }
+    CU(c, cudaMemcpyAsync(host, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_download_async(rt_ctx *c, int buffer, int slot, void *pinned_host, size_t bytes)
+{
+    if (!c || !pinned_host) return RT_EINVAL;
+    CU(c, cudaSetDevice(c->cfg.device));
+    void *p = nullptr;
+    size_t elem = 0;
+    if (buffer == RT_BUF_DEPTH) return fail(c, RT_EINVAL, "rt_download_async: depth needs rt_download");
+    int rc = plane_ptr(c, buffer, slot, &p, &elem);
+    if (rc != RT_OK) return rc;
+    if (bytes != c->npix * elem) return fail(c, RT_EINVAL, "rt_download_async: expected %zu bytes, got %zu", c->npix * elem, bytes);
+    CU(c, cudaMemcpyAsync(pinned_host, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    return RT_OK;
+}
+
+int rt_upload(rt_ctx *c, int buffer, int slot, int layout, const void *host, size_t bytes)
+{
+    if (!c || !host) return RT_EINVAL;
+    if (layout != RT_LAYOUT_ROW_MAJOR && layout != RT_LAYOUT_REFERENCE) return fail(c, RT_EINVAL, "rt_upload: bad layout");
+    if (buffer != RT_BUF_COLOR && buffer != RT_BUF_NORMAL && buffer != RT_BUF_DEPTH && buffer != RT_BUF_RAW_COLOR)
+        return fail(c, RT_EINVAL, "rt_upload: buffer %d is not writable", buffer);
+    if (bytes != c->npix * 16) return fail(c, RT_EINVAL, "rt_upload: expected %zu bytes, got %zu", c->npix * 16, bytes);
+    CU(c, cudaSetDevice(c->cfg.device));
+    float4 *tmp = nullptr;
+    CU(c, cudaMalloc((void **)&tmp, bytes));
+    cudaError_t e = cudaMemcpyAsync(tmp, host, bytes, cudaMemcpyHostToDevice, c->stream);
+    const float4 *rowmajor = tmp;
+    if (e == cudaSuccess && layout == RT_LAYOUT_REFERENCE) {
+        e = launch_transpose(tmp, c->staging, c->cfg.width, c->rows, 16, false, c->stream);
+        rowmajor = (const float4 *)c->staging;
+    }
+    int rc = RT_OK;
+    if (e == cudaSuccess) {
+        if (buffer == RT_BUF_DEPTH) {
+            if (slot < 0 || slot >= c->cfg.num_frames) rc = fail(c, RT_EINVAL, "slot %d outside the ring", slot);
+            else {
+                const size_t off = (size_t)slot * c->npix;
+                e = launch_split_depth(rowmajor, c->ring_depth_xy + off, c->ring_depth_w + off, c->npix, c->stream);
+            }
+        } else {
+            void *p = nullptr;
+            size_t elem = 0;
+            rc = plane_ptr(c, buffer, slot, &p, &elem);
+            if (rc == RT_OK) e = cudaMemcpyAsync(p, rowmajor, bytes, cudaMemcpyDeviceToDevice, c->stream);
+        }
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(tmp);
+    if (rc != RT_OK) return rc;
+    CU(c, e);
+    return RT_OK;
+}
+
+int rt_get_stats(rt_ctx *c, rt_stats *out)
+{
+    if (!c || !out) return RT_EINVAL;
+    CU(c, cudaSetDevice(c->cfg.device));
+    const size_t bytes = STAT_STRIPES * ST_COUNT * sizeof(unsigned long long);
+    CU(c, cudaMemcpyAsync(c->stats_host, c->stats, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    uint64_t t[ST_COUNT] = { 0 };
+    for (int s = 0; s < STAT_STRIPES; s++)
+        for (int k = 0; k < ST_COUNT; k++) t[k] += c->stats_host[s * ST_COUNT + k];
+    memset(out, 0, sizeof *out);
+    out->rays_closest = t[ST_RAYS_CLOSEST]; out->rays_shadow = t[ST_RAYS_SHADOW];
+    out->primary = t[ST_PRIMARY]; out->jittered = t[ST_JITTERED];
+    out->seg_nonterminal = t[ST_SEG_NONTERMINAL]; out->seg_terminal = t[ST_SEG_TERMINAL];
+    out->shaded = t[ST_SHADED]; out->reflective = t[ST_REFLECTIVE]; out->pixels = t[ST_PIXELS];
+    out->pp_nonbackground = t[ST_PP_NONBACKGROUND]; out->pp_hist_evaluated = t[ST_PP_HIST_EVALUATED];
+    out->pp_hist_accepted = t[ST_PP_HIST_ACCEPTED];
+    float ms = 0.0f;
+    if (c->timing && c->ev_trace_valid && cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) out->ms_trace_last = ms;
+    if (c->timing && c->ev_post_valid && cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]) == cudaSuccess) out->ms_post_last = ms;
+    cudaGetLastError();
+    return RT_OK;
+}
+
+int rt_reset_stats(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, cudaMemsetAsync(c->stats, 0, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long), c->stream));
+    return RT_OK;
+}
+
+// ---- diagnostics -------------------------------------------------------------------------------
+int rt_debug_eval_math(int device, int kind, const float *a, const float *b, float *out, size_t n)
+{
+    if (!a || !out || kind < 0 || kind > 2 || (kind != 0 && !b)) return RT_EINVAL;
+    if (rt_device_count() <= device || device < 0) return RT_ENODEVICE;
+    if (n == 0) return RT_OK;
+    if (cudaSetDevice(device) != cudaSuccess) return RT_ECUDA;
+    float *da = nullptr, *db = nullptr, *dout = nullptr;
+    cudaError_t e = cudaMalloc((void **)&da, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&db, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&dout, n * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(da, a, n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = b ? cudaMemcpy(db, b, n * 4, cudaMemcpyHostToDevice) : cudaMemset(db, 0, n * 4);
+    if (e == cudaSuccess) e = launch_eval_math(kind, da, db, dout, n, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(out, dout, n * 4, cudaMemcpyDeviceToHost);
+    cudaFree(da); cudaFree(db); cudaFree(dout);
+    if (e != cudaSuccess) { g_create_err = cudaGetErrorString(e); cudaGetLastError(); return RT_ECUDA; }
+    return RT_OK;
+}
+
+int rt_measure_fp32_peak(int device, double *tflops_out)
+{
+    if (!tflops_out) return RT_EINVAL;
+    if (rt_device_count() <= device || device < 0) return RT_ENODEVICE;
+    if (cudaSetDevice(device) != cudaSuccess) return RT_ECUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return RT_ECUDA;
+    float *sink = nullptr;
+    cudaEvent_t e0, e1;
+    if (cudaMalloc((void **)&sink, 4) != cudaSuccess) return RT_ENOMEM;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int blocks = prop.multiProcessorCount * 8, iters = 4096;
+    double best = 0.0;
+    for (int rep = 0; rep < 6; rep++) {
+        cudaEventRecord(e0, 0);
+        launch_fp32_peak(sink, blocks, iters, 0);
+        cudaEventRecord(e1, 0);
+        if (cudaEventSynchronize(e1) != cudaSuccess) break;
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double flops = (double)blocks * 256.0 * iters * 16.0 * 8.0 * 2.0;
+        double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return RT_ECUDA;
+    *tflops_out = best;
+    return RT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,711 @@
+// rt_kernels.cu -- sm_100a kernels of the per-pixel hot path.
+//
+//   rt_ao_trace_kernel      <- resources/ao_compute.glsl:161-340 (= aop_compute.glsl:159-337)
+//   rt_phong_kernel         <- resources/p_compute.glsl:145-246
+//   rt_hybrid_kernel        <- resources/h_compute.glsl:145-322
+//   rt_halo_pack_kernel     <- the out-of-range neighbour reads of aop_postprocessing.glsl:81-90,150-159
+//   rt_ao_postprocess_kernel<- resources/aop_postprocessing.glsl:57-209
+//
+// FP32 CUDA-core work, no tensor cores (nothing here is a contraction).  The reference launches
+// one 1x1 work-group per pixel (1 live lane per warp, src/main.cpp:604); here a warp owns an
+// 8x4 pixel tile so primary rays are coherent and every G-buffer store is a full 128-byte line.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -prec-div=true -prec-sqrt=true
+#include "rt_kernels.cuh"
+#include "rt_math.cuh"
+
+namespace rt {
+
+// ---------------------------------------------------------------------------------------------
+// intersection (ao_compute.glsl:75-136)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float sphere_eval_ray(float3 pos, float3 dir, float4 s0, float r2)
+{
+    float3 pmc = sub3(pos, xyz(s0));
+    float b = dot3(dir, pmc);
+    float del = b * b - dot3(pmc, pmc) + r2;
+    float res = -1.0f;
+    if (del == 0.0f) {
+        res = -b;
+    } else if (del > 0.0f) {
+        float im = __fsqrt_rn(del);
+        float t1 = -b + im;
+        float t2 = -b - im;
+        res = (t2 < 0.0f) ? ((t1 < 0.0f) ? -1.0f : t1) : t2;
+    }
+    return res;
+}
+
+__device__ __forceinline__ float plane_eval_ray(float3 pos, float3 dir, float4 s0, float4 s3)
+{
+    float3 n = xyz(s0);
+    float denom = dot3(n, dir);
+    if (denom < 0.001f && denom > -0.001f) return -1.0f;
+    return __fdiv_rn(dot3(n, sub3(xyz(s3), pos)), denom);
+}
+
+__device__ __forceinline__ float eval_ray(const DevShape &s, float3 pos, float3 dir)
+{
+    if (s.id == SPHERE_ID) return sphere_eval_ray(pos, dir, s.s0, s.r2);
+    if (s.id == PLANE_ID) return plane_eval_ray(pos, dir, s.s0, s.s3);
+    return -1.0f;
+}
+
+// closest hit over the object table, read from the constant bank with warp-uniform indices
+// (ao_compute.glsl:183-194 / p_compute.glsl:177-188 / h_compute.glsl:199-210)
+__device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, float3 dir, float tmin, float &t_out)
+{
+    float t = -1.0f;
+    int ind = -1;
+#pragma unroll
+    for (int i = 0; i < RT_MAX_SHAPES; i++) {
+        if (i >= p.nshapes) break;
+        float res_t = eval_ray(p.shapes[i], pos, dir);
+        if (res_t > tmin && (res_t < t || t < 0.0f)) {
+            t = res_t;
+            ind = i;
+        }
+    }
+    t_out = t;
+    return ind;
+}
+
+__device__ __forceinline__ float3 shape_normal(const DevShape &s, float3 pt)
+{
+    if (s.id == SPHERE_ID) return normalize3(sub3(pt, xyz(s.s0)));
+    return xyz(s.s0);
+}
+
+__device__ __forceinline__ float3 primary_dir(const FrameParams &p, float hp, float vp)
+{
+    return normalize3(add3(add3(p.llc, scale3(hp, p.horiz)), scale3(vp, p.vert)));
+}
+
+// ao_compute.glsl:143-158
+__device__ __forceinline__ float3 get_pt_within_unit_sphere(float4 r0, float4 r1, float fx, float fy)
+{
+    float a = random2(r0.x + fx * r1.z, r0.y + fy * r1.w) * 2.0f - 1.0f;
+    float b = random2(r0.z - fx * r1.z, r0.w - fy * r1.w) * 2.0f - 1.0f;
+    float c = random2(r1.x * fx + r1.z, r1.y * fy + r1.w) * 2.0f - 1.0f;
+    return normalize3(mk3(a, b, c));
+}
+
+__device__ __forceinline__ float4 gamma_correct(float r, float g, float b)
+{
+    const float gm = __fdiv_rn(1.0f, 2.2f);
+    return make_float4(pow_f32(r, gm), pow_f32(g, gm), pow_f32(b, gm), 0.0f);
+}
+
+// pixel owned by this thread: a block is a 16x8 pixel tile, each warp an 8x4 sub-tile
+constexpr int TILE_W = 16, TILE_H = 8, TRACE_THREADS = 128;
+__device__ __forceinline__ void tile_pixel(int &x, int &yl)
+{
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    x = blockIdx.x * TILE_W + ((warp & 1) << 3) + (lane & 7);
+    yl = blockIdx.y * TILE_H + ((warp >> 1) << 2) + (lane >> 3);
+}
+
+// block-level reduction of per-thread counters into one stripe of the global statistics
+template <int N>
+__device__ __forceinline__ void flush_stats(unsigned long long *stats, const int (&idx)[N], unsigned (&val)[N])
+{
+    __shared__ unsigned s_acc[N];
+    if (threadIdx.x < N) s_acc[threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < N; k++) {
+        unsigned v = __reduce_add_sync(0xffffffffu, val[k]);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_acc[k], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < N && s_acc[threadIdx.x]) {
+        unsigned stripe = (blockIdx.x + blockIdx.y * gridDim.x) % STAT_STRIPES;
+        atomicAdd(&stats[stripe * ST_COUNT + idx[threadIdx.x]], (unsigned long long)s_acc[threadIdx.x]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// AO trace (modes 1 and 2)
+// ---------------------------------------------------------------------------------------------
+// One thread per pixel.  The AA samples and their <= RD path segments are flattened into ONE loop
+// whose body is one segment, so a warp stays converged on the intersection code and its run time is
+// max over lanes of the pixel's total segment count (not the sum over samples of the per-sample max).
+__global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+{
+    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ float4 s_rand[2 * RT_MAX_AA];
+    for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
+    for (int i = threadIdx.x; i < 2 * p.AA; i += blockDim.x) s_rand[i] = p.rand[i];
+    __syncthreads();
+
+    int x, yl;
+    tile_pixel(x, yl);
+    const bool active = (x < p.W) && (yl < p.rows);
+    const int y = p.y0 + yl;
+    const size_t pix = (size_t)yl * p.W + x;
+    unsigned n_nonterm = 0, n_term = 0;
+
+    if (active) {
+        const float fx = (float)x, fy = (float)y;
+        const float fW = (float)p.W, fH = (float)p.H;
+        float ar = 0.0f, ag = 0.0f, ab = 0.0f;   // result_color summed over samples
+        float3 nrm = mk3(0.0f, 0.0f, 0.0f);
+        float nrm_w = 0.0f;
+        float dx = 0.0f, dy = 0.0f, dw = 0.0f;  // depth_buffer[frame][x][y] (.z is always 0)
+        bool keep_normal = false;
+        int hit0 = -1;
+
+        int aa = 0;
+        bool need_new = true, have_ru = false;
+        float3 pos = p.cam, dir = p.cam, ru = p.cam;
+        float cr = 1.0f, cg = 1.0f, cb = 1.0f;
+        int i = p.RD;
+
+        while (aa < p.AA) {
+            if (need_new) {
+                float hp, vp;
+                if (aa == 0) {
+                    hp = __fdiv_rn(fx, fW);
+                    vp = __fdiv_rn(fy, fH);
+                } else {
+                    // ao_compute.glsl:310-323, seeds cross-wired exactly as written there
+                    float4 rf = s_rand[2 * aa], rs = s_rand[2 * aa + 1];
+                    float s1x = rs.x, s1y = rf.y, s2x = rf.z, s2y = rs.w;
+                    float s3x = rf.x, s3y = rs.y, s4x = rs.z, s4y = rf.w;
+                    float ax = ((s1x + fx * s2x) - fx) + s3x;
+                    float ay = ((s1y + fy * s2y) - fy) + s3y;
+                    float bx = s4x * fx - (s3x * fx) * s2x;
+                    float by = s4y * fy - (s3y * fy) * s2y;
+                    float r1 = random2(ax, ay), r2 = random2(bx, by);
+                    float inv = __fdiv_rn(1.0f, __fsqrt_rn(dot2(r1, r2, r1, r2)));
+                    float jx = __fdiv_rn(r1 * inv, 6.0f) - 0.08333f;
+                    float jy = __fdiv_rn(r2 * inv, 6.0f) - 0.08333f;
+                    hp = __fdiv_rn(fx + jx, fW);
+                    vp = __fdiv_rn(fy + jy, fH);
+                }
+                dir = primary_dir(p, hp, vp);
+                pos = p.cam;
+                cr = cg = cb = 1.0f;
+                i = p.RD;
+                need_new = false;
+                have_ru = false;
+            }
+
+            // ---- one path segment: ambient_occlusion_helper, ao_compute.glsl:161-261 ----
+            float t;
+            const int ind = closest_hit(p, pos, dir, 0.0001f, t);
+            const bool first = (aa == 0) && (i == p.RD);
+            if (first) hit0 = ind;
+            bool stop;
+            float a0r, a0g, a0b;
+            if (ind < 0) {
+                if (first) { nrm = mk3(0.0f, 0.0f, 0.0f); nrm_w = 0.0f; dx = 0.0f; dw = 0.0f; }
+                a0r = p.bg.x; a0g = p.bg.y; a0b = p.bg.z;
+                stop = true;
+                dy = (float)(p.RD - i);
+            } else {
+                const DevShape &s = s_shapes[ind];
+                a0r = s.col.x; a0g = s.col.y; a0b = s.col.z;
+                if (s.emissive > 0.9f) {
+                    if (first) {
+                        // the shader returns before touching normals/depth: the slot keeps what an
+                        // earlier frame left there (ao_compute.glsl:199-208 precede :222-229)
+                        keep_normal = true;
+                        float2 od = o.depth_xy[pix];
+                        dx = od.x;
+                        dw = o.depth_w[pix];
+                    }
+                    stop = true;
+                    dy = (float)(p.RD - i);
+                } else {
+                    float3 curr_pos = add3(p.cam, scale3(t, dir)); // camera origin even on bounces (:210)
+                    float3 normal = shape_normal(s, curr_pos);
+                    if (first) { nrm = normal; nrm_w = 1.0f; dx = t; dy = 0.0f; dw = 1.0f; }
+                    pos = curr_pos;
+                    if (!have_ru) {
+                        ru = get_pt_within_unit_sphere(s_rand[2 * aa], s_rand[2 * aa + 1], fx, fy);
+                        have_ru = true;
+                    }
+                    float refl = s.s3.w;
+                    if (refl > 0.999f) {
+                        dir = normalize3(add3(ru, normal));
+                    } else {
+                        float dn = dot3(dir, normal);
+                        float3 R = normalize3(sub3(dir, scale3(2.0f, scale3(dn, normal))));
+                        dir = normalize3(add3(R, scale3(refl, ru)));
+                    }
+                    stop = false;
+                }
+            }
+            cr *= a0r; cg *= a0g; cb *= a0b;
+            if (stop) n_term++; else n_nonterm++;
+            i--;
+            if (stop || i == 0) {
+                ar += cr; ag += cg; ab += cb;
+                aa++;
+                need_new = true;
+            }
+        }
+
+        const float fAA = (float)p.AA;
+        float4 c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+        o.color[pix] = c;
+        if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
+        o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
+        o.depth_w[pix] = __fdiv_rn(dw, fAA);
+        o.hit[pix] = hit0;
+    }
+
+    const int idx[6] = { ST_SEG_NONTERMINAL, ST_SEG_TERMINAL, ST_RAYS_CLOSEST, ST_PIXELS, ST_PRIMARY, ST_JITTERED };
+    unsigned val[6] = { n_nonterm, n_term, n_nonterm + n_term, active ? 1u : 0u, active ? 1u : 0u,
+                        active ? (unsigned)(p.AA - 1) : 0u };
+    flush_stats<6>(o.stats, idx, val);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Phong (mode 3) and Phong + reflections (mode 4)
+// ---------------------------------------------------------------------------------------------
+// shadow_ray, p_compute.glsl:145-166: FP64 t and FP64 length, every object tested
+__device__ __forceinline__ bool shadow_ray(const FrameParams &p, float3 pos)
+{
+    float3 lv = sub3(p.light, pos);
+    float3 l = normalize3(lv);
+    float len = length3(lv);
+    float3 new_pos = add3(pos, scale3(0.01f, l));
+    bool lit = true;
+#pragma unroll
+    for (int i = 0; i < RT_MAX_SHAPES; i++) {
+        if (i >= p.nshapes) break;
+        double t = (double)eval_ray(p.shapes[i], new_pos, l);
+        if (lit && t > (double)0.0001f) {
+            double ln = dlength3(__dmul_rn(t, (double)l.x), __dmul_rn(t, (double)l.y), __dmul_rn(t, (double)l.z));
+            if (ln < (double)len) lit = false;
+        }
+    }
+    return lit;
+}
+
+// lit / shadowed colour of a hit on the full vec4 (h_compute.glsl:231-249; p_compute.glsl:205-218
+// is the same arithmetic with w = 0)
+__device__ __forceinline__ float4 phong_shade(const FrameParams &p, float4 att, float3 curr_pos, float3 dir,
+                                              float3 normal, bool lit)
+{
+    if (lit) {
+        float3 l = normalize3(sub3(p.light, curr_pos));
+        float spec = pow_f32(clampf(dot3(normalize3(sub3(l, dir)), normal), 0.0f, 1.0f), 500.0f);
+        float4 r = scale4(clampf(dot3(normal, l), 0.06f, 1.0f), att);
+        return make_float4(r.x + spec, r.y + spec, r.z + spec, r.w + spec);
+    }
+    return scale4(0.06f, att);
+}
+
+__global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+{
+    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
+    __syncthreads();
+    int x, yl;
+    tile_pixel(x, yl);
+    const bool active = (x < p.W) && (yl < p.rows);
+    unsigned n_shadow = 0;
+    if (active) {
+        const int y = p.y0 + yl;
+        const size_t pix = (size_t)yl * p.W + x;
+        float3 dir = primary_dir(p, __fdiv_rn((float)x, (float)p.W), __fdiv_rn((float)y, (float)p.H));
+        float t;
+        int ind = closest_hit(p, p.cam, dir, 0.0f, t);
+        float4 col;
+        if (ind < 0) {
+            col = p.bg;
+        } else {
+            const DevShape &s = s_shapes[ind];
+            float3 curr_pos = add3(p.cam, scale3(t, dir));
+            bool lit = shadow_ray(p, curr_pos);
+            n_shadow = 1;
+            float3 normal = shape_normal(s, curr_pos);
+            float4 att = make_float4(s.col.x, s.col.y, s.col.z, 0.0f);
+            col = phong_shade(p, att, curr_pos, dir, normal, lit);
+        }
+        // result_color = vec4(0) + phong(dir)
+        o.color[pix] = gamma_correct(0.0f + col.x, 0.0f + col.y, 0.0f + col.z);
+        o.hit[pix] = ind;
+    }
+    const int idx[5] = { ST_RAYS_CLOSEST, ST_RAYS_SHADOW, ST_SHADED, ST_PIXELS, ST_PRIMARY };
+    unsigned val[5] = { active ? 1u : 0u, n_shadow, n_shadow, active ? 1u : 0u, active ? 1u : 0u };
+    flush_stats<5>(o.stats, idx, val);
+}
+
+__global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+{
+    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
+    __syncthreads();
+    int x, yl;
+    tile_pixel(x, yl);
+    const bool active = (x < p.W) && (yl < p.rows);
+    unsigned n_rays = 0, n_shaded = 0, n_refl = 0;
+    if (active) {
+        const int y = p.y0 + yl;
+        const size_t pix = (size_t)yl * p.W + x;
+        float3 dir = primary_dir(p, __fdiv_rn((float)x, (float)p.W), __fdiv_rn((float)y, (float)p.H));
+        float3 pos = p.cam;
+        float4 result = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float cw = 0.0f, a2w = 0.0f;
+        int first_ind = -1;
+        // hybrid(): h_compute.glsl:269-297, first segment peeled there, folded into the loop here
+        for (int i = p.RD; i > 0; i--) {
+            float t;
+            int ind = closest_hit(p, pos, dir, 0.001f, t);
+            n_rays++;
+            if (i == p.RD) first_ind = ind;
+            float4 a0;
+            bool stop = false;
+            if (ind < 0) {
+                a0 = p.bg;
+                stop = true;
+            } else {
+                const DevShape &s = s_shapes[ind];
+                float3 curr_pos = add3(pos, scale3(t, dir));
+                bool lit = shadow_ray(p, curr_pos);
+                float3 normal = shape_normal(s, curr_pos);
+                a0 = phong_shade(p, s.col, curr_pos, dir, normal, lit);
+                n_shaded++;
+                float reflectivity = 1.0f - s.s3.w;
+                if (reflectivity < 0.001f) {
+                    stop = true;
+                } else {
+                    float dn = dot3(dir, normal);
+                    dir = normalize3(sub3(dir, scale3(2.0f, scale3(dn, normal))));
+                    pos = curr_pos;
+                    a2w = reflectivity;
+                    n_refl++;
+                }
+            }
+            if (i == p.RD) {
+                cw = a2w;
+                result = a0;
+            } else {
+                result = div4(add4(result, scale4(cw, a0)), 1.0f + cw);
+                cw = cw * a2w;
+            }
+            if (stop) break;
+        }
+        o.color[pix] = gamma_correct(0.0f + result.x, 0.0f + result.y, 0.0f + result.z);
+        o.hit[pix] = first_ind;
+    }
+    const int idx[6] = { ST_RAYS_CLOSEST, ST_RAYS_SHADOW, ST_SHADED, ST_REFLECTIVE, ST_PIXELS, ST_PRIMARY };
+    unsigned val[6] = { n_rays, n_shaded, n_shaded, n_refl, active ? 1u : 0u, active ? 1u : 0u };
+    flush_stats<6>(o.stats, idx, val);
+}
+
+cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s)
+{
+    dim3 grid((p.W + TILE_W - 1) / TILE_W, (p.rows + TILE_H - 1) / TILE_H);
+    dim3 block(TRACE_THREADS);
+    if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO)
+        rt_ao_trace_kernel<<<grid, block, 0, s>>>(p, o);
+    else if (p.mode == RT_MODE_PHONG)
+        rt_phong_kernel<<<grid, block, 0, s>>>(p, o);
+    else
+        rt_hybrid_kernel<<<grid, block, 0, s>>>(p, o);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// post-processing (mode 1, second pass)
+// ---------------------------------------------------------------------------------------------
+// Packs the rows a neighbouring band needs.  send_lo = this band's bottom row, send_hi = its top
+// row.  Under FLAT32 the band that owns image row H-1 instead builds, in send_hi, the row that the
+// shader's `[f][x][y - 1]` with y = 0 (uint wrap) actually addresses: flat index (f*W + x)*H - 1,
+// i.e. (x-1, H-1) of the same slot, and for x = 0 the last element of the previous slot / array
+// (aop_postprocessing.glsl:150-159 over the layout of src/main.cpp:79-84).
+__global__ void rt_halo_pack_kernel(PostParams q)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= q.W) return;
+    const size_t plane = (size_t)q.rows * q.W;
+    const float4 *nslot = q.ring_normal + (size_t)q.slot * plane;
+    const float2 *dslot = q.ring_depth_xy + (size_t)q.slot * plane;
+    if (q.send_lo) {
+        HaloRow lo = halo_row_view(q.send_lo, q.W);
+        lo.color[x] = q.raw[x];
+        lo.normal[x] = nslot[x];
+        lo.depth[x] = dslot[x];
+    }
+    if (!q.send_hi) return;
+    HaloRow hi = halo_row_view(q.send_hi, q.W);
+    const size_t top = (size_t)(q.rows - 1) * q.W;
+    const bool owns_top = (q.y0 + q.rows == q.H);
+    if (q.edge_mode == RT_EDGE_FLAT32 && owns_top) {
+        if (x >= 1) {
+            hi.color[x] = q.raw[top + x - 1];
+            hi.normal[x] = nslot[top + x - 1];
+            hi.depth[x] = dslot[top + x - 1];
+        } else if (q.slot >= 1) {
+            const size_t last = (size_t)(q.slot - 1) * plane + top + q.W - 1;
+            hi.color[0] = q.ring_color[last];
+            hi.normal[0] = q.ring_normal[last];
+            hi.depth[0] = q.ring_depth_xy[last];
+        } else {
+            // slot 0, x 0: one element before each array = the last element of the array before it
+            const size_t last = (size_t)(q.NF - 1) * plane + top + q.W - 1;
+            hi.color[0] = q.rand_last;          // pixels[-1]  = rand_buffer[2*AA-1]
+            hi.normal[0] = q.ring_color[last];  // normals[-1] = pixels[NF-1][W-1][H-1]
+            float4 n = q.ring_normal[last];     // depth[-1]   = normals_buffer[NF-1][W-1][H-1]
+            hi.depth[0] = make_float2(n.x, n.y);
+        }
+    } else {
+        hi.color[x] = q.raw[top + x];
+        hi.normal[x] = nslot[top + x];
+        hi.depth[x] = dslot[top + x];
+    }
+}
+
+struct NbRec { float4 color, normal; float2 depth; };
+
+__device__ __forceinline__ float nb_weight(float4 nn, float nd, float nb, const NbRec &r)
+{
+    if (r.normal.w < 0.001f) return 1.0f;
+    float normal_dot = dot3(xyz(nn), xyz(r.normal));
+    float depth_diff = 1.0f - clampf(fabsf(nd - r.depth.x), 0.0f, 1.0f);
+    float bounces_diff = 1.0f - clampf(__fdiv_rn(fabsf(nb - r.depth.y), 1.7f), 0.0f, 1.0f);
+    return normal_dot * depth_diff * bounces_diff + 0.2f;
+}
+
+constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 8;
+
+__global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y) rt_ao_postprocess_kernel(const __grid_constant__ PostParams q)
+{
+    const int x = blockIdx.x * PP_BLOCK_X + threadIdx.x;
+    const int yl = blockIdx.y * PP_BLOCK_Y + threadIdx.y;
+    const bool active = (x < q.W) && (yl < q.rows);
+    unsigned n_nonbg = 0, n_eval = 0, n_acc = 0;
+    if (active) {
+        const int y = q.y0 + yl;
+        const size_t plane = (size_t)q.rows * q.W;
+        const size_t pix = (size_t)yl * q.W + x;
+        const float4 *nslot = q.ring_normal + (size_t)q.slot * plane;
+        const float2 *dslot = q.ring_depth_xy + (size_t)q.slot * plane;
+        float4 color = q.raw[pix];
+        const float4 nn = nslot[pix];
+        if (nn.w > 0.99f) {
+            n_nonbg = 1;
+            const float2 dd = dslot[pix];
+            const float new_depth = dd.x, new_bounces = dd.y;
+            const bool flat = (q.edge_mode == RT_EDGE_FLAT32);
+            const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            NbRec R, L, U, D;
+            R.color = L.color = U.color = D.color = z4;
+            float r = 0.0f, l = 0.0f, u = 0.0f, d = 0.0f;
+
+            // right: x < WIDTH is always true in the shader (:81); CLEAN uses x + 1 < WIDTH
+            if (x + 1 < q.W) {
+                R.color = q.raw[pix + 1]; R.normal = nslot[pix + 1]; R.depth = dslot[pix + 1];
+                r = nb_weight(nn, new_depth, new_bounces, R);
+            } else if (flat) {
+                // [f][W][y] is [f+1][0][y]; past the last slot it is the next array's [0][0][y]
+                const size_t col0 = (size_t)yl * q.W;
+                if (q.slot + 1 < q.NF) {
+                    const size_t off = (size_t)(q.slot + 1) * plane + col0;
+                    R.color = q.ring_color[off]; R.normal = q.ring_normal[off]; R.depth = q.ring_depth_xy[off];
+                } else {
+                    R.color = q.ring_normal[col0];                   // pixels -> normals_buffer[0][0][y]
+                    float2 d0 = q.ring_depth_xy[col0];               // normals -> depth_buffer[0][0][y]
+                    R.normal = make_float4(d0.x, d0.y, 0.0f, q.ring_depth_w[col0]);
+                    R.depth = make_float2(0.0f, 0.0f);               // depth -> past the struct
+                }
+                r = nb_weight(nn, new_depth, new_bounces, R);
+            }
+            if (x > 0) {
+                L.color = q.raw[pix - 1]; L.normal = nslot[pix - 1]; L.depth = dslot[pix - 1];
+                l = nb_weight(nn, new_depth, new_bounces, L);
+            }
+            if (y + 1 < q.H) {
+                if (yl + 1 < q.rows) {
+                    U.color = q.raw[pix + q.W]; U.normal = nslot[pix + q.W]; U.depth = dslot[pix + q.W];
+                } else {
+                    HaloRow h = halo_row_view(q.halo_hi, q.W);
+                    U.color = h.color[x]; U.normal = h.normal[x]; U.depth = h.depth[x];
+                }
+                u = nb_weight(nn, new_depth, new_bounces, U);
+            }
+            // down: `y - 1 > 0` on a uint (:150) is true for y = 0 and false for y = 1
+            const bool has_d = flat ? (y != 1) : (y > 0);
+            if (has_d) {
+                if (yl > 0) {
+                    D.color = q.raw[pix - q.W]; D.normal = nslot[pix - q.W]; D.depth = dslot[pix - q.W];
+                } else {
+                    HaloRow h = halo_row_view(q.halo_lo, q.W);
+                    D.color = h.color[x]; D.normal = h.normal[x]; D.depth = h.depth[x];
+                }
+                d = nb_weight(nn, new_depth, new_bounces, D);
+            }
+            // color = (color + u*up + d*down + l*left + r*right) / (1 + u + d + l + r)   (:173)
+            float4 num = add4(add4(add4(add4(color, scale4(u, U.color)), scale4(d, D.color)), scale4(l, L.color)),
+                              scale4(r, R.color));
+            color = div4(num, 1.0f + u + d + l + r);
+
+            // temporal blend over the previous NF-1 ring slots (:175-201)
+            float4 color_sum = z4;
+            float denominator = 0.9f;
+            for (int i = 1; i < q.NF; i++) {
+                int cf = q.slot - i;
+                if (cf < 0) cf += q.NF;
+                const size_t off = (size_t)cf * plane + pix;
+                const float4 cn = q.ring_normal[off];
+                const float2 cd = q.ring_depth_xy[off];
+                n_eval++;
+                float normal_dot = dot3(xyz(nn), xyz(cn));
+                float depth_diff = 1.0f - clampf(fabsf(new_depth - cd.x), 0.0f, 1.0f);
+                float bounces_diff = 1.0f - clampf(__fdiv_rn(fabsf(new_bounces - cd.y), 1.7f), 0.0f, 1.0f);
+                float coeff = normal_dot * depth_diff * bounces_diff;
+                if (coeff > 0.85f) {
+                    color_sum = add4(color_sum, scale4(coeff, q.ring_color[off]));
+                    denominator += coeff;
+                    n_acc++;
+                } else
+                    break;
+            }
+            color = div4(add4(scale4(0.9f, color), color_sum), denominator);
+        }
+        q.ring_color[(size_t)q.slot * plane + pix] = color; // pixels[new_frame] and img_output
+    }
+    const int idx[3] = { ST_PP_NONBACKGROUND, ST_PP_HIST_EVALUATED, ST_PP_HIST_ACCEPTED };
+    unsigned val[3] = { n_nonbg, n_eval, n_acc };
+    // flush_stats indexes by threadIdx.x; this block is 2-D
+    __shared__ unsigned s_acc[3];
+    const int tid = threadIdx.y * PP_BLOCK_X + threadIdx.x;
+    if (tid < 3) s_acc[tid] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        unsigned v = __reduce_add_sync(0xffffffffu, val[k]);
+        if ((tid & 31) == 0 && v) atomicAdd(&s_acc[k], v);
+    }
+    __syncthreads();
+    if (tid < 3 && s_acc[tid]) {
+        unsigned stripe = (blockIdx.x + blockIdx.y * gridDim.x) % STAT_STRIPES;
+        atomicAdd(&q.stats[stripe * ST_COUNT + idx[tid]], (unsigned long long)s_acc[tid]);
+    }
+}
+
+cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s)
+{
+    rt_halo_pack_kernel<<<(q.W + 255) / 256, 256, 0, s>>>(q);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s)
+{
+    dim3 grid((q.W + PP_BLOCK_X - 1) / PP_BLOCK_X, (q.rows + PP_BLOCK_Y - 1) / PP_BLOCK_Y);
+    dim3 block(PP_BLOCK_X, PP_BLOCK_Y);
+    rt_ao_postprocess_kernel<<<grid, block, 0, s>>>(q);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// layout helpers for rt_download / rt_upload
+// ---------------------------------------------------------------------------------------------
+// row-major [rows][W] <-> the reference's x-major [W][rows] (src/main.cpp:81-84), tiled through
+// shared memory so both sides are coalesced
+template <typename T>
+__global__ void rt_transpose_kernel(const T *__restrict__ src, T *__restrict__ dst, int src_w, int src_h)
+{
+    __shared__ T tile[32][33];
+    int x = blockIdx.x * 32 + threadIdx.x;
+    int y0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int y = y0 + j;
+        if (x < src_w && y < src_h) tile[j][threadIdx.x] = src[(size_t)y * src_w + x];
+    }
+    __syncthreads();
+    int ox = blockIdx.y * 32 + threadIdx.x; // along src_h
+    int oy0 = blockIdx.x * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int oy = oy0 + j; // along src_w
+        if (ox < src_h && oy < src_w) dst[(size_t)oy * src_h + ox] = tile[threadIdx.x][j];
+    }
+}
+
+cudaError_t launch_transpose(const void *src, void *dst, int W, int rows, int elem_bytes, bool to_reference, cudaStream_t s)
+{
+    // to_reference: src is [rows][W] -> dst [W][rows]; otherwise src is [W][rows] -> dst [rows][W]
+    int sw = to_reference ? W : rows, sh = to_reference ? rows : W;
+    dim3 grid((sw + 31) / 32, (sh + 31) / 32), block(32, 8);
+    if (elem_bytes == 16)
+        rt_transpose_kernel<float4><<<grid, block, 0, s>>>((const float4 *)src, (float4 *)dst, sw, sh);
+    else if (elem_bytes == 4)
+        rt_transpose_kernel<int><<<grid, block, 0, s>>>((const int *)src, (int *)dst, sw, sh);
+    else
+        return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+__global__ void rt_expand_depth_kernel(const float2 *xy, const float *w, float4 *out, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        float2 d = xy[i];
+        out[i] = make_float4(d.x, d.y, 0.0f, w[i]);
+    }
+}
+__global__ void rt_split_depth_kernel(const float4 *in, float2 *xy, float *w, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        float4 d = in[i];
+        xy[i] = make_float2(d.x, d.y);
+        w[i] = d.w;
+    }
+}
+cudaError_t launch_expand_depth(const float2 *xy, const float *w, float4 *out, size_t n, cudaStream_t s)
+{
+    rt_expand_depth_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(xy, w, out, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_split_depth(const float4 *in, float2 *xy, float *w, size_t n, cudaStream_t s)
+{
+    rt_split_depth_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, xy, w, n);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// diagnostics
+// ---------------------------------------------------------------------------------------------
+__global__ void rt_eval_math_kernel(int kind, const float *a, const float *b, float *out, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (kind == 0) out[i] = sin_f32(a[i]);
+    else if (kind == 1) out[i] = pow_f32(a[i], b[i]);
+    else out[i] = random2(a[i], b[i]);
+}
+cudaError_t launch_eval_math(int kind, const float *a, const float *b, float *out, size_t n, cudaStream_t s)
+{
+    rt_eval_math_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(kind, a, b, out, n);
+    return cudaGetLastError();
+}
+
+// FP32 FMA roofline probe: 8 independent chains per thread, 2 flops per FFMA
+__global__ void __launch_bounds__(256) rt_fp32_peak_kernel(float *sink, int iters)
+{
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.0f, a2 = a0 + 2.0f, a3 = a0 + 3.0f;
+    float a4 = a0 + 4.0f, a5 = a0 + 5.0f, a6 = a0 + 6.0f, a7 = a0 + 7.0f;
+    const float m = 0.999f, c = 1e-3f;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            a0 = __fmaf_rn(a0, m, c); a1 = __fmaf_rn(a1, m, c); a2 = __fmaf_rn(a2, m, c); a3 = __fmaf_rn(a3, m, c);
+            a4 = __fmaf_rn(a4, m, c); a5 = __fmaf_rn(a5, m, c); a6 = __fmaf_rn(a6, m, c); a7 = __fmaf_rn(a7, m, c);
+        }
+    }
+    float r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (r == 123.456f) sink[0] = r; // never true; keeps the chains alive
+}
+cudaError_t launch_fp32_peak(float *sink, int blocks, int iters, cudaStream_t s)
+{
+    rt_fp32_peak_kernel<<<blocks, 256, 0, s>>>(sink, iters);
+    return cudaGetLastError();
+}
+
+} // namespace rt

@@ -1,0 +1,112 @@
+// rt_kernels.cuh -- device-side data contract shared by the kernels and the C ABI.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rt.h"
+
+namespace rt {
+
+constexpr int SPHERE_ID = 1; // resources/ao_compute.glsl:15-17
+constexpr int PLANE_ID = 5;
+
+// One scene object, rebuilt from the reference's vec4[5] record (src/main.cpp:59-77) by
+// rt_upload_scene.  r2 = radius * radius in binary32, the product the shader forms per test.
+struct DevShape {
+    float4 s0;  // sphere: (center, radius)   plane: (normal, dist)
+    float4 s3;  // (p0 | unused, reflectivity)
+    float4 col; // (color, id as float)  -- shape[4], the "attenuation"
+    float emissive; // shape[1].w
+    float r2;
+    int id; // int(col.w)
+    int pad;
+};
+
+// Everything a trace dispatch needs besides the output planes; passed by value as a
+// __grid_constant__ kernel parameter (constant bank), so the per-object loop reads it with
+// warp-uniform addresses.  This replaces the per-frame 55.8 MB SSBO upload of
+// src/main.cpp:598-602: ~1.4 KB travel per frame.
+struct FrameParams {
+    int W, H, AA, RD, NF;
+    int y0, rows; // row band [y0, y0 + rows)
+    int slot, nshapes, edge_mode, mode;
+    int band_index, band_count;
+    int pad0;
+    float3 llc, horiz, vert, cam, light;
+    float4 bg;
+    DevShape shapes[RT_MAX_SHAPES];
+    float4 rand[2 * RT_MAX_AA];
+};
+
+// statistics live in STAT_STRIPES interleaved copies to spread atomic traffic
+constexpr int STAT_STRIPES = 16;
+enum StatIdx {
+    ST_RAYS_CLOSEST = 0,
+    ST_RAYS_SHADOW,
+    ST_PRIMARY,
+    ST_JITTERED,
+    ST_SEG_NONTERMINAL,
+    ST_SEG_TERMINAL,
+    ST_SHADED,
+    ST_REFLECTIVE,
+    ST_PIXELS,
+    ST_PP_NONBACKGROUND,
+    ST_PP_HIST_EVALUATED,
+    ST_PP_HIST_ACCEPTED,
+    ST_COUNT
+};
+
+// output planes of one trace dispatch; all row-major [rows][W] of this band
+struct TraceOut {
+    float4 *color;    // ring colour plane of the slot, or the raw plane in mode 1
+    float4 *normal;   // ring normal plane of the slot
+    float2 *depth_xy; // ring depth.xy plane of the slot
+    float *depth_w;   // ring depth.w plane of the slot
+    int *hit;         // hit-index plane
+    unsigned long long *stats; // [STAT_STRIPES][ST_COUNT]
+};
+
+// a halo record row: three consecutive arrays of W elements
+struct HaloRow {
+    float4 *color;
+    float4 *normal;
+    float2 *depth;
+};
+__host__ __device__ inline size_t halo_row_bytes(int W) { return (size_t)W * 40; }
+__host__ __device__ inline HaloRow halo_row_view(void *base, int W)
+{
+    HaloRow h;
+    h.color = (float4 *)base;
+    h.normal = h.color + W;
+    h.depth = (float2 *)(h.normal + W);
+    return h;
+}
+
+struct PostParams {
+    int W, H, AA, NF;
+    int y0, rows;
+    int slot, edge_mode;
+    int band_index, band_count;
+    const float4 *raw;    // aop_compute output of this frame
+    float4 *ring_color;   // [NF][rows*W]
+    const float4 *ring_normal;
+    const float2 *ring_depth_xy;
+    const float *ring_depth_w;
+    void *halo_lo, *halo_hi;   // received records: row y0-1 (or the wrapped row) / row y0+rows
+    void *send_lo, *send_hi;   // packed by the pack kernel
+    float4 rand_last;          // rand_buffer[2*AA-1]: what pixels[0][0][-1] aliases (FLAT32)
+    unsigned long long *stats;
+};
+
+// launchers (rt_kernels.cu)
+cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s);
+cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s);
+cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s);
+cudaError_t launch_transpose(const void *src, void *dst, int W, int rows, int elem_bytes, bool to_reference, cudaStream_t s);
+cudaError_t launch_expand_depth(const float2 *xy, const float *w, float4 *out, size_t n, cudaStream_t s);
+cudaError_t launch_split_depth(const float4 *in, float2 *xy, float *w, size_t n, cudaStream_t s);
+cudaError_t launch_eval_math(int kind, const float *a, const float *b, float *out, size_t n, cudaStream_t s);
+cudaError_t launch_fp32_peak(float *sink, int blocks, int iters, cudaStream_t s);
+
+} // namespace rt

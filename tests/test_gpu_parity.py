@@ -1,0 +1,213 @@
+"""GPU parity: the CUDA path through the C ABI against the CPU oracle, bit-for-bit.
+
+north_star tolerances are hit-index bit-exact, colour PSNR >= 40 dB with >= 99.9 % of pixels within
+2/255, depth/normals within 1e-4 relative.  Because the GLSL built-ins are defined as explicit IEEE
+sequences on both sides, the bar used here is stricter: every buffer bit-identical."""
+import numpy as np
+import pytest
+
+import real_time_ray_tracer_b200 as rtb
+from real_time_ray_tracer_b200 import api
+from oracle import oracle as orc
+from tests.util import Scenario, diff_report, same_bits
+
+pytestmark = pytest.mark.gpu
+
+
+def check_frame(rt, o, slot, mode, what=""):
+    for buf, which, name in ((rtb.BUF_COLOR, orc.PIXELS, "color"), (rtb.BUF_NORMAL, orc.NORMALS, "normal"),
+                             (rtb.BUF_DEPTH, orc.DEPTH, "depth")):
+        got, want = rt.download(buf, slot), o.get(which, slot)
+        assert same_bits(got, want), f"{what} mode {mode} slot {slot} {name}: {diff_report(got, want)}"
+    assert np.array_equal(rt.download(rtb.BUF_HIT_INDEX), o.get(orc.HIT_INDEX)), f"{what} hit index"
+    assert same_bits(rt.download(rtb.BUF_IMAGE), o.get(orc.IMAGE)), f"{what} image"
+
+
+def test_math_builtins_bit_exact():
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.uniform(-5e5, 5e5, 200000), rng.uniform(-8, 8, 100000),
+                        [0.0, -0.0, 1e-30, 3.14159274, 1.57079637, 4.4e5, -4.4e5, 1e7, 1e30]]).astype(np.float32)
+    assert same_bits(api.debug_eval_math("sin", x), orc.eval_math("sin", x))
+    a = np.concatenate([rng.uniform(0, 1, 100000), rng.uniform(0, 20, 100000), [0.0, 1.0, 1e-38, 1e-45, 16.0]]).astype(np.float32)
+    for y in (1.0 / 2.2, 500.0):
+        b = np.full_like(a, np.float32(y))
+        assert same_bits(api.debug_eval_math("pow", a, b), orc.eval_math("pow", a, b))
+    sx = rng.uniform(0, 8000, 200000).astype(np.float32)
+    sy = rng.uniform(0, 4400, 200000).astype(np.float32)
+    assert same_bits(api.debug_eval_math("random", sx, sy), orc.eval_math("random", sx, sy))
+
+
+@pytest.mark.parametrize("scene", ["scene1", "scene5", "scene6"])
+@pytest.mark.parametrize("mode", [2, 3, 4, 1])
+@pytest.mark.parametrize("size", [(67, 45), (440, 330)])
+def test_single_frame_all_modes(scene, mode, size):
+    W, H = size
+    AA = 4
+    sc = Scenario(scene)
+    with rtb.RayTracer(W, H, AA) as rt:
+        o = orc.Oracle(W, H, AA)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        slot, u, rb = sc.next(mode, AA)
+        rt.render_frame(mode, u, rb)
+        o.render(mode, u, rb)
+        if mode == 1:
+            assert same_bits(rt.download(rtb.BUF_RAW_COLOR), o.get(orc.PIXELS, slot))
+            rt.postprocess()
+            o.postprocess()
+        check_frame(rt, o, slot, mode, f"{scene} {W}x{H}")
+        so, sg = o.stats(), rt.stats()
+        for k in so:
+            assert so[k] == sg[k], (k, so[k], sg[k])
+        o.close()
+
+
+def test_config1_phong_640x480():
+    """BASELINE.json configs[0]: mode 3, scene1, 640x480, single frame."""
+    W, H = 640, 480
+    sc = Scenario("scene1")
+    with rtb.RayTracer(W, H, 4) as rt:
+        o = orc.Oracle(W, H, 4)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        slot, u, rb = sc.next(3, 4)
+        rt.render_frame(3, u, None)
+        o.render(3, u, None)
+        assert same_bits(rt.download(rtb.BUF_COLOR, slot), o.get(orc.PIXELS, slot))
+        assert np.array_equal(rt.download(rtb.BUF_HIT_INDEX), o.get(orc.HIT_INDEX))
+        o.close()
+
+
+@pytest.mark.parametrize("edge_mode", [rtb.EDGE_FLAT32, rtb.EDGE_CLEAN])
+@pytest.mark.parametrize("scene,keys", [("scene1", ("d",)), ("scene6", ("e",)), ("scene5", ("w", "q"))])
+def test_mode1_sequence_moving_camera(edge_mode, scene, keys):
+    """20 frames of AO + post-processing with camera motion: exercises the history ring wrap-around,
+    the temporal accept/break logic, stale slots behind emissive primaries and the border semantics."""
+    W, H, AA = 96, 64, 4
+    sc = Scenario(scene, keys=keys)
+    with rtb.RayTracer(W, H, AA, edge_mode=edge_mode) as rt:
+        o = orc.Oracle(W, H, AA, edge_mode=edge_mode)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        for k in range(20):
+            slot, u, rb = sc.next(1, AA)
+            rt.render_frame(1, u, rb)
+            rt.postprocess()
+            o.render(1, u, rb)
+            o.postprocess()
+            check_frame(rt, o, slot, 1, f"{scene} frame {k} edge {edge_mode}")
+        assert o.stats()["pp_hist_accepted"] > 0
+        so, sg = o.stats(), rt.stats()
+        for k in so:
+            assert so[k] == sg[k], (k, so[k], sg[k])
+        o.close()
+
+
+def test_mode_switching_shares_the_ring():
+    """all modes write pixels[slot] of one ring (src/main.cpp:555); Phong frames leave normals/depth stale"""
+    W, H, AA = 80, 60, 4
+    sc = Scenario("scene1", keys=("a",), light_movement=True)
+    with rtb.RayTracer(W, H, AA) as rt:
+        o = orc.Oracle(W, H, AA)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        for k, mode in enumerate([1, 1, 3, 4, 1, 2, 1, 1, 3, 1, 1, 1]):
+            slot, u, rb = sc.next(mode, AA)
+            rt.render_frame(mode, u, rb)
+            o.render(mode, u, rb)
+            if mode == 1:
+                rt.postprocess()
+                o.postprocess()
+            check_frame(rt, o, slot, mode, f"frame {k}")
+        o.close()
+
+
+@pytest.mark.parametrize("aa", [1, 2, 16])
+def test_aa_counts(aa):
+    W, H = 64, 48
+    sc = Scenario("scene1")
+    with rtb.RayTracer(W, H, aa) as rt:
+        o = orc.Oracle(W, H, aa)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        for k in range(3):
+            slot, u, rb = sc.next(1, aa)
+            rt.render_frame(1, u, rb)
+            rt.postprocess()
+            o.render(1, u, rb)
+            o.postprocess()
+            check_frame(rt, o, slot, 1, f"aa {aa} frame {k}")
+        o.close()
+
+
+def test_reference_layout_and_upload_roundtrip():
+    W, H, AA = 50, 30, 2
+    rng = np.random.default_rng(3)
+    with rtb.RayTracer(W, H, AA) as rt:
+        for buf in (rtb.BUF_COLOR, rtb.BUF_NORMAL):
+            a = rng.standard_normal((H, W, 4)).astype(np.float32)
+            rt.upload(buf, 3, a)
+            assert same_bits(rt.download(buf, 3), a)
+            assert same_bits(rt.download(buf, 3, rtb.LAYOUT_REFERENCE), a.transpose(1, 0, 2))
+            rt.upload(buf, 5, a.transpose(1, 0, 2).copy(), rtb.LAYOUT_REFERENCE)
+            assert same_bits(rt.download(buf, 5), a)
+        d = rng.standard_normal((H, W, 4)).astype(np.float32)
+        d[..., 2] = 0
+        rt.upload(rtb.BUF_DEPTH, 1, d)
+        assert same_bits(rt.download(rtb.BUF_DEPTH, 1), d)
+        assert same_bits(rt.download(rtb.BUF_DEPTH, 1, rtb.LAYOUT_REFERENCE), d.transpose(1, 0, 2))
+
+
+def test_seeded_ring_garbage_history():
+    """post-processing over an arbitrary (uploaded) ring: every FLAT32 alias path gets non-zero data"""
+    W, H, AA, NF = 48, 40, 4, 8
+    rng = np.random.default_rng(7)
+    sc = Scenario("scene1")
+    with rtb.RayTracer(W, H, AA) as rt:
+        o = orc.Oracle(W, H, AA)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        for s in range(NF):
+            for buf, which in ((rtb.BUF_COLOR, orc.PIXELS), (rtb.BUF_NORMAL, orc.NORMALS), (rtb.BUF_DEPTH, orc.DEPTH)):
+                a = rng.uniform(0, 1, (H, W, 4)).astype(np.float32)
+                if buf == rtb.BUF_NORMAL:
+                    a[..., 3] = (rng.uniform(0, 1, (H, W)) > 0.3).astype(np.float32)
+                if buf == rtb.BUF_DEPTH:
+                    a[..., 2] = 0
+                rt.upload(buf, s, a)
+                o.put(which, s, a)
+        for k in range(10):  # slots 0..7, 0, 1: covers slot 0 and slot NF-1 alias cases
+            slot, u, rb = sc.next(1, AA)
+            rt.render_frame(1, u, rb)
+            rt.postprocess()
+            o.render(1, u, rb)
+            o.postprocess()
+            check_frame(rt, o, slot, 1, f"garbage ring frame {k}")
+        o.close()
+
+
+def test_errors_are_reported_not_fatal():
+    with rtb.RayTracer(32, 24, 4) as rt:
+        sc = Scenario("scene1")
+        slot, u, rb = sc.next(1, 4)
+        with pytest.raises(rtb.RtError):  # no scene uploaded: mode.z = 5 > 0 shapes
+            rt.render_frame(1, u, rb)
+        rt.upload_scene(sc.shapes, sc.n)
+        with pytest.raises(rtb.RtError):
+            rt.postprocess()  # nothing rendered in mode 1
+        with pytest.raises(rtb.RtError):
+            rt.render_frame(2, u, None)  # AO needs rand_buffer
+        with pytest.raises(rtb.RtError):
+            rt.render_frame(5, u, rb)  # "not yet implemented" (src/main.cpp:576)
+        bad = u.copy()
+        bad[0, 1] = 8
+        with pytest.raises(rtb.RtError):
+            rt.render_frame(2, bad, rb)
+        with pytest.raises(rtb.RtError):
+            rt.upload_scene(np.zeros((11, 5, 4), np.float32), 11)
+        rt.render_frame(2, u, rb)  # still usable
+        rt.synchronize()
+    with pytest.raises(rtb.RtError):
+        rtb.RayTracer(0, 10)
+    with pytest.raises(rtb.RtError):
+        rtb.RayTracer(10, 10, aa=17)
