@@ -49,7 +49,7 @@ RTR_INLINE double rtr_u2d(uint64_t u) { double d; memcpy(&d, &u, 8); return d; }
  * fdlibm k_sin.c set (even quadrant, leading coefficient 0) or the k_cos.c set
  * (odd quadrant).  Accurate to < 1 binary32 ulp for |x| < 2^20*pi/2, which
  * covers every argument the shaders produce up to 7680x4320
- * (|dot(st,(12.9898,78.233))| < 4.5e5).  Deterministic for any input.
+ * (|dot(st,(12.9898,78.233))| < 4.5e5).  Deterministic for any input; |x| >= 2^50 gives x - x.
  */
 #define RTR_TWO_OVER_PI 6.36619772367581382433e-01 /* 0x3FE45F306DC9C883 */
 #define RTR_PIO2_1 1.57079632673412561417e+00      /* 0x3FF921FB54400000 */
@@ -70,6 +70,8 @@ RTR_INLINE float rtr_sin(float x)
         -1.38888888888741095749e-03, 4.16666666666666019037e-02,
         -0.5 };
     double xd = (double)x;
+    /* outside the rounding trick's range (|x| >= 2^50, inf, NaN): 0 for finite x, NaN otherwise */
+    if (!(fabs(xd) < 1125899906842624.0)) return x - x;
     double kd = (xd * RTR_TWO_OVER_PI + RTR_RND_MAGIC) - RTR_RND_MAGIC;
     double r = fma(-kd, RTR_PIO2_1, xd);
     r = fma(-kd, RTR_PIO2_2, r);
