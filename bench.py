@@ -1,0 +1,476 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline metric (Mrays/s, frames/s per lighting mode) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+
+A step is one frame of the hot path.  Default workload = BASELINE.json configs[1]:
+ray-traced ambient occlusion (mode 2), default scene, 1920x1080, AA 4, fresh rand_buffer per frame.
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every definition used here.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from real_time_ray_tracer_b200 import host  # noqa: E402
+
+# name -> (mode, scene, W, H, AA, aspect, keys, light_movement)
+WORKLOADS = {
+    "config1_phong_640x480": (3, "scene1", 640, 480, 4, host.ASPECT_RATIO, (), False),
+    "config2_ao_1080p": (2, "scene1", 1920, 1080, 4, host.FULLSCREEN_ASPECT_RATIO, (), False),
+    "config3_hybrid_1080p": (4, "scene5", 1920, 1080, 4, host.FULLSCREEN_ASPECT_RATIO, (), True),
+    "config4_aopp_4k": (1, "scene1", 3840, 2160, 4, host.FULLSCREEN_ASPECT_RATIO, ("d",), False),
+    "config5_aopp_8k_aa16": (1, "scene1", 7680, 4320, 16, host.FULLSCREEN_ASPECT_RATIO, ("d",), False),
+}
+DEFAULT_WORKLOAD = "config2_ao_1080p"
+
+
+def flops_from_counters(st: dict, n_spheres: int, n_planes: int) -> float:
+    """Algorithmic FP32 flops of a frame from the ray counters, SURVEY.md 8(d) constants."""
+    f_trav = 20 * n_spheres + 14 * n_planes
+    return (st["rays_closest"] * f_trav + st["seg_nonterminal"] * 82 + st["seg_terminal"] * 4
+            + st["primary"] * 23 + st["jittered"] * 63 + st["rays_shadow"] * (f_trav + 33)
+            + st["shaded"] * 64 + st["reflective"] * 38 + st["pixels"] * 11)
+
+
+def pp_bytes_from_counters(st: dict) -> float:
+    """Algorithmic HBM bytes of the post-processing pass: every pixel reads raw colour 16 + normal 16
+    and writes the ring colour 16 (the image IS the ring slot: no second store); a non-background pixel
+    also reads depth.xy 8; per history frame evaluated 24 (normal 16 + depth.xy 8), +16 when its colour
+    is accepted.  Neighbour reads are not counted (each record is compulsory-loaded once)."""
+    return (st["pixels"] * 48 + st["pp_nonbackground"] * 8 + st["pp_hist_evaluated"] * 24
+            + st["pp_hist_accepted"] * 16)
+
+
+class Frames:
+    """Deterministic per-frame inputs of a workload, like Application.render() produces them."""
+
+    def __init__(self, name: str):
+        mode, scene, W, H, AA, aspect, keys, light = WORKLOADS[name]
+        self.name, self.mode, self.W, self.H, self.AA = name, mode, W, H, AA
+        f, bg = host.SCENES[scene]
+        self.scene = f()
+        self.bg = bg.copy()
+        self.n = len(self.scene.shapes)
+        self.n_spheres = sum(1 for s in self.scene.shapes if s.id() == host.SPHERE_ID)
+        self.n_planes = sum(1 for s in self.scene.shapes if s.id() == host.PLANE_ID)
+        self.shapes = host.load_shape_buffer(self.scene)
+        self.cam = host.camera()
+        for k in keys:
+            setattr(self.cam, k, 1)
+        self.cam.light_movement = int(light)
+        self.aspect = aspect
+        self.light = host.DEFAULT_LIGHT_POS.copy()
+        self.frame = 0
+
+    def next(self):
+        host.update_camera(self.cam, 1.0 / 60.0)
+        hz, vt, llc = host.camera_basis(self.cam, self.aspect)
+        rb = None
+        if self.mode in (1, 2):
+            rb = host.fill_rand_buffer(self.AA, self.frame)
+        else:
+            self.light = host.moving_light(self.light, bool(self.cam.light_movement))
+        slot = self.frame % host.NUM_FRAMES
+        u = host.pack_uniforms(slot, self.n, hz, vt, llc, self.cam.location, self.light, self.bg)
+        self.frame += 1
+        return slot, u, rb
+
+
+class ClockSampler:
+    """nvidia-smi SM clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.stop_flag, self.proc = index, [], False, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [t.strip() for t in s.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# the B200 arm
+# ---------------------------------------------------------------------------------------------
+def run_b200(args) -> None:
+    import torch
+    import torch.distributed as dist
+
+    import real_time_ray_tracer_b200 as rtb
+    from real_time_ray_tracer_b200 import _lib as L
+    from real_time_ray_tracer_b200 import api, bands
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    fr = Frames(args.workload)
+    W, H, AA, mode = fr.W, fr.H, fr.AA, fr.mode
+    K, Wm = args.steps, args.warmup
+
+    # row bands; cost-weighted from a 1/8-scale probe frame rendered identically on every rank
+    row_cost = None
+    if world > 1 and not args.even_bands:
+        row_cost = probe_row_cost(rtb, fr, local)
+    plan = bands.plan_bands(H, world, row_cost)
+    y0, rows = plan[rank]
+    rt = rtb.RayTracer(W, H, AA, device=local, band_y0=y0, band_rows=rows, band_index=rank, band_count=world)
+    stream = torch.cuda.current_stream()
+    rt.set_stream(stream.cuda_stream)
+    rt.upload_scene(fr.shapes, fr.n)
+    eng = bands.GpuBandEngine(rt)
+    br = bands.BandedRenderer(eng, W, H, plan, rank, world)
+    full = torch.empty(W * H * 4, dtype=torch.float32, device=f"cuda:{local}") if (world > 1 and rank == 0) else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        slot, u, rb = fr.next()
+        br.render(mode, u, rb)
+        if world > 1:
+            br.gather(slot, full)
+        return slot
+
+    for _ in range(Wm):
+        step()
+    barrier()
+    rt.reset_stats()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    st = rt.stats()
+    keys = list(L.STAT_COUNTERS)
+    cnt = torch.tensor([float(st[k]) for k in keys], dtype=torch.float64, device=f"cuda:{local}")
+    tms = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    tot = {k: float(v) for k, v in zip(keys, cnt.tolist())}
+    ms = float(tms.item())
+    rays = tot["rays_closest"] + tot["rays_shadow"]
+    mrays = rays / (ms * 1e-3) / 1e6
+
+    # ---- dominant kernel alone: per-launch CUDA events on the launching stream -----------------
+    rt.set_timing(True)
+    tr_ms, pp_ms = [], []
+    for _ in range(min(K, 16)):
+        slot, u, rb = fr.next()
+        rt.reset_stats()
+        br.render(mode, u, rb)
+        s1 = rt.stats()
+        tr_ms.append((s1["ms_trace_last"], flops_from_counters(s1, fr.n_spheres, fr.n_planes),
+                      s1["rays_closest"] + s1["rays_shadow"]))
+        if mode == 1:
+            pp_ms.append((s1["ms_post_last"], pp_bytes_from_counters(s1)))
+    rt.set_timing(False)
+    barrier()
+
+    # ---- end to end through the public API with HOST buffers -----------------------------------
+    e2e = None
+    if args.e2e:
+        e2e = run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, min(K, 32), barrier)
+
+    if rank == 0:
+        peak_tf = api.measure_fp32_peak(local)
+        t_ms = float(np.mean([t for t, _, _ in tr_ms]))
+        fl = float(np.mean([f for _, f, _ in tr_ms]))
+        kr = float(np.mean([r for _, _, r in tr_ms]))
+        ach = fl / (t_ms * 1e-3) / 1e12
+        roof = {"bound": "fp32", "kernel": {1: "rt_ao_trace_kernel", 2: "rt_ao_trace_kernel", 3: "rt_phong_kernel",
+                                             4: "rt_hybrid_kernel"}[mode],
+                "achieved": round(ach, 4), "peak": round(peak_tf, 3), "unit": "TFLOP/s",
+                "frac": round(ach / peak_tf, 5), "traffic": None,
+                "peak_source": "FFMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)",
+                "kernel_ms": round(t_ms, 5), "kernel_mrays_per_s": round(kr / (t_ms * 1e-3) / 1e6, 1),
+                "flops_per_launch": fl, "per_rank_band": world > 1}
+        out = {
+            "metric": f"Mrays/s, lighting mode {mode}, {W}x{H}", "value": round(mrays, 2), "unit": "Mrays/s",
+            "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": round(ms / K, 5),
+            "frames_per_s": round(K / (ms * 1e-3), 2),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "impl": "b200",
+            "config": {"workload": args.workload, "mode": mode, "width": W, "height": H, "aa": AA,
+                       "recursion_depth": host.RECURSION_DEPTH, "ring_frames": host.NUM_FRAMES,
+                       "parallelism": f"row-bands x{world}", "bands": plan,
+                       "l2": "no input reuse: ~1.4 KB of kernel parameters in, each frame writes a different "
+                             "ring slot (8 x %.0f MB > 126 MB L2)" % (W * H * 44 / 1e6)},
+            "rays_per_frame": rays / K,
+            "roofline": roof, "clocks": clocks,
+            "gpu_launches": K * (1 if mode != 1 else 3) * world,
+        }
+        if mode == 1 and pp_ms:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+                os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+            hbm = peaks.get("hbm_gbs", 6650.0)
+            p_ms = float(np.mean([t for t, _ in pp_ms]))
+            p_b = float(np.mean([b for _, b in pp_ms]))
+            out["roofline_postprocess"] = {
+                "bound": "hbm", "kernel": "rt_ao_postprocess_kernel", "achieved": round(p_b / (p_ms * 1e-3) / 1e9, 1),
+                "peak": hbm, "unit": "GB/s", "frac": round(p_b / (p_ms * 1e-3) / 1e9 / hbm, 4), "traffic": None,
+                "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback", "kernel_ms": round(p_ms, 5)}
+        if e2e:
+            out["e2e"] = e2e
+        if args.cpu_baseline and world == 1:
+            out["cpu_baseline"] = cpu_baseline(args.workload)
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def probe_row_cost(rtb, fr: "Frames", device: int):
+    """Per-image-row cost estimate from a 1/8-scale AO frame: 1 + mean bounce count of the row."""
+    s = 8
+    w, h = max(fr.W // s, 16), max(fr.H // s, 16)
+    probe = Frames(fr.name)
+    with rtb.RayTracer(w, h, min(fr.AA, 4), device=device) as rt:
+        rt.upload_scene(probe.shapes, probe.n)
+        slot, u, rb = probe.next()
+        if rb is None or rb.shape[0] != 2 * min(fr.AA, 4):
+            rb = host.fill_rand_buffer(min(fr.AA, 4), 0)
+        rt.render_frame(2, u, rb)
+        d = rt.download(rtb.BUF_DEPTH, slot)
+    cost_small = 1.0 + d[..., 1].mean(axis=1) * min(fr.AA, 4) * 4.0
+    return np.interp(np.arange(fr.H) * (h / fr.H), np.arange(h), cost_small)
+
+
+def run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, steps, barrier):
+    """Same metric through the public API with HOST buffers: every step re-packs and uploads the scene
+    table, passes uniforms + rand_buffer from host memory, renders, gathers the bands and reads the frame's
+    colour image back into pinned host memory; the step ends when the image is on the host."""
+    W, H = fr.W, fr.H
+    pinned = torch.empty(W * H * 4, dtype=torch.float32, pin_memory=True) if rank == 0 else None
+    rt.reset_stats()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        shapes = host.load_shape_buffer(fr.scene)           # loadShapeBuffer() every frame (main.cpp:768)
+        rt.upload_scene(shapes, fr.n)
+        slot, u, rb = fr.next()
+        br.render(fr.mode, u, rb)
+        if world > 1:
+            br.gather(slot, full)
+            if rank == 0:
+                pinned.copy_(full, non_blocking=True)
+        else:
+            rt.download_async(L.BUF_COLOR, slot, pinned.data_ptr(), pinned.numel() * 4)
+        torch.cuda.synchronize()
+    barrier()
+    dt = time.perf_counter() - t0
+    st = rt.stats()
+    cnt = torch.tensor([float(st["rays_closest"] + st["rays_shadow"]), dt], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        c0 = cnt[:1].clone()
+        dist.all_reduce(c0, op=dist.ReduceOp.SUM)
+        t1 = cnt[1:].clone()
+        dist.all_reduce(t1, op=dist.ReduceOp.MAX)
+        rays, dt = float(c0.item()), float(t1.item())
+    else:
+        rays = float(cnt[0].item())
+    return {"value": round(rays / dt / 1e6, 2), "unit": "Mrays/s", "frames_per_s": round(steps / dt, 2),
+            "ms_per_step": round(dt / steps * 1e3, 4), "steps": steps,
+            "h2d_bytes_per_step": int(fr.n * 80 + 112 + (8 * fr.AA * 4 if fr.mode in (1, 2) else 0)),
+            "d2h_bytes_per_step": int(W * H * 16),
+            "what": "upload_scene + uniforms + rand_buffer from host, render (+post-process), gather, "
+                    "float4 colour image read back to pinned host memory, synchronised every frame"}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU legs (the only places bench.py may touch oracle/)
+# ---------------------------------------------------------------------------------------------
+def _band_for_budget(H: int, est_frame_s: float, budget_s: float):
+    """rows of a centred band so that one step costs about budget_s"""
+    frac = min(1.0, budget_s / max(est_frame_s, 1e-9))
+    rows = max(8, int(H * frac))
+    y0 = max(0, (H - rows) // 2)
+    return y0, min(H, y0 + rows)
+
+
+def cpu_baseline(workload: str, budget_s: float = 12.0) -> dict:
+    """The oracle port (oracle/rt_oracle.c, OpenMP over rows, all host cores) on a bounded sample of the
+    same workload: whole frames while they fit the budget, else a centred row band of each frame."""
+    from oracle import oracle as orc
+
+    fr = Frames(workload)
+    o = orc.Oracle(fr.W, fr.H, fr.AA)
+    o.set_scene(fr.shapes, fr.n)
+    cores = o.threads()
+    # calibrate on a thin band
+    slot, u, rb = fr.next()
+    y0, y1 = _band_for_budget(fr.H, 1.0, 0.03)
+    t = time.perf_counter()
+    o.render(fr.mode, u, rb, rows=(y0, y1))
+    est = (time.perf_counter() - t) * fr.H / (y1 - y0)
+    o.reset_stats()
+    if est * 3 <= budget_s:
+        rows, frames = (0, fr.H), max(3, min(32, int(budget_s / est)))
+    else:
+        rows, frames = _band_for_budget(fr.H, est, budget_s / 3), 3
+    t = time.perf_counter()
+    for _ in range(frames):
+        slot, u, rb = fr.next()
+        o.render(fr.mode, u, rb, rows=rows)
+        if fr.mode == 1:
+            o.postprocess(rows=rows)
+    dt = time.perf_counter() - t
+    st = o.stats()
+    rays = st["rays_closest"] + st["rays_shadow"]
+    o.close()
+    px = (rows[1] - rows[0]) * fr.W
+    return {"value": round(rays / dt / 1e6, 3), "unit": "Mrays/s", "cores": cores, "kind": "port",
+            "frames_per_s_equiv": round(frames * px / (fr.W * fr.H) / dt, 4),
+            "sample": f"{frames} frames x rows [{rows[0]},{rows[1]}) of {fr.H} ({workload}), {dt:.1f} s"}
+
+
+def run_reference(args) -> None:
+    """--impl reference: the reference's OWN shader text compiled as C++ (oracle/_ref/, built by
+    oracle/build_ref.py from /root/reference/resources/*.glsl) on all host cores.  Falls back to the oracle
+    port when no prebuilt library matches the workload's size."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle as orc
+
+    fr = Frames(args.workload)
+    K, Wm = args.steps, args.warmup
+    prog = {1: "aop_compute", 2: "ao_compute", 3: "p_compute", 4: "h_compute"}[fr.mode]
+    have = os.path.exists(orc.glsl_ref_lib_path(fr.W, fr.H, fr.AA)) or os.path.isdir("/root/reference/resources")
+    counter = orc.Oracle(fr.W, fr.H, fr.AA)     # ray counts only (deterministic, not timed)
+    counter.set_scene(fr.shapes, fr.n)
+    if have:
+        g = orc.GlslRef(fr.W, fr.H, fr.AA)
+        g.set_scene(fr.shapes, fr.n)
+        cores, kind = g.nthreads, "reference"
+
+        def run(u, rb, rows):
+            g.set_uniforms(u, rb)
+            g.dispatch(prog, rows=rows)
+            if fr.mode == 1:
+                g.dispatch("aop_postprocessing", rows=rows)
+    else:
+        o = orc.Oracle(fr.W, fr.H, fr.AA)
+        o.set_scene(fr.shapes, fr.n)
+        cores, kind = o.threads(), "port"
+
+        def run(u, rb, rows):
+            o.render(fr.mode, u, rb, rows=rows)
+            if fr.mode == 1:
+                o.postprocess(rows=rows)
+    # size each step to ~budget/(K+W) seconds
+    slot, u, rb = fr.next()
+    y0, y1 = _band_for_budget(fr.H, 1.0, 0.03)
+    t = time.perf_counter()
+    run(u, rb, (y0, y1))
+    est = (time.perf_counter() - t) * fr.H / (y1 - y0)
+    rows = _band_for_budget(fr.H, est, max(0.25, args.ref_budget / max(1, K + Wm)))
+    for _ in range(Wm):
+        slot, u, rb = fr.next()
+        run(u, rb, rows)
+    counter.reset_stats()
+    dt = 0.0
+    for _ in range(K):
+        slot, u, rb = fr.next()
+        t = time.perf_counter()
+        run(u, rb, rows)
+        dt += time.perf_counter() - t
+        counter.render(fr.mode, u, rb, rows=rows)
+    st = counter.stats()
+    rays = st["rays_closest"] + st["rays_shadow"]
+    v = round(rays / dt / 1e6, 3)
+    sample = f"{K} steps x rows [{rows[0]},{rows[1]}) of {fr.H} ({args.workload}), {dt:.1f} s"
+    out = {"metric": f"Mrays/s, lighting mode {fr.mode}, {fr.W}x{fr.H}", "value": v, "unit": "Mrays/s",
+           "n_gpus": args.gpus, "steps": K, "warmup": Wm, "ms_per_step": round(dt / K * 1e3, 3),
+           "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "impl": "reference",
+           "config": {"workload": args.workload, "mode": fr.mode, "width": fr.W, "height": fr.H, "aa": fr.AA},
+           "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+           "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-e2e", dest="e2e", action="store_false")
+    ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    ap.add_argument("--even-bands", action="store_true", help="equal-height bands instead of cost-weighted")
+    ap.add_argument("--ref-budget", type=float, default=60.0, help="seconds of CPU work for --impl reference")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

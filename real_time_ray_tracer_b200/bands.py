@@ -1,0 +1,147 @@
+"""Row-band sharding of a frame across the GPUs of one box (one process per GPU).
+
+The trace kernels need no exchange (pixels are independent).  The post-processing pass of mode 1 reads
+the four neighbours of the CURRENT frame (aop_postprocessing.glsl:81-171), so each band needs one record
+row from the band below and one from the band above; under the literal FLAT32 border semantics image row
+0 additionally reads image row H-1 (``[f][x][y-1]`` with y = 0 wraps), which turns the exchange into a
+ring.  Temporal history stays rank-local.  Bands are finally gathered on rank 0.
+
+The exchange is written against ``torch.distributed`` point-to-point ops, so it runs over NCCL/NVLink on
+the GPU box and over gloo in the CPU tests; the per-band engine is duck-typed (``GpuBandEngine`` here, a
+CPU oracle adapter in tests/).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+
+def plan_bands(height: int, n: int, row_cost: Optional[Sequence[float]] = None) -> List[Tuple[int, int]]:
+    """Split rows [0, height) into n contiguous bands [(y0, rows)].  With ``row_cost`` (one number per
+    image row, e.g. rays traced per row in an earlier frame) the cut points equalise cumulative cost --
+    sky rows end after one segment while sphere rows bounce up to 20 times -- otherwise rows are split
+    evenly.  Every band gets at least one row."""
+    if n < 1 or height < n:
+        raise ValueError("need 1 <= n <= height")
+    if row_cost is None:
+        cuts = [round(i * height / n) for i in range(n + 1)]
+    else:
+        c = np.asarray(row_cost, dtype=np.float64)
+        if c.shape != (height,):
+            raise ValueError("row_cost must have one entry per image row")
+        cum = np.concatenate([[0.0], np.cumsum(np.maximum(c, 1e-9))])
+        cuts = [0]
+        for i in range(1, n):
+            y = int(np.searchsorted(cum, cum[-1] * i / n))
+            y = max(cuts[-1] + 1, min(y, height - (n - i)))
+            cuts.append(y)
+        cuts.append(height)
+    return [(cuts[i], cuts[i + 1] - cuts[i]) for i in range(n)]
+
+
+class _DevBuf:
+    """a raw device pointer as a __cuda_array_interface__ object (for torch.as_tensor)"""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<f4", "data": (ptr, False),
+                                         "version": 3}
+
+
+def device_tensor(ptr: int, nbytes: int, device: int):
+    import torch
+
+    return torch.as_tensor(_DevBuf(ptr, nbytes), device=f"cuda:{device}")
+
+
+class GpuBandEngine:
+    """One band on one GPU: a RayTracer context whose halo rows and colour planes are exposed as torch
+    tensors aliasing the library's device memory (no copies)."""
+
+    def __init__(self, tracer):
+        from . import _lib as L
+
+        self.rt = tracer
+        info = tracer.halo_info()
+        d = tracer.device
+        self.send_lo = device_tensor(info.send_lo, info.row_bytes, d)
+        self.send_hi = device_tensor(info.send_hi, info.row_bytes, d)
+        self.recv_lo = device_tensor(info.recv_lo, info.row_bytes, d)
+        self.recv_hi = device_tensor(info.recv_hi, info.row_bytes, d)
+        self._color = []
+        for s in range(tracer.NF):
+            p, n = tracer.device_ptr(L.BUF_COLOR, s)
+            self._color.append(device_tensor(p, n, d))
+
+    def render_frame(self, mode, uniforms, rand_buffer):
+        self.rt.render_frame(mode, uniforms, rand_buffer)
+
+    def halo_pack(self):
+        self.rt.halo_pack()
+
+    def postprocess(self):
+        self.rt.postprocess()
+
+    def band_color(self, slot: int):
+        """float32 tensor [rows*W*4] of pixels[slot] for this band (row-major)"""
+        return self._color[slot]
+
+
+class BandedRenderer:
+    """Drives one band per rank: trace -> (mode 1: pack, ring halo exchange, post-process) -> gather."""
+
+    def __init__(self, engine, width: int, height: int, bands: List[Tuple[int, int]], rank: int, world: int,
+                 group=None):
+        self.e, self.W, self.H = engine, width, height
+        self.bands, self.rank, self.world, self.group = bands, rank, world, group
+
+    def exchange_halo(self):
+        """send_hi -> recv_lo of band (r+1) % n (the last band's send_hi is the wrapped row image row 0
+        reads under FLAT32); send_lo -> recv_hi of band r-1."""
+        import torch.distributed as dist
+
+        if self.world == 1:
+            self.e.recv_lo.copy_(self.e.send_hi)
+            return
+        r, n = self.rank, self.world
+        ops = [dist.P2POp(dist.isend, self.e.send_hi, (r + 1) % n, self.group),
+               dist.P2POp(dist.irecv, self.e.recv_lo, (r - 1) % n, self.group)]
+        if r > 0:
+            ops.append(dist.P2POp(dist.isend, self.e.send_lo, r - 1, self.group))
+        if r < n - 1:
+            ops.append(dist.P2POp(dist.irecv, self.e.recv_hi, r + 1, self.group))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+    def render(self, mode: int, uniforms, rand_buffer):
+        self.e.render_frame(mode, uniforms, rand_buffer)
+        if mode == 1:
+            self.e.halo_pack()
+            self.exchange_halo()
+            self.e.postprocess()
+
+    def gather(self, slot: int, out=None):
+        """Assemble pixels[slot] of all bands on rank 0 into ``out`` (float32 [H*W*4], row-major).
+        Bands are contiguous row ranges, so every band lands in place with no re-packing."""
+        import torch.distributed as dist
+
+        mine = self.e.band_color(slot)
+        if self.world == 1:
+            if out is not None:
+                out.copy_(mine)
+                return out
+            return mine
+        if self.rank == 0:
+            ops = []
+            for r, (y0, rows) in enumerate(self.bands):
+                dst = out[y0 * self.W * 4:(y0 + rows) * self.W * 4]
+                if r == 0:
+                    dst.copy_(mine)
+                else:
+                    ops.append(dist.P2POp(dist.irecv, dst, r, self.group))
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            return out
+        for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, mine, 0, self.group)]):
+            w.wait()
+        return None
