@@ -166,7 +166,10 @@ def run_b200(args) -> None:
     plan = bands.plan_bands(H, world, row_cost)
     y0, rows = plan[rank]
     rt = rtb.RayTracer(W, H, AA, device=local, band_y0=y0, band_rows=rows, band_index=rank, band_count=world)
-    stream = torch.cuda.current_stream()
+    # a non-default stream made current: the kernels, the NCCL ops and the timing events all live on it
+    # (torch.cuda.Event only sees torch's current stream; handle 0 would mean "the context's own stream")
+    stream = torch.cuda.Stream(device=local)
+    torch.cuda.set_stream(stream)
     rt.set_stream(stream.cuda_stream)
     rt.upload_scene(fr.shapes, fr.n)
     eng = bands.GpuBandEngine(rt)

@@ -43,56 +43,41 @@ RTR_INLINE uint64_t rtr_d2u(double d) { uint64_t u; memcpy(&u, &d, 8); return u;
 RTR_INLINE double rtr_u2d(uint64_t u) { double d; memcpy(&d, &u, 8); return d; }
 
 /* ---- sin(float) ----------------------------------------------------------
- * binary64 evaluation, Cody-Waite reduction by pi/2 with the three-part
- * constant of fdlibm's e_rem_pio2.c (33+33+53 bits), quadrant from k&3,
- * one Horner polynomial of degree 6 in z=r*r whose coefficients are the
- * fdlibm k_sin.c set (even quadrant, leading coefficient 0) or the k_cos.c set
- * (odd quadrant).  Accurate to < 1 binary32 ulp for |x| < 2^20*pi/2, which
- * covers every argument the shaders produce up to 7680x4320
- * (|dot(st,(12.9898,78.233))| < 4.5e5).  Deterministic for any input; |x| >= 2^50 gives x - x.
+ * binary32 throughout: k = round(x * 2/pi) by the add-magic trick, Cody-Waite reduction
+ * r = x - k*pi/2 as three fused multiply-adds with pi/2 split into three binary32 parts,
+ * quadrant from k&3, then ONE degree-3 Horner polynomial in z = r*r whose coefficients are
+ * the Cephes sinf set (even quadrant) or the Cephes cosf set (odd quadrant).
+ * Absolute error ~1.5e-7 for |x| < 5e5, which covers every argument the shaders produce
+ * up to 7680x4320 (|dot(st,(12.9898,78.233))| < 4.5e5).  Defined for any input:
+ * |x| >= 2^22 (where the rounding trick ends), inf and NaN give x - x.
+ * ~22 FP32 instructions on the GPU; the shaders call it five times per AO sample.
  */
-#define RTR_TWO_OVER_PI 6.36619772367581382433e-01 /* 0x3FE45F306DC9C883 */
-#define RTR_PIO2_1 1.57079632673412561417e+00      /* 0x3FF921FB54400000 */
-#define RTR_PIO2_2 6.07710050630396597660e-11      /* 0x3DD0B4611A600000 */
-#define RTR_PIO2_3 2.02226624879595063154e-21      /* 0x3BA3198A2E037073 */
-#define RTR_RND_MAGIC 6755399441055744.0           /* 1.5 * 2^52 */
+#define RTR_SIN_2_OVER_PI 0x1.45f306p-1f   /* RN32(2/pi)            0x3F22F983 */
+#define RTR_SIN_P1 0x1.921fb6p+0f          /* RN32(pi/2)            0x3FC90FDB */
+#define RTR_SIN_P2 -0x1.777a5cp-25f        /* RN32(pi/2 - P1)       0xB33BBD2E */
+#define RTR_SIN_P3 -0x1.ee59dap-50f        /* RN32(pi/2 - P1 - P2)  0xA6F72CED */
+#define RTR_SIN_MAGIC 12582912.0f          /* 1.5 * 2^23 */
 
 RTR_INLINE float rtr_sin(float x)
 {
-    static const double S[7] = { /* even quadrant: sin(r) = r + (r*z)*P(z) */
-        0.0,
-        1.58969099521155010221e-10, -2.50507602534068634195e-08,
-        2.75573137070700676789e-06, -1.98412698298579493134e-04,
-        8.33333333332248946124e-03, -1.66666666666666324348e-01 };
-    static const double C[7] = { /* odd quadrant: cos(r) = 1 + z*P(z) */
-        -1.13596475577881948265e-11, 2.08757232129817482790e-09,
-        -2.75573143513906633035e-07, 2.48015872894767294178e-05,
-        -1.38888888888741095749e-03, 4.16666666666666019037e-02,
-        -0.5 };
-    double xd = (double)x;
-    /* outside the rounding trick's range (|x| >= 2^50, inf, NaN): 0 for finite x, NaN otherwise */
-    if (!(fabs(xd) < 1125899906842624.0)) return x - x;
-    double kd = (xd * RTR_TWO_OVER_PI + RTR_RND_MAGIC) - RTR_RND_MAGIC;
-    double r = fma(-kd, RTR_PIO2_1, xd);
-    r = fma(-kd, RTR_PIO2_2, r);
-    r = fma(-kd, RTR_PIO2_3, r);
-    /* quadrant: kd is integral and |kd| < 2^51 for every finite binary32 x */
-    int64_t k = (int64_t)kd;
-    int odd = (int)(k & 1);
-    const double *c = odd ? C : S;
-    double z = r * r;
-    double p = c[0];
-    p = fma(p, z, c[1]);
-    p = fma(p, z, c[2]);
-    p = fma(p, z, c[3]);
-    p = fma(p, z, c[4]);
-    p = fma(p, z, c[5]);
-    p = fma(p, z, c[6]);
-    double a = odd ? 1.0 : r;
-    double b = odd ? z : r * z;
-    double res = fma(b, p, a);
+    if (!(fabsf(x) < 4194304.0f)) return x - x;
+    float t = x * RTR_SIN_2_OVER_PI;
+    float kf = (t + RTR_SIN_MAGIC) - RTR_SIN_MAGIC;
+    float nk = -kf;
+    float r = fmaf(nk, RTR_SIN_P1, x);
+    r = fmaf(nk, RTR_SIN_P2, r);
+    r = fmaf(nk, RTR_SIN_P3, r);
+    int k = (int)kf;
+    int odd = k & 1;
+    float z = r * r;
+    float p = odd ? 2.443315711809948e-5f : -1.9515295891e-4f;
+    p = fmaf(p, z, odd ? -1.388731625493765e-3f : 8.3321608736e-3f);
+    p = fmaf(p, z, odd ? 4.166664568298827e-2f : -1.6666654611e-1f);
+    float a = odd ? fmaf(-0.5f, z, 1.0f) : r;
+    float b = odd ? z * z : r * z;
+    float res = fmaf(b, p, a);
     if (k & 2) res = -res;
-    return (float)res;
+    return res;
 }
 
 /* ---- pow(float x, float y) for x >= 0 ------------------------------------
@@ -101,6 +86,7 @@ RTR_INLINE float rtr_sin(float x)
  * sites have y > 0), x < 0 or NaN -> NaN.  Relative error ~1e-15 before the
  * final rounding to binary32.
  */
+#define RTR_RND_MAGIC 6755399441055744.0 /* 1.5 * 2^52 */
 #define RTR_LN2_HI 6.93147180369123816490e-01 /* 0x3FE62E42FEE00000 */
 #define RTR_LN2_LO 1.90821492927058770002e-10 /* 0x3DEA39EF35793C76 */
 #define RTR_LOG2E 1.44269504088896338700e+00  /* 0x3FF71547652B82FE */
