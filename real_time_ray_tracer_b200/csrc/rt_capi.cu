@@ -7,6 +7,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -30,6 +31,8 @@ struct rt_ctx {
     void *halo[4] = { nullptr, nullptr, nullptr, nullptr }; // send_lo, send_hi, recv_lo, recv_hi
     void *staging = nullptr; // npix * 16 bytes, layout conversions
     unsigned long long *stats = nullptr;
+    unsigned *work = nullptr; // streaming AO kernel's unit counters
+    bool tile_kernel = false; // RT_AO_KERNEL=tile selects the first-generation kernel (profiling A/B)
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
     int nshapes = 0;
@@ -81,7 +84,7 @@ static void free_all(rt_ctx *c)
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
-    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats);
+    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->work);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
@@ -135,6 +138,8 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0((void **)&c->hit, c->npix * sizeof(int));
     alloc0(&c->staging, c->npix * sizeof(float4));
     alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
+    alloc0((void **)&c->work, 2 * sizeof(unsigned));
+    { const char *k = getenv("RT_AO_KERNEL"); c->tile_kernel = (k && strcmp(k, "tile") == 0); }
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width));
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
@@ -235,6 +240,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     o.depth_w = c->ring_depth_w + off;
     o.hit = c->hit;
     o.stats = c->stats;
+    o.work = c->tile_kernel ? nullptr : c->work;
     if (c->timing) CU(c, cudaEventRecord(c->ev[0], c->stream));
     CU(c, launch_trace(p, o, c->stream));
     if (c->timing) { CU(c, cudaEventRecord(c->ev[1], c->stream)); c->ev_trace_valid = true; }

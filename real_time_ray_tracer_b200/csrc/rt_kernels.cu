@@ -13,88 +13,9 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -prec-div=true -prec-sqrt=true
 #include "rt_kernels.cuh"
 #include "rt_math.cuh"
+#include "rt_trace_common.cuh"
 
 namespace rt {
-
-// ---------------------------------------------------------------------------------------------
-// intersection (ao_compute.glsl:75-136)
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float sphere_eval_ray(float3 pos, float3 dir, float4 s0, float r2)
-{
-    float3 pmc = sub3(pos, xyz(s0));
-    float b = dot3(dir, pmc);
-    float del = b * b - dot3(pmc, pmc) + r2;
-    float res = -1.0f;
-    if (del == 0.0f) {
-        res = -b;
-    } else if (del > 0.0f) {
-        float im = __fsqrt_rn(del);
-        float t1 = -b + im;
-        float t2 = -b - im;
-        res = (t2 < 0.0f) ? ((t1 < 0.0f) ? -1.0f : t1) : t2;
-    }
-    return res;
-}
-
-__device__ __forceinline__ float plane_eval_ray(float3 pos, float3 dir, float4 s0, float4 s3)
-{
-    float3 n = xyz(s0);
-    float denom = dot3(n, dir);
-    if (denom < 0.001f && denom > -0.001f) return -1.0f;
-    return __fdiv_rn(dot3(n, sub3(xyz(s3), pos)), denom);
-}
-
-__device__ __forceinline__ float eval_ray(const DevShape &s, float3 pos, float3 dir)
-{
-    if (s.id == SPHERE_ID) return sphere_eval_ray(pos, dir, s.s0, s.r2);
-    if (s.id == PLANE_ID) return plane_eval_ray(pos, dir, s.s0, s.s3);
-    return -1.0f;
-}
-
-// closest hit over the object table, read from the constant bank with warp-uniform indices
-// (ao_compute.glsl:183-194 / p_compute.glsl:177-188 / h_compute.glsl:199-210)
-__device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, float3 dir, float tmin, float &t_out)
-{
-    float t = -1.0f;
-    int ind = -1;
-#pragma unroll
-    for (int i = 0; i < RT_MAX_SHAPES; i++) {
-        if (i >= p.nshapes) break;
-        float res_t = eval_ray(p.shapes[i], pos, dir);
-        if (res_t > tmin && (res_t < t || t < 0.0f)) {
-            t = res_t;
-            ind = i;
-        }
-    }
-    t_out = t;
-    return ind;
-}
-
-__device__ __forceinline__ float3 shape_normal(const DevShape &s, float3 pt)
-{
-    if (s.id == SPHERE_ID) return normalize3(sub3(pt, xyz(s.s0)));
-    return xyz(s.s0);
-}
-
-__device__ __forceinline__ float3 primary_dir(const FrameParams &p, float hp, float vp)
-{
-    return normalize3(add3(add3(p.llc, scale3(hp, p.horiz)), scale3(vp, p.vert)));
-}
-
-// ao_compute.glsl:143-158
-__device__ __forceinline__ float3 get_pt_within_unit_sphere(float4 r0, float4 r1, float fx, float fy)
-{
-    float a = random2(r0.x + fx * r1.z, r0.y + fy * r1.w) * 2.0f - 1.0f;
-    float b = random2(r0.z - fx * r1.z, r0.w - fy * r1.w) * 2.0f - 1.0f;
-    float c = random2(r1.x * fx + r1.z, r1.y * fy + r1.w) * 2.0f - 1.0f;
-    return normalize3(mk3(a, b, c));
-}
-
-__device__ __forceinline__ float4 gamma_correct(float r, float g, float b)
-{
-    const float gm = __fdiv_rn(1.0f, 2.2f);
-    return make_float4(pow_f32(r, gm), pow_f32(g, gm), pow_f32(b, gm), 0.0f);
-}
 
 // pixel owned by this thread: a block is a 16x8 pixel tile, each warp an 8x4 sub-tile
 constexpr int TILE_W = 16, TILE_H = 8, TRACE_THREADS = 128;
@@ -402,8 +323,10 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
 {
     dim3 grid((p.W + TILE_W - 1) / TILE_W, (p.rows + TILE_H - 1) / TILE_H);
     dim3 block(TRACE_THREADS);
-    if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO)
-        rt_ao_trace_kernel<<<grid, block, 0, s>>>(p, o);
+    if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO) {
+        if (o.work) return launch_ao_stream(p, o, s); // persistent streaming kernel (rt_ao_stream.cu)
+        rt_ao_trace_kernel<<<grid, block, 0, s>>>(p, o); // first-generation tile kernel, kept for A/B profiling
+    }
     else if (p.mode == RT_MODE_PHONG)
         rt_phong_kernel<<<grid, block, 0, s>>>(p, o);
     else

@@ -65,6 +65,7 @@ struct TraceOut {
     float *depth_w;   // ring depth.w plane of the slot
     int *hit;         // hit-index plane
     unsigned long long *stats; // [STAT_STRIPES][ST_COUNT]
+    unsigned *work;   // [2] unit counter + finished-warp counter of the streaming AO kernel (self re-arming)
 };
 
 // a halo record row: three consecutive arrays of W elements
@@ -101,6 +102,7 @@ struct PostParams {
 
 // launchers (rt_kernels.cu)
 cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s);
+cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s);
 cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s);
 cudaError_t launch_transpose(const void *src, void *dst, int W, int rows, int elem_bytes, bool to_reference, cudaStream_t s);
