@@ -675,3 +675,25 @@ void rto_eval_math(int kind, const float *a, const float *b, float *out, long lo
         }
     }
 }
+
+/* Test helper: the kernels divide by the frame constants 6, WIDTH and HEIGHT with
+ *   q = a * y;  r = fma(-q, b, a);  q' = fma(r, y, q)      (y = RN(1/b))
+ * instead of an IEEE divide.  Returns how many binary32 numerators with bit patterns in
+ * [lo_bits, hi_bits] give q' != a / b (expected: 0).  tests/test_oracle_math.py sweeps it. */
+long long rto_check_div_by_const(float b, unsigned lo_bits, unsigned hi_bits)
+{
+    const float y = 1.0f / b;
+    long long bad = 0;
+#pragma omp parallel for reduction(+ : bad) schedule(static)
+    for (long long u = (long long)lo_bits; u <= (long long)hi_bits; u++) {
+        unsigned ub = (unsigned)u;
+        float a;
+        memcpy(&a, &ub, 4);
+        float q = a * y;
+        float r = fmaf(-q, b, a);
+        float q2 = fmaf(r, y, q);
+        float ref = a / b;
+        if (memcmp(&q2, &ref, 4) != 0 && !(q2 != q2 && ref != ref)) bad++;
+    }
+    return bad;
+}

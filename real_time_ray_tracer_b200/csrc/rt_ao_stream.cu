@@ -7,7 +7,7 @@
 // Here
 //   * every warp is independent (no block barrier after the table staging);
 //   * lanes PULL pixels: when a lane's pixel is done it takes the next pixel of the warp's current
-//     8x16-pixel unit, and the warp takes the next unit from a global counter when the unit is used
+//     8x4-pixel unit, and the warp takes the next unit from a global counter when the unit is used
 //     up, so no lane waits for another lane's path and the only tail is the last path of the frame;
 //   * one loop iteration = GENERATE (new-sample setup and bounce direction merged into ONE instruction
 //     stream: both need up to three random() and a chain of normalize) then TRACE (closest hit + classify)
@@ -20,7 +20,7 @@
 
 namespace rt {
 
-constexpr int UNIT_W = 8, UNIT_H = 16, UNIT_PIX = UNIT_W * UNIT_H;
+constexpr int UNIT_W = 8, UNIT_H = 4, UNIT_PIX = UNIT_W * UNIT_H;
 constexpr int STREAM_THREADS = 128;
 
 __global__ void __launch_bounds__(STREAM_THREADS) rt_ao_stream_kernel(const __grid_constant__ FrameParams p, TraceOut o)
@@ -37,7 +37,6 @@ __global__ void __launch_bounds__(STREAM_THREADS) rt_ao_stream_kernel(const __gr
     const int units_x = (p.W + UNIT_W - 1) / UNIT_W;
     const int units_y = (p.rows + UNIT_H - 1) / UNIT_H;
     const int n_units = units_x * units_y;
-    const float fW = (float)p.W, fH = (float)p.H;
 
     // warp-uniform work cursor
     int unit_x0 = 0, unit_y0 = 0, next_j = UNIT_PIX;
@@ -137,8 +136,8 @@ __global__ void __launch_bounds__(STREAM_THREADS) rt_ao_stream_kernel(const __gr
                 else v = mk3(q1 * 2.0f - 1.0f, q2 * 2.0f - 1.0f, q3 * 2.0f - 1.0f);
                 const float3 n1 = normalize3(v);
                 if (S_jit) {
-                    jx = __fdiv_rn(n1.x, 6.0f) - 0.08333f;
-                    jy = __fdiv_rn(n1.y, 6.0f) - 0.08333f;
+                    jx = div_const(n1.x, 6.0f, RT_INV6) - 0.08333f;
+                    jy = div_const(n1.y, 6.0f, RT_INV6) - 0.08333f;
                 } else {
                     ru = n1;
                     have_ru = true;
@@ -147,8 +146,8 @@ __global__ void __launch_bounds__(STREAM_THREADS) rt_ao_stream_kernel(const __gr
             float3 v2, cpos = p.cam;
             if (S) {
                 // sample 0 is un-jittered: fx + 0.0f == fx exactly
-                const float hp = __fdiv_rn(fx + jx, fW);
-                const float vp = __fdiv_rn(fy + jy, fH);
+                const float hp = div_const(fx + jx, p.fW, p.invW);
+                const float vp = div_const(fy + jy, p.fH, p.invH);
                 v2 = add3(add3(p.llc, scale3(hp, p.horiz)), scale3(vp, p.vert));
             } else {
                 cpos = add3(p.cam, scale3(t_hit, dir)); // camera origin even on bounces (:210)

@@ -32,7 +32,7 @@ struct rt_ctx {
     void *staging = nullptr; // npix * 16 bytes, layout conversions
     unsigned long long *stats = nullptr;
     unsigned *work = nullptr; // streaming AO kernel's unit counters
-    bool tile_kernel = false; // RT_AO_KERNEL=tile selects the first-generation kernel (profiling A/B)
+    bool tile_kernel = true; // RT_AO_KERNEL=stream selects the persistent streaming kernel, =tile the tile kernel
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
     int nshapes = 0;
@@ -139,7 +139,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0(&c->staging, c->npix * sizeof(float4));
     alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     alloc0((void **)&c->work, 2 * sizeof(unsigned));
-    { const char *k = getenv("RT_AO_KERNEL"); c->tile_kernel = (k && strcmp(k, "tile") == 0); }
+    { const char *k = getenv("RT_AO_KERNEL"); if (k) c->tile_kernel = (strcmp(k, "stream") != 0); }
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width));
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
@@ -221,6 +221,11 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     FrameParams &p = c->fp;
     p.W = c->cfg.width; p.H = c->cfg.height; p.AA = c->cfg.aa; p.RD = c->cfg.recursion_depth; p.NF = c->cfg.num_frames;
     p.y0 = c->cfg.band_y0; p.rows = c->rows;
+    {
+        volatile float fw = (float)p.W, fh = (float)p.H; // binary32 reciprocals, correctly rounded
+        volatile float iw = 1.0f / fw, ih = 1.0f / fh;
+        p.fW = fw; p.fH = fh; p.invW = iw; p.invH = ih;
+    }
     p.slot = slot; p.nshapes = nobj; p.edge_mode = c->cfg.edge_mode; p.mode = mode;
     p.band_index = c->cfg.band_index; p.band_count = c->cfg.band_count;
     p.llc = f3(u->llc_minus_campos); p.horiz = f3(u->horizontal); p.vert = f3(u->vertical);

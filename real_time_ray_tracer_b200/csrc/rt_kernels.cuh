@@ -33,6 +33,7 @@ struct FrameParams {
     int slot, nshapes, edge_mode, mode;
     int band_index, band_count;
     int pad0;
+    float fW, fH, invW, invH; // (float)W, (float)H and their correctly rounded reciprocals (host-computed)
     float3 llc, horiz, vert, cam, light;
     float4 bg;
     DevShape shapes[RT_MAX_SHAPES];

@@ -1,0 +1,103 @@
+"""The oracle's built-in definitions (oracle/rt_ref_math.h): accuracy against libm, determinism
+properties, and the known-answer intersections of SURVEY.md 8(c)."""
+import ctypes as C
+import math
+import struct
+
+import numpy as np
+
+from oracle import oracle as orc
+from real_time_ray_tracer_b200 import host
+from tests.util import Scenario
+
+
+def test_sin_accuracy_and_edges():
+    rng = np.random.default_rng(0)
+    for lo, hi, tol in [(-8, 8, 1.2e-7), (-1e3, 1e3, 1.2e-7), (-5e5, 5e5, 1.5e-7)]:
+        x = rng.uniform(lo, hi, 300000).astype(np.float32)
+        err = np.abs(orc.eval_math("sin", x) - np.sin(x.astype(np.float64))).max()
+        assert err < tol, (lo, hi, err)
+    e = orc.eval_math("sin", np.array([0.0, np.inf, -np.inf, np.nan, 1e30, 4194304.0], np.float32))
+    assert e[0] == 0.0 and np.isnan(e[1]) and np.isnan(e[2]) and np.isnan(e[3]) and e[4] == 0.0 and e[5] == 0.0
+
+
+def test_pow_accuracy_and_edges():
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.uniform(0, 1, 200000), rng.uniform(0, 20, 100000)]).astype(np.float32)
+    for y in (np.float32(1.0) / np.float32(2.2), np.float32(500.0), np.float32(2.0)):
+        got = orc.eval_math("pow", x, np.full_like(x, y)).astype(np.float64)
+        with np.errstate(over="ignore"):
+            ref = np.power(x.astype(np.float64), float(y))
+        big = ref > 3.0e38                      # rounds to +inf in binary32
+        assert np.isinf(got[ref > 3.5e38]).all()
+        ok = (ref > 1e-37) & ~big               # below that binary32 is subnormal: absolute comparison
+        rel = np.abs(got[ok] - ref[ok]) / ref[ok]
+        assert rel.max() < 1.0e-7, (y, rel.max())
+        tiny = ref <= 1e-37
+        if tiny.any():
+            assert np.abs(got[tiny] - ref[tiny]).max() < 1e-37
+    e = orc.eval_math("pow", np.array([0.0, 1.0, -1.0, np.inf], np.float32), np.full(4, 0.4545, np.float32))
+    assert e[0] == 0.0 and e[1] == 1.0 and np.isnan(e[2]) and np.isinf(e[3])
+
+
+def test_random_is_in_unit_interval_and_uniform():
+    rng = np.random.default_rng(2)
+    sx = rng.uniform(0, 8000, 500000).astype(np.float32)
+    sy = rng.uniform(0, 4400, 500000).astype(np.float32)
+    r = orc.eval_math("random", sx, sy)
+    assert r.min() >= 0.0 and r.max() <= 1.0
+    h = np.histogram(r, 10, (0, 1))[0] / r.size
+    assert np.abs(h - 0.1).max() < 0.01
+
+
+def test_division_by_frame_constants_is_ieee():
+    """the kernels' reciprocal + FMA division equals a / b for every binary32 numerator that can occur"""
+    L = orc.lib()
+    L.rto_check_div_by_const.restype = C.c_longlong
+    L.rto_check_div_by_const.argtypes = [C.c_float, C.c_uint, C.c_uint]
+
+    def bits(f):
+        return struct.unpack("<I", struct.pack("<f", f))[0]
+
+    # 6: jitter / 6 (ao_compute.glsl:319), numerator in [0, 1]; W, H: (x + jitter) / W
+    assert L.rto_check_div_by_const(6.0, bits(2.0 ** -100), bits(2.0)) == 0
+    for b in (440, 330, 640, 480, 1920, 1080, 3840, 2160, 7680, 4320, 67, 45):
+        assert L.rto_check_div_by_const(float(b), bits(2.0 ** -30), bits(8192.0)) == 0
+        assert L.rto_check_div_by_const(float(b), bits(-(2.0 ** -30)), bits(-1.0)) == 0
+
+
+def test_known_answer_centre_pixel():
+    """centre pixel of 440x330, scene1, default camera: dir = (0,0,-1) hits sphere 0
+    (centre (0,-0.5,0), r 2) at t = 14 - sqrt(3.75); sphere 1 has del = -4; the plane is parallel."""
+    W, H = 440, 330
+    sc = Scenario("scene1")
+    o = orc.Oracle(W, H, 4)
+    o.set_scene(sc.shapes, sc.n)
+    slot, u, rb = sc.next(2, 4)
+    o.render(2, u, rb)
+    hit = o.get(orc.HIT_INDEX)
+    depth = o.get(orc.DEPTH, slot)
+    nrm = o.get(orc.NORMALS, slot)
+    assert hit[165, 220] == 0
+    t = 14.0 - math.sqrt(3.75)
+    assert abs(depth[165, 220, 0] * 4 - t) < 2e-6       # depth.x is t / AA
+    assert depth[165, 220, 3] == 0.25                    # 1 / AA
+    n = nrm[165, 220]
+    assert n[3] == 1.0 and abs(n[0]) < 1e-6 and abs(n[1] - 0.25) < 1e-6 and abs(n[2] - math.sqrt(3.75) / 2) < 1e-6
+    # top-left corner is sky: normal and depth zero, hit -1
+    assert hit[H - 1, 0] == -1 and not nrm[H - 1, 0].any() and depth[H - 1, 0, 0] == 0
+    o.close()
+
+
+def test_ray_counter_identities():
+    W, H, AA = 96, 64, 4
+    sc = Scenario("scene6")
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(sc.shapes, sc.n)
+    slot, u, rb = sc.next(1, AA)
+    o.render(1, u, rb)
+    st = o.stats()
+    assert st["pixels"] == W * H and st["primary"] == W * H and st["jittered"] == W * H * (AA - 1)
+    assert st["rays_closest"] == st["seg_terminal"] + st["seg_nonterminal"]
+    assert st["seg_terminal"] <= W * H * AA  # a sample may run out of depth instead of terminating
+    o.close()
