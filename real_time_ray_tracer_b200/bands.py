@@ -101,8 +101,7 @@ class BandedRenderer:
         import torch.distributed as dist
 
         if self.world == 1:
-            self.e.recv_lo.copy_(self.e.send_hi)
-            return
+            return  # a single band packs the wrapped row straight into its own lower halo
         r, n = self.rank, self.world
         ops = [dist.P2POp(dist.isend, self.e.send_hi, (r + 1) % n, self.group),
                dist.P2POp(dist.irecv, self.e.recv_lo, (r - 1) % n, self.group)]
@@ -116,8 +115,9 @@ class BandedRenderer:
     def render(self, mode: int, uniforms, rand_buffer):
         self.e.render_frame(mode, uniforms, rand_buffer)
         if mode == 1:
-            self.e.halo_pack()
-            self.exchange_halo()
+            if self.world > 1:
+                self.e.halo_pack()
+                self.exchange_halo()
             self.e.postprocess()
 
     def gather(self, slot: int, out=None):

@@ -211,3 +211,114 @@ def test_errors_are_reported_not_fatal():
         rtb.RayTracer(0, 10)
     with pytest.raises(rtb.RtError):
         rtb.RayTracer(10, 10, aa=17)
+
+
+@pytest.mark.parametrize("edge_mode", [rtb.EDGE_FLAT32, rtb.EDGE_CLEAN])
+@pytest.mark.parametrize("cuts", [[0, 30, 64], [0, 1, 9, 40, 64]])
+def test_row_bands_on_one_gpu_equal_the_whole_frame(edge_mode, cuts):
+    """N band contexts on one device, halo rows moved with device copies exactly as BandedRenderer moves them
+    between ranks (send_hi -> recv_lo of the next band, ring-wise; send_lo -> recv_hi of the previous)."""
+    import torch
+
+    from real_time_ray_tracer_b200 import bands
+
+    W, H, AA = 96, 64, 4
+    n = len(cuts) - 1
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        rts = [rtb.RayTracer(W, H, AA, edge_mode=edge_mode, band_y0=cuts[i], band_rows=cuts[i + 1] - cuts[i],
+                             band_index=i, band_count=n) for i in range(n)]
+        engs = []
+        for rt in rts:
+            rt.set_stream(stream.cuda_stream)
+            engs.append(bands.GpuBandEngine(rt))
+        sc = Scenario("scene1", keys=("d", "e"))
+        o = orc.Oracle(W, H, AA, edge_mode=edge_mode)
+        o.set_scene(sc.shapes, sc.n)
+        for rt in rts:
+            rt.upload_scene(sc.shapes, sc.n)
+        for k in range(11):
+            slot, u, rb = sc.next(1, AA)
+            for e in engs:
+                e.render_frame(1, u, rb)
+                e.halo_pack()
+            for i, e in enumerate(engs):
+                engs[(i + 1) % n].recv_lo.copy_(e.send_hi)
+                if i > 0:
+                    engs[i - 1].recv_hi.copy_(e.send_lo)
+            for e in engs:
+                e.postprocess()
+            o.render(1, u, rb)
+            o.postprocess()
+            stream.synchronize()
+            for buf, which in ((rtb.BUF_COLOR, orc.PIXELS), (rtb.BUF_NORMAL, orc.NORMALS), (rtb.BUF_DEPTH, orc.DEPTH)):
+                got = np.concatenate([rt.download(buf, slot) for rt in rts], axis=0)
+                want = o.get(which, slot)
+                assert same_bits(got, want), f"frame {k} buffer {buf}: {diff_report(got, want)}"
+            got = np.concatenate([rt.download(rtb.BUF_HIT_INDEX) for rt in rts], axis=0)
+            assert np.array_equal(got, o.get(orc.HIT_INDEX))
+        tot = {}
+        for rt in rts:
+            for kk, v in rt.stats().items():
+                if not kk.startswith("ms_"):
+                    tot[kk] = tot.get(kk, 0) + v
+        for kk, v in o.stats().items():
+            assert tot[kk] == v, (kk, tot[kk], v)
+        for rt in rts:
+            rt.close()
+        o.close()
+
+
+@pytest.mark.parametrize("kernel", ["tile", "stream"])
+def test_both_ao_kernels(kernel, monkeypatch):
+    """the tile kernel and the persistent streaming kernel are two schedules of the same arithmetic"""
+    monkeypatch.setenv("RT_AO_KERNEL", kernel)
+    W, H, AA = 203, 117, 4
+    for scene, rd in (("scene1", 20), ("scene6", 20), ("scene1", 1), ("scene5", 3)):
+        sc = Scenario(scene, keys=("e",))
+        with rtb.RayTracer(W, H, AA, recursion_depth=rd) as rt:
+            o = orc.Oracle(W, H, AA, recursion_depth=rd)
+            rt.upload_scene(sc.shapes, sc.n)
+            o.set_scene(sc.shapes, sc.n)
+            for k in range(3):
+                slot, u, rb = sc.next(1, AA)
+                rt.render_frame(1, u, rb)
+                rt.postprocess()
+                o.render(1, u, rb)
+                o.postprocess()
+                check_frame(rt, o, slot, 1, f"{kernel} {scene} rd {rd} frame {k}")
+            so, sg = o.stats(), rt.stats()
+            for kk in so:
+                assert so[kk] == sg[kk], (kernel, kk, so[kk], sg[kk])
+            o.close()
+
+
+def test_full_size_properties_1080p():
+    """BASELINE config 2 at full size, where the oracle is too slow for a tight loop: determinism (same inputs,
+    same bits), ray-counter identities, and agreement of the un-jittered hit index between modes 2 and 3."""
+    W, H, AA = 1920, 1080, 4
+    sc = Scenario("scene1", aspect=1.777777)
+    with rtb.RayTracer(W, H, AA) as rt:
+        rt.upload_scene(sc.shapes, sc.n)
+        slot, u, rb = sc.next(2, AA)
+        rt.render_frame(2, u, rb)
+        a = rt.download(rtb.BUF_COLOR, slot)
+        hit2 = rt.download(rtb.BUF_HIT_INDEX)
+        st = rt.stats()
+        assert st["pixels"] == W * H and st["rays_closest"] == st["seg_terminal"] + st["seg_nonterminal"]
+        assert st["jittered"] == W * H * (AA - 1) and st["rays_closest"] >= W * H * AA
+        rt.render_frame(2, u, rb)
+        assert same_bits(rt.download(rtb.BUF_COLOR, slot), a)
+        u3 = u.copy()
+        u3[0, 1] = 1
+        rt.render_frame(3, u3, None)
+        hit3 = rt.download(rtb.BUF_HIT_INDEX)
+        # thresholds differ (t > 0.0001 vs t > 0) but from the default camera every hit is metres away
+        assert np.array_equal(hit2, hit3)
+        assert np.isfinite(a).all() and a[..., 3].max() == 0
+        # one full-size row band of the oracle as a spot check (rows 500..507)
+        o = orc.Oracle(W, H, AA)
+        o.set_scene(sc.shapes, sc.n)
+        o.render(2, u, rb, rows=(500, 508))
+        assert same_bits(o.get(orc.PIXELS, slot)[500:508], a[500:508])
+        o.close()
