@@ -99,7 +99,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -159,11 +159,34 @@ def run_b200(args) -> None:
     W, H, AA, mode = fr.W, fr.H, fr.AA, fr.mode
     K, Wm = args.steps, args.warmup
 
-    # row bands; cost-weighted from a 1/8-scale probe frame rendered identically on every rank
+    # row bands: start from a 1/8-scale probe frame, then re-cut from the measured per-band device times
+    # (two warm-up rounds); contexts are rebuilt, which is fine before the timed region
     row_cost = None
     if world > 1 and not args.even_bands:
         row_cost = probe_row_cost(rtb, fr, local)
     plan = bands.plan_bands(H, world, row_cost)
+    if world > 1 and not args.even_bands:
+        for _ in range(args.replan):
+            y0, rows = plan[rank]
+            with rtb.RayTracer(W, H, AA, device=local, band_y0=y0, band_rows=rows, band_index=rank,
+                               band_count=world) as tmp:
+                tmp.upload_scene(fr.shapes, fr.n)
+                tmp.set_timing(True)
+                probe = Frames(args.workload)
+                acc = []
+                for k in range(4):
+                    slot, u, rb = probe.next()
+                    tmp.render_frame(mode, u, rb)
+                    if mode == 1:
+                        tmp.halo_pack()
+                        tmp.postprocess()
+                    st = tmp.stats()
+                    if k > 0:
+                        acc.append(st["ms_trace_last"] + st["ms_post_last"])
+            t = torch.tensor([float(np.mean(acc))], dtype=torch.float64, device=f"cuda:{local}")
+            allt = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(allt, t)
+            plan = bands.replan_from_times(plan, [float(x.item()) for x in allt], H)
     y0, rows = plan[rank]
     rt = rtb.RayTracer(W, H, AA, device=local, band_y0=y0, band_rows=rows, band_index=rank, band_count=world)
     # a non-default stream made current: the kernels, the NCCL ops and the timing events all live on it
@@ -188,13 +211,13 @@ def run_b200(args) -> None:
             br.gather(slot, full)
         return slot
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()  # nvidia-smi needs a moment to deliver its first sample: start before the warm-up
     for _ in range(Wm):
         step()
     barrier()
     rt.reset_stats()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -234,7 +257,7 @@ def run_b200(args) -> None:
     # ---- end to end through the public API with HOST buffers -----------------------------------
     e2e = None
     if args.e2e:
-        e2e = run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, min(K, 32), barrier)
+        e2e = run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, min(K, 64), barrier)
 
     if rank == 0:
         peak_tf = api.measure_fp32_peak(local)
@@ -302,25 +325,48 @@ def probe_row_cost(rtb, fr: "Frames", device: int):
 
 def run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, steps, barrier):
     """Same metric through the public API with HOST buffers: every step re-packs and uploads the scene
-    table, passes uniforms + rand_buffer from host memory, renders, gathers the bands and reads the frame's
-    colour image back into pinned host memory; the step ends when the image is on the host."""
+    table, passes uniforms + rand_buffer from host memory, renders (+ post-process, halo ring, gather) and
+    reads the frame's float4 colour image back into pinned host memory.  The read-back of frame k runs on a
+    copy stream while frame k+1 renders (two pinned buffers; the host waits for frame k-1 before it reuses a
+    buffer), so every frame reaches the host inside the timed region and PCIe overlaps with compute."""
+    from real_time_ray_tracer_b200 import bands as _bands
+
     W, H = fr.W, fr.H
-    pinned = torch.empty(W * H * 4, dtype=torch.float32, pin_memory=True) if rank == 0 else None
+    main = torch.cuda.current_stream()
+    copy_stream = torch.cuda.Stream(device=local)
+    pinned = [torch.empty(W * H * 4, dtype=torch.float32, pin_memory=True) for _ in range(2)] if rank == 0 else None
+    done = [torch.cuda.Event() for _ in range(2)]
+    color = None
+    if world == 1:
+        color = []
+        for s in range(rt.NF):
+            p, n = rt.device_ptr(L.BUF_COLOR, s)
+            color.append(_bands.device_tensor(p, n, local))
     rt.reset_stats()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(steps):
+    for k in range(steps):
         shapes = host.load_shape_buffer(fr.scene)           # loadShapeBuffer() every frame (main.cpp:768)
         rt.upload_scene(shapes, fr.n)
         slot, u, rb = fr.next()
         br.render(fr.mode, u, rb)
         if world > 1:
             br.gather(slot, full)
-            if rank == 0:
-                pinned.copy_(full, non_blocking=True)
-        else:
-            rt.download_async(L.BUF_COLOR, slot, pinned.data_ptr(), pinned.numel() * 4)
-        torch.cuda.synchronize()
+        if rank == 0:
+            rendered = torch.cuda.Event()
+            rendered.record(main)
+            if k >= 2:
+                done[k % 2].synchronize()                   # the consumer has frame k-2 before its buffer is reused
+            copy_stream.wait_event(rendered)
+            with torch.cuda.stream(copy_stream):
+                pinned[k % 2].copy_(full if world > 1 else color[slot], non_blocking=True)
+                done[k % 2].record(copy_stream)
+            if world > 1:
+                main.wait_event(done[k % 2])                # `full` is overwritten by the next gather
+    if rank == 0:
+        for e in done:
+            e.synchronize()
+    torch.cuda.synchronize()
     barrier()
     dt = time.perf_counter() - t0
     st = rt.stats()
@@ -337,8 +383,8 @@ def run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, steps, ba
             "ms_per_step": round(dt / steps * 1e3, 4), "steps": steps,
             "h2d_bytes_per_step": int(fr.n * 80 + 112 + (8 * fr.AA * 4 if fr.mode in (1, 2) else 0)),
             "d2h_bytes_per_step": int(W * H * 16),
-            "what": "upload_scene + uniforms + rand_buffer from host, render (+post-process), gather, "
-                    "float4 colour image read back to pinned host memory, synchronised every frame"}
+            "what": "upload_scene + uniforms + rand_buffer from host, render (+post-process, halo, gather), float4 "
+                    "colour image read back to pinned host memory; read-back of frame k overlaps frame k+1"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -428,7 +474,7 @@ def run_reference(args) -> None:
     t = time.perf_counter()
     run(u, rb, (y0, y1))
     est = (time.perf_counter() - t) * fr.H / (y1 - y0)
-    rows = _band_for_budget(fr.H, est, max(0.25, args.ref_budget / max(1, K + Wm)))
+    rows = _band_for_budget(fr.H, est, max(0.1, args.ref_budget / max(1, K + Wm)))
     for _ in range(Wm):
         slot, u, rb = fr.next()
         run(u, rb, rows)
@@ -458,13 +504,14 @@ def run_reference(args) -> None:
 def main():
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
-    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=512)
+    ap.add_argument("--warmup", type=int, default=64)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", dest="e2e", action="store_false")
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     ap.add_argument("--even-bands", action="store_true", help="equal-height bands instead of cost-weighted")
+    ap.add_argument("--replan", type=int, default=2, help="band re-cut rounds from measured times (N > 1)")
     ap.add_argument("--ref-budget", type=float, default=60.0, help="seconds of CPU work for --impl reference")
     args = ap.parse_args()
     if args.warmup < 3:

@@ -40,6 +40,16 @@ def plan_bands(height: int, n: int, row_cost: Optional[Sequence[float]] = None) 
     return [(cuts[i], cuts[i + 1] - cuts[i]) for i in range(n)]
 
 
+def replan_from_times(plan: List[Tuple[int, int]], band_ms: Sequence[float], height: int) -> List[Tuple[int, int]]:
+    """New cut points from the measured device time of each band: the time of a band is spread evenly over
+    its rows (a piecewise-constant cost density) and the bands are re-cut to equal cost.  Two or three
+    iterations during warm-up converge; this is the "cost-weighted band heights" of SURVEY 8(e)."""
+    cost = np.empty(height, dtype=np.float64)
+    for (y0, rows), ms in zip(plan, band_ms):
+        cost[y0:y0 + rows] = max(float(ms), 1e-6) / rows
+    return plan_bands(height, len(plan), cost)
+
+
 class _DevBuf:
     """a raw device pointer as a __cuda_array_interface__ object (for torch.as_tensor)"""
 
