@@ -385,13 +385,13 @@ __device__ __forceinline__ float nb_weight(float4 nn, float nd, float nb, const 
     if (r.normal.w < 0.001f) return 1.0f;
     float normal_dot = dot3(xyz(nn), xyz(r.normal));
     float depth_diff = 1.0f - clampf(fabsf(nd - r.depth.x), 0.0f, 1.0f);
-    float bounces_diff = 1.0f - clampf(__fdiv_rn(fabsf(nb - r.depth.y), 1.7f), 0.0f, 1.0f);
+    float bounces_diff = 1.0f - clampf(div_const(fabsf(nb - r.depth.y), 1.7f, RT_INV1P7), 0.0f, 1.0f);
     return normal_dot * depth_diff * bounces_diff + 0.2f;
 }
 
-constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 8;
+constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 4;
 
-__global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y) rt_ao_postprocess_kernel(const __grid_constant__ PostParams q)
+__global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, 8) rt_ao_postprocess_kernel(const __grid_constant__ PostParams q)
 {
     const int x = blockIdx.x * PP_BLOCK_X + threadIdx.x;
     const int yl = blockIdx.y * PP_BLOCK_Y + threadIdx.y;
@@ -462,47 +462,67 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y) rt_ao_postprocess_kern
                               scale4(r, R.color));
             color = div4(num, 1.0f + u + d + l + r);
 
-            // temporal blend over the previous NF-1 ring slots (:175-201)
+            // temporal blend over the previous NF-1 ring slots (:175-201).  The shader walks the ring one
+            // frame at a time and stops at the first rejected frame; done literally that is a chain of up to
+            // NF-1 dependent round trips to HBM.  Here the normal/depth records of up to four frames are
+            // requested together, their coefficients evaluated in ring order, and the colours of the accepted
+            // ones requested together: two round trips per batch, same arithmetic in the same order.
             float4 color_sum = z4;
             float denominator = 0.9f;
-            for (int i = 1; i < q.NF; i++) {
-                int cf = q.slot - i;
-                if (cf < 0) cf += q.NF;
-                const size_t off = (size_t)cf * plane + pix;
-                const float4 cn = q.ring_normal[off];
-                const float2 cd = q.ring_depth_xy[off];
-                n_eval++;
-                float normal_dot = dot3(xyz(nn), xyz(cn));
-                float depth_diff = 1.0f - clampf(fabsf(new_depth - cd.x), 0.0f, 1.0f);
-                float bounces_diff = 1.0f - clampf(__fdiv_rn(fabsf(new_bounces - cd.y), 1.7f), 0.0f, 1.0f);
-                float coeff = normal_dot * depth_diff * bounces_diff;
-                if (coeff > 0.85f) {
-                    color_sum = add4(color_sum, scale4(coeff, q.ring_color[off]));
-                    denominator += coeff;
-                    n_acc++;
-                } else
-                    break;
+            bool go = true;
+            for (int i0 = 1; go && i0 < q.NF; i0 += 4) {
+                float4 cn[4];
+                float2 cd[4];
+                size_t off[4];
+                float coeff[4];
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    int cf = q.slot - (i0 + b);
+                    if (cf < 0) cf += q.NF;
+                    off[b] = (size_t)cf * plane + pix;
+                    if (i0 + b < q.NF) {
+                        cn[b] = q.ring_normal[off[b]];
+                        cd[b] = q.ring_depth_xy[off[b]];
+                    }
+                }
+                int acc = 0;
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    if (go && i0 + b < q.NF) {
+                        n_eval++;
+                        float normal_dot = dot3(xyz(nn), xyz(cn[b]));
+                        float depth_diff = 1.0f - clampf(fabsf(new_depth - cd[b].x), 0.0f, 1.0f);
+                        float bounces_diff = 1.0f - clampf(div_const(fabsf(new_bounces - cd[b].y), 1.7f, RT_INV1P7), 0.0f, 1.0f);
+                        coeff[b] = normal_dot * depth_diff * bounces_diff;
+                        if (coeff[b] > 0.85f) acc = b + 1; else go = false;
+                    }
+                }
+                float4 hc[4];
+#pragma unroll
+                for (int b = 0; b < 4; b++)
+                    if (b < acc) hc[b] = q.ring_color[off[b]];
+#pragma unroll
+                for (int b = 0; b < 4; b++)
+                    if (b < acc) {
+                        color_sum = add4(color_sum, scale4(coeff[b], hc[b]));
+                        denominator += coeff[b];
+                        n_acc++;
+                    }
             }
             color = div4(add4(scale4(0.9f, color), color_sum), denominator);
         }
         q.ring_color[(size_t)q.slot * plane + pix] = color; // pixels[new_frame] and img_output
     }
+    // per-warp flush, no block barrier: a warp of background pixels must not wait for its block-mates
     const int idx[3] = { ST_PP_NONBACKGROUND, ST_PP_HIST_EVALUATED, ST_PP_HIST_ACCEPTED };
     unsigned val[3] = { n_nonbg, n_eval, n_acc };
-    // flush_stats indexes by threadIdx.x; this block is 2-D
-    __shared__ unsigned s_acc[3];
     const int tid = threadIdx.y * PP_BLOCK_X + threadIdx.x;
-    if (tid < 3) s_acc[tid] = 0;
-    __syncthreads();
+    const unsigned gw = (blockIdx.x + blockIdx.y * gridDim.x) * ((PP_BLOCK_X * PP_BLOCK_Y) >> 5) + (tid >> 5);
+    unsigned long long *st = q.stats + (gw % STAT_STRIPES) * ST_COUNT;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
         unsigned v = __reduce_add_sync(0xffffffffu, val[k]);
-        if ((tid & 31) == 0 && v) atomicAdd(&s_acc[k], v);
-    }
-    __syncthreads();
-    if (tid < 3 && s_acc[tid]) {
-        unsigned stripe = (blockIdx.x + blockIdx.y * gridDim.x) % STAT_STRIPES;
-        atomicAdd(&q.stats[stripe * ST_COUNT + idx[tid]], (unsigned long long)s_acc[tid]);
+        if ((tid & 31) == 0 && v) atomicAdd(&st[idx[k]], (unsigned long long)v);
     }
 }
 

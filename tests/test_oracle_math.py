@@ -61,6 +61,8 @@ def test_division_by_frame_constants_is_ieee():
 
     # 6: jitter / 6 (ao_compute.glsl:319), numerator in [0, 1]; W, H: (x + jitter) / W
     assert L.rto_check_div_by_const(6.0, bits(2.0 ** -100), bits(2.0)) == 0
+    # 1.7: |bounces - bounces'| / 1.7 in the post-processing weights (aop_postprocessing.glsl:94)
+    assert L.rto_check_div_by_const(float(np.float32(1.7)), bits(2.0 ** -100), bits(4096.0)) == 0
     for b in (440, 330, 640, 480, 1920, 1080, 3840, 2160, 7680, 4320, 67, 45):
         assert L.rto_check_div_by_const(float(b), bits(2.0 ** -30), bits(8192.0)) == 0
         assert L.rto_check_div_by_const(float(b), bits(-(2.0 ** -30)), bits(-1.0)) == 0
