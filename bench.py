@@ -197,7 +197,11 @@ def run_b200(args) -> None:
     rt.upload_scene(fr.shapes, fr.n)
     eng = bands.GpuBandEngine(rt)
     br = bands.BandedRenderer(eng, W, H, plan, rank, world)
-    full = torch.empty(W * H * 4, dtype=torch.float32, device=f"cuda:{local}") if (world > 1 and rank == 0) else None
+    # rank 0 assembles frames in two alternating buffers so the gather of frame k overlaps the trace of k+1
+    fulls = [torch.empty(W * H * 4, dtype=torch.float32, device=f"cuda:{local}") for _ in range(2)] \
+        if (world > 1 and rank == 0) else [None, None]
+    full = fulls[0]
+    pending = {"works": [], "k": 0}
 
     def barrier():
         if world > 1:
@@ -208,14 +212,21 @@ def run_b200(args) -> None:
         slot, u, rb = fr.next()
         br.render(mode, u, rb)
         if world > 1:
-            br.gather(slot, full)
+            br.gather_finish(pending["works"])          # frame k-1 is complete on rank 0
+            pending["works"] = br.gather_start(slot, fulls[pending["k"] & 1])
+            pending["k"] += 1
         return slot
+
+    def drain():
+        br.gather_finish(pending["works"])
+        pending["works"] = []
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()  # nvidia-smi needs a moment to deliver its first sample: start before the warm-up
     for _ in range(Wm):
         step()
+    drain()
     barrier()
     rt.reset_stats()
     barrier()
@@ -223,6 +234,7 @@ def run_b200(args) -> None:
     e0.record()
     for _ in range(K):
         step()
+    drain()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -511,7 +523,7 @@ def main():
     ap.add_argument("--no-e2e", dest="e2e", action="store_false")
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     ap.add_argument("--even-bands", action="store_true", help="equal-height bands instead of cost-weighted")
-    ap.add_argument("--replan", type=int, default=2, help="band re-cut rounds from measured times (N > 1)")
+    ap.add_argument("--replan", type=int, default=3, help="band re-cut rounds from measured times (N > 1)")
     ap.add_argument("--ref-budget", type=float, default=60.0, help="seconds of CPU work for --impl reference")
     args = ap.parse_args()
     if args.warmup < 3:

@@ -185,7 +185,8 @@ int rt_get_stats(rt_ctx *ctx, rt_stats *out); /* synchronises */
 int rt_reset_stats(rt_ctx *ctx);
 
 /* diagnostics used by the parity tests and the benchmark */
-/* element-wise built-ins on the device: kind 0 sin(a), 1 pow(a,b), 2 random(vec2(a,b)) */
+/* element-wise built-ins on the device: kind 0 sin(a), 1 pow(a,b), 2 random(vec2(a,b)),
+ * 3 1/sqrt(a) as normalize() forms it, 4 sqrt(a) as the sphere test forms it */
 int rt_debug_eval_math(int device, int kind, const float *a, const float *b, float *out, size_t n);
 /* dependent-free FFMA microbenchmark: measured FP32 FMA throughput of the device in TFLOP/s */
 int rt_measure_fp32_peak(int device, double *tflops_out);

@@ -145,7 +145,7 @@ def eval_math(kind, a, b=None):
     a = np.ascontiguousarray(a, dtype=np.float32)
     b = np.zeros_like(a) if b is None else np.ascontiguousarray(b, dtype=np.float32)
     out = np.empty_like(a)
-    lib().rto_eval_math({"sin": 0, "pow": 1, "random": 2}[kind], _ptr(a), _ptr(b), _ptr(out), a.size)
+    lib().rto_eval_math({"sin": 0, "pow": 1, "random": 2, "inv_sqrt": 3, "sqrt_pos": 4}[kind], _ptr(a), _ptr(b), _ptr(out), a.size)
     return out
 
 

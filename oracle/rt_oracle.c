@@ -663,16 +663,18 @@ int rto_put(rto_ctx *c, int which, int slot, const void *in)
 void rto_get_stats(const rto_ctx *c, rto_stats *out) { *out = c->stats; }
 void rto_reset_stats(rto_ctx *c) { memset(&c->stats, 0, sizeof c->stats); }
 
-/* element-wise built-ins for the math parity tests: kind 0 sin, 1 pow(x,y), 2 random(x,y) */
+/* element-wise built-ins for the math parity tests: kind 0 sin, 1 pow(x,y), 2 random(x,y),
+ * 3 1/sqrt(x), 4 sqrt(x) for x > 0 else 0 */
 void rto_eval_math(int kind, const float *a, const float *b, float *out, long long n)
 {
     for (long long i = 0; i < n; i++) {
         if (kind == 0) out[i] = rtr_sin(a[i]);
         else if (kind == 1) out[i] = rtr_pow(a[i], b[i]);
-        else {
+        else if (kind == 2) {
             rtr_v2 st = { a[i], b[i] };
             out[i] = rtr_random(st);
-        }
+        } else if (kind == 3) out[i] = 1.0f / sqrtf(a[i]);
+        else out[i] = (a[i] > 0.0f) ? sqrtf(a[i]) : 0.0f;
     }
 }
 

@@ -146,7 +146,7 @@ def debug_eval_math(kind: str, a, b=None, device: int = 0) -> np.ndarray:
     a = np.ascontiguousarray(a, dtype=np.float32)
     b = np.zeros_like(a) if b is None else np.ascontiguousarray(b, dtype=np.float32)
     out = np.empty_like(a)
-    rc = lib.rt_debug_eval_math(device, {"sin": 0, "pow": 1, "random": 2}[kind], a.ctypes.data_as(C.c_void_p),
+    rc = lib.rt_debug_eval_math(device, {"sin": 0, "pow": 1, "random": 2, "inv_sqrt": 3, "sqrt_pos": 4}[kind], a.ctypes.data_as(C.c_void_p),
                                 b.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), a.size)
     if rc != L.RT_OK:
         raise RtError(rc, lib.rt_last_error(None).decode())

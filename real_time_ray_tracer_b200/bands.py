@@ -130,17 +130,18 @@ class BandedRenderer:
                 self.exchange_halo()
             self.e.postprocess()
 
-    def gather(self, slot: int, out=None):
-        """Assemble pixels[slot] of all bands on rank 0 into ``out`` (float32 [H*W*4], row-major).
-        Bands are contiguous row ranges, so every band lands in place with no re-packing."""
+    def gather_start(self, slot: int, out=None):
+        """Start assembling pixels[slot] of all bands on rank 0 into ``out`` (float32 [H*W*4], row-major) and
+        return the pending work handles.  Bands are contiguous row ranges, so every band lands in place with no
+        re-packing.  The transfers run on NCCL's stream: the caller may trace the next frame meanwhile (a ring
+        slot is not rewritten for NF-1 frames) and calls ``gather_finish`` before it reuses ``out``."""
         import torch.distributed as dist
 
         mine = self.e.band_color(slot)
         if self.world == 1:
             if out is not None:
                 out.copy_(mine)
-                return out
-            return mine
+            return []
         if self.rank == 0:
             ops = []
             for r, (y0, rows) in enumerate(self.bands):
@@ -149,9 +150,17 @@ class BandedRenderer:
                     dst.copy_(mine)
                 else:
                     ops.append(dist.P2POp(dist.irecv, dst, r, self.group))
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
-            return out
-        for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, mine, 0, self.group)]):
+            return dist.batch_isend_irecv(ops)
+        return dist.batch_isend_irecv([dist.P2POp(dist.isend, mine, 0, self.group)])
+
+    @staticmethod
+    def gather_finish(works):
+        for w in works:
             w.wait()
-        return None
+
+    def gather(self, slot: int, out=None):
+        """blocking gather: ``out`` (rank 0) holds the whole frame when the current stream reaches this point"""
+        self.gather_finish(self.gather_start(slot, out))
+        if self.world == 1 and out is None:
+            return self.e.band_color(slot)
+        return out if self.rank == 0 else None

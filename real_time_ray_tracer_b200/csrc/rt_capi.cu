@@ -477,7 +477,7 @@ int rt_reset_stats(rt_ctx *c)
 // ---- diagnostics -------------------------------------------------------------------------------
 int rt_debug_eval_math(int device, int kind, const float *a, const float *b, float *out, size_t n)
 {
-    if (!a || !out || kind < 0 || kind > 2 || (kind != 0 && !b)) return RT_EINVAL;
+    if (!a || !out || kind < 0 || kind > 4 || ((kind == 1 || kind == 2) && !b)) return RT_EINVAL;
     if (rt_device_count() <= device || device < 0) return RT_ENODEVICE;
     if (n == 0) return RT_OK;
     if (cudaSetDevice(device) != cudaSuccess) return RT_ECUDA;

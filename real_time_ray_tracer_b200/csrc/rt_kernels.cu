@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid
                     float bx = s4x * fx - (s3x * fx) * s2x;
                     float by = s4y * fy - (s3y * fy) * s2y;
                     float r1 = random2(ax, ay), r2 = random2(bx, by);
-                    float inv = __fdiv_rn(1.0f, __fsqrt_rn(dot2(r1, r2, r1, r2)));
+                    float inv = inv_sqrt_ieee(dot2(r1, r2, r1, r2));
                     float jx = div_const(r1 * inv, 6.0f, RT_INV6) - 0.08333f;
                     float jy = div_const(r2 * inv, 6.0f, RT_INV6) - 0.08333f;
                     hp = div_const(fx + jx, p.fW, p.invW);
@@ -615,7 +615,13 @@ __global__ void rt_eval_math_kernel(int kind, const float *a, const float *b, fl
     if (i >= n) return;
     if (kind == 0) out[i] = sin_f32(a[i]);
     else if (kind == 1) out[i] = pow_f32(a[i], b[i]);
-    else out[i] = random2(a[i], b[i]);
+    else if (kind == 2) out[i] = random2(a[i], b[i]);
+    else if (kind == 3) out[i] = inv_sqrt_ieee(a[i]);   // must equal 1.0f / sqrtf(a)
+    else {                                               // must equal sqrtf(a) for a > 0
+        float im = sqrt_fast(a[i]);
+        if (!sqrt_fast_ok(a[i])) im = (a[i] > 0.0f) ? __fsqrt_rn(a[i]) : 0.0f;
+        out[i] = im;
+    }
 }
 cudaError_t launch_eval_math(int kind, const float *a, const float *b, float *out, size_t n, cudaStream_t s)
 {

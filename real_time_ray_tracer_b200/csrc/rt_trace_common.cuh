@@ -11,16 +11,20 @@ namespace rt {
 // ---------------------------------------------------------------------------------------------
 // intersection (ao_compute.glsl:75-136)
 // ---------------------------------------------------------------------------------------------
+// sphere_eval_ray with ONE branch.  Every caller only tests the result against a threshold >= 0
+// (ao_compute.glsl:186, p_compute.glsl:161,180, h_compute.glsl:202), so the shader's `del == 0 -> -b` case
+// folds into the general formula: with sqrt(0) = 0 it gives -b when -b >= 0 and a negative number (rejected
+// either way) otherwise.  del < 0 and NaN give -1.  The branch stays because whole warps miss a sphere
+// (sky, floor) and then skip the square root altogether.
 __device__ __forceinline__ float sphere_eval_ray(float3 pos, float3 dir, float4 s0, float r2)
 {
     float3 pmc = sub3(pos, xyz(s0));
     float b = dot3(dir, pmc);
     float del = b * b - dot3(pmc, pmc) + r2;
     float res = -1.0f;
-    if (del == 0.0f) {
-        res = -b;
-    } else if (del > 0.0f) {
-        float im = __fsqrt_rn(del);
+    if (del >= 0.0f) {
+        float im = sqrt_fast(del);
+        if (!sqrt_fast_ok(del)) im = (del > 0.0f) ? __fsqrt_rn(del) : 0.0f; // 0, subnormal, +inf
         float t1 = -b + im;
         float t2 = -b - im;
         res = (t2 < 0.0f) ? ((t1 < 0.0f) ? -1.0f : t1) : t2;
@@ -47,18 +51,20 @@ __device__ __forceinline__ float eval_ray(const DevShape &s, float3 pos, float3 
 // (ao_compute.glsl:183-194 / p_compute.glsl:177-188 / h_compute.glsl:199-210)
 __device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, float3 dir, float tmin, float &t_out)
 {
-    float t = -1.0f;
+    // `res_t > tmin && (res_t < t || t < 0)` with t starting at -1: candidates are positive, so they order
+    // like unsigned integers and "no hit yet" can be the all-ones pattern (above +inf, like the shader's t < 0)
+    unsigned tb = 0xffffffffu;
     int ind = -1;
 #pragma unroll
     for (int i = 0; i < RT_MAX_SHAPES; i++) {
         if (i >= p.nshapes) break;
         float res_t = eval_ray(p.shapes[i], pos, dir);
-        if (res_t > tmin && (res_t < t || t < 0.0f)) {
-            t = res_t;
+        if (res_t > tmin && __float_as_uint(res_t) < tb) {
+            tb = __float_as_uint(res_t);
             ind = i;
         }
     }
-    t_out = t;
+    t_out = (ind < 0) ? -1.0f : __uint_as_float(tb);
     return ind;
 }
 

@@ -32,6 +32,13 @@ def test_math_builtins_bit_exact():
     for y in (1.0 / 2.2, 500.0):
         b = np.full_like(a, np.float32(y))
         assert same_bits(api.debug_eval_math("pow", a, b), orc.eval_math("pow", a, b))
+    # the kernels' range-check-free sqrt / reciprocal: every exponent, subnormals, 0, inf, negatives, NaN
+    bits = rng.integers(0, 2 ** 32, 2_000_000, dtype=np.uint64).astype(np.uint32)
+    v = np.concatenate([bits.view(np.float32), np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 1e-45, 1.17549435e-38, 3.4e38],
+                                                          np.float32)])
+    with np.errstate(all="ignore"):
+        assert same_bits(api.debug_eval_math("inv_sqrt", v), orc.eval_math("inv_sqrt", v))
+        assert same_bits(api.debug_eval_math("sqrt_pos", v), orc.eval_math("sqrt_pos", v))
     sx = rng.uniform(0, 8000, 200000).astype(np.float32)
     sy = rng.uniform(0, 4400, 200000).astype(np.float32)
     assert same_bits(api.debug_eval_math("random", sx, sy), orc.eval_math("random", sx, sy))
