@@ -76,6 +76,7 @@ typedef struct rto_ctx {
     int nshapes;
     rto_stats stats;
     int nthreads;
+    unsigned char *pathlen; /* optional analysis aid: segments walked per (pixel, sample), [y][x][aa] */
 } rto_ctx;
 
 /* views into the struct */
@@ -129,6 +130,9 @@ void rto_destroy(rto_ctx *c)
     if (!c) return;
     free(c->base); free(c->raw); free(c->image); free(c->hit_index); free(c);
 }
+
+/* analysis aid (schedule simulations in DESIGN.md): caller-owned buffer of W*H*AA bytes, or NULL */
+void rto_set_pathlen_buffer(rto_ctx *c, unsigned char *buf) { if (c) c->pathlen = buf; }
 
 int rto_set_threads(rto_ctx *c, int n)
 {
@@ -284,6 +288,7 @@ static rtr_v4 ambient_occlusion(rto_ctx *c, rtr_v3 dir, int aa, unsigned x, unsi
             dep->y = (float)(RD - i);
         }
         result = rtr_mul4(result, a0);
+        if (c->pathlen) c->pathlen[((long long)y * c->cfg.width + x) * c->cfg.aa + aa] = (unsigned char)(RD - i + 1);
         if (stop) { st->seg_terminal++; break; }
         st->seg_nonterminal++;
     }

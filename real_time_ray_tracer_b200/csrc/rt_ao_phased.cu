@@ -1,0 +1,237 @@
+// rt_ao_phased.cu -- AO trace (modes 1 and 2), default kernel: sample-synchronous head, flattened tail.
+//
+// Same arithmetic as resources/ao_compute.glsl:161-340 (= aop_compute.glsl:159-337), scheduled by what
+// the path-length distribution looks like (tools/schedule_sim.py over the oracle, config 2: 42 % of the
+// samples end on their camera ray, 42 % on the segment after it, 12 % on the third, 0.02 % run all 20):
+//
+//   HEAD  for each sample of a chunk of four, with the warp converged: build the camera ray (jitter: two
+//         random() and a normalize), closest hit with the per-frame camera constants (FrameParams::prim),
+//         classify; lanes that hit a non-emissive shape draw the sample's random unit vector, bounce, trace
+//         the SECOND segment and classify again.  A warp is an 8x4 pixel tile, so these lanes are almost
+//         always the whole warp or none of it (simulated lane utilisation 0.996).
+//   TAIL  the few samples still alive after two segments keep (dir, t, hit ids, random vector) in shared
+//         memory; each lane then walks its own survivors in sample order in ONE flattened loop whose body
+//         is bounce + closest hit + classify, adding the finished samples of the head on the way so the
+//         colour sum keeps the shader's order  ((s0 + s1) + s2) + s3.
+//
+// The first-generation kernel (rt_ao_trace_kernel, one flattened loop over everything) ran all of that in
+// one loop body: lanes out of phase made the warp execute camera-ray setup, random vector, both bounce
+// flavours and the traversal in most iterations (ncu: 18.6 of 32 lanes active per instruction).
+#include "rt_kernels.cuh"
+#include "rt_math.cuh"
+#include "rt_trace_common.cuh"
+
+namespace rt {
+
+constexpr int PH_TILE_W = 16, PH_TILE_H = 8, PH_THREADS = 128;
+constexpr int AO_CHUNK = 4;     // samples whose state is parked in shared memory at a time
+constexpr int ST_FIELDS = 8;    // survivor: dir.xyz, t, ids, ru.xyz   finished: colour.rgb, terminal depth
+
+__global__ void __launch_bounds__(PH_THREADS) rt_ao_phased_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+{
+    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ float4 s_rand[2 * RT_MAX_AA];
+    __shared__ float s_state[AO_CHUNK][ST_FIELDS][PH_THREADS]; // [sample][field][thread]: conflict-free
+    const int tid = threadIdx.x;
+#pragma unroll 1
+    for (int i = tid; i < p.nshapes; i += PH_THREADS) s_shapes[i] = p.shapes[i];
+#pragma unroll 1
+    for (int i = tid; i < 2 * p.AA; i += PH_THREADS) s_rand[i] = p.rand[i];
+    __syncthreads();
+
+    const int lane = tid & 31, warp = tid >> 5;
+    const int x = blockIdx.x * PH_TILE_W + ((warp & 1) << 3) + (lane & 7);
+    const int yl = blockIdx.y * PH_TILE_H + ((warp >> 1) << 2) + (lane >> 3);
+    const bool active = (x < p.W) && (yl < p.rows);
+    unsigned n_nonterm = 0, n_term = 0;
+
+    if (active) {
+        const int y = p.y0 + yl;
+        const size_t pix = (size_t)yl * p.W + x;
+        const float fx = (float)x, fy = (float)y;
+        const int RD = p.RD;
+        float ar = 0.0f, ag = 0.0f, ab = 0.0f;  // result_color summed over samples, in sample order
+        float3 nrm = mk3(0.0f, 0.0f, 0.0f);
+        float nrm_w = 0.0f;
+        float dx = 0.0f, dy = 0.0f, dw = 0.0f;  // depth_buffer[frame][x][y] (.z is always 0)
+        bool keep_normal = false;
+        int hit0 = -1;
+
+        for (int c0 = 0; c0 < p.AA; c0 += AO_CHUNK) {
+            const int nch = min(AO_CHUNK, p.AA - c0);
+            unsigned pending = 0;
+
+            // ---------------------------------------------------------------- HEAD (sample-synchronous)
+#pragma unroll 1
+            for (int k = 0; k < nch; k++) {
+                const int aa = c0 + k;
+                const float4 rf = s_rand[2 * aa], rs = s_rand[2 * aa + 1];
+                float hp, vp;
+                if (aa == 0) {
+                    hp = div_const(fx, p.fW, p.invW);
+                    vp = div_const(fy, p.fH, p.invH);
+                } else {
+                    // ao_compute.glsl:310-323, seeds cross-wired exactly as written there
+                    float s1x = rs.x, s1y = rf.y, s2x = rf.z, s2y = rs.w;
+                    float s3x = rf.x, s3y = rs.y, s4x = rs.z, s4y = rf.w;
+                    float ax = ((s1x + fx * s2x) - fx) + s3x;
+                    float ay = ((s1y + fy * s2y) - fy) + s3y;
+                    float bx = s4x * fx - (s3x * fx) * s2x;
+                    float by = s4y * fy - (s3y * fy) * s2y;
+                    float r1 = random2(ax, ay), r2 = random2(bx, by);
+                    float inv = inv_sqrt_ieee(dot2(r1, r2, r1, r2));
+                    float jx = div_const(r1 * inv, 6.0f, RT_INV6) - 0.08333f;
+                    float jy = div_const(r2 * inv, 6.0f, RT_INV6) - 0.08333f;
+                    hp = div_const(fx + jx, p.fW, p.invW);
+                    vp = div_const(fy + jy, p.fH, p.invH);
+                }
+                float3 dir = primary_dir(p, hp, vp);
+                float t;
+                int ind = closest_hit_primary(p, dir, 0.0001f, t);
+                const bool first = (aa == 0);
+                if (first) hit0 = ind;
+
+                // finished-sample record: colour and RD - i of the terminating segment (-1: ran out of depth)
+                float f_r = p.bg.x, f_g = p.bg.y, f_b = p.bg.z, f_term = 0.0f;
+                bool bounce = false;
+                if (ind >= 0) {
+                    const DevShape &s = s_shapes[ind];
+                    if (s.emissive > 0.9f) {
+                        f_r = s.col.x; f_g = s.col.y; f_b = s.col.z;
+                        if (first) {
+                            // the shader returns before touching normals/depth: the slot keeps what an
+                            // earlier frame left there (ao_compute.glsl:199-208 precede :222-229)
+                            keep_normal = true;
+                            dx = o.depth_xy[pix].x;
+                            dw = o.depth_w[pix];
+                        }
+                    } else {
+                        bounce = true;
+                    }
+                }
+                if (!bounce) n_term++; else n_nonterm++;
+
+                if (bounce) {
+                    const DevShape &s = s_shapes[ind];
+                    const float3 ru = get_pt_within_unit_sphere(rf, rs, fx, fy);
+                    float3 pos, normal;
+                    ao_bounce(p, s, t, ru, dir, pos, normal);
+                    if (first) { nrm = normal; nrm_w = 1.0f; dx = t; dw = 1.0f; }
+                    f_r = s.col.x; f_g = s.col.y; f_b = s.col.z;    // 1 * a0 == a0
+                    f_term = -1.0f;
+                    if (RD > 1) {
+                        // ---- second segment
+                        float t2;
+                        const int ind2 = closest_hit(p, pos, dir, 0.0001f, t2);
+                        if (ind2 < 0) {
+                            f_r *= p.bg.x; f_g *= p.bg.y; f_b *= p.bg.z;
+                            f_term = 1.0f;
+                            n_term++;
+                        } else {
+                            const DevShape &s2 = s_shapes[ind2];
+                            if (s2.emissive > 0.9f) {
+                                f_r *= s2.col.x; f_g *= s2.col.y; f_b *= s2.col.z;
+                                f_term = 1.0f;
+                                n_term++;
+                            } else {
+                                n_nonterm++;
+                                if (RD > 2) {
+                                    // survivor: the tail re-forms its colour from the two ids
+                                    pending |= 1u << k;
+                                    s_state[k][0][tid] = dir.x; s_state[k][1][tid] = dir.y; s_state[k][2][tid] = dir.z;
+                                    s_state[k][3][tid] = t2;
+                                    s_state[k][4][tid] = __int_as_float(ind | (ind2 << 8));
+                                    s_state[k][5][tid] = ru.x; s_state[k][6][tid] = ru.y; s_state[k][7][tid] = ru.z;
+                                } else {
+                                    f_r *= s2.col.x; f_g *= s2.col.y; f_b *= s2.col.z;
+                                }
+                            }
+                        }
+                    }
+                }   // a miss on the first segment leaves normal = 0, depth = (0, 0, 0, 0): the initial values
+                if (!((pending >> k) & 1u)) {
+                    s_state[k][0][tid] = f_r; s_state[k][1][tid] = f_g; s_state[k][2][tid] = f_b;
+                    s_state[k][3][tid] = f_term;
+                }
+            }
+
+            // ---------------------------------------------------------------- TAIL (flattened per lane)
+            int k = 0, i = 0, ind = -1;
+            bool need_load = true;
+            float3 dir = p.cam, ru = p.cam;
+            float t = 0.0f, cr = 0.0f, cg = 0.0f, cb = 0.0f;
+            for (;;) {
+                if (need_load) {
+                    while (k < nch && !((pending >> k) & 1u)) {
+                        ar += s_state[k][0][tid]; ag += s_state[k][1][tid]; ab += s_state[k][2][tid];
+                        const float ft = s_state[k][3][tid];
+                        if (ft >= 0.0f) dy = ft;
+                        k++;
+                    }
+                    if (k >= nch) break;
+                    dir = mk3(s_state[k][0][tid], s_state[k][1][tid], s_state[k][2][tid]);
+                    t = s_state[k][3][tid];
+                    const int ids = __float_as_int(s_state[k][4][tid]);
+                    ru = mk3(s_state[k][5][tid], s_state[k][6][tid], s_state[k][7][tid]);
+                    ind = ids >> 8;
+                    const DevShape &a = s_shapes[ids & 0xff], &b = s_shapes[ind];
+                    cr = a.col.x * b.col.x; cg = a.col.y * b.col.y; cb = a.col.z * b.col.z;
+                    i = RD - 2;
+                    need_load = false;
+                }
+                // one path segment: bounce off (ind, t), closest hit, classify (ao_compute.glsl:161-261)
+                float3 pos, normal;
+                ao_bounce(p, s_shapes[ind], t, ru, dir, pos, normal);
+                ind = closest_hit(p, pos, dir, 0.0001f, t);
+                bool stop = true;
+                float a0r = p.bg.x, a0g = p.bg.y, a0b = p.bg.z;
+                if (ind >= 0) {
+                    const DevShape &s = s_shapes[ind];
+                    a0r = s.col.x; a0g = s.col.y; a0b = s.col.z;
+                    stop = s.emissive > 0.9f;
+                }
+                cr *= a0r; cg *= a0g; cb *= a0b;
+                if (stop) n_term++; else n_nonterm++;
+                const float term = (float)(RD - i);
+                i--;
+                if (stop || i == 0) {
+                    ar += cr; ag += cg; ab += cb;
+                    if (stop) dy = term;
+                    k++;
+                    need_load = true;
+                }
+            }
+        }
+
+        const float fAA = (float)p.AA;
+        o.color[pix] = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+        if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
+        o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
+        o.depth_w[pix] = __fdiv_rn(dw, fAA);
+        o.hit[pix] = hit0;
+    }
+
+    // per-warp statistics flush, no block barrier
+    const unsigned gw = (blockIdx.x + blockIdx.y * gridDim.x) * (PH_THREADS >> 5) + warp;
+    unsigned long long *st = o.stats + (gw % STAT_STRIPES) * ST_COUNT;
+    const unsigned v_non = __reduce_add_sync(0xffffffffu, n_nonterm);
+    const unsigned v_term = __reduce_add_sync(0xffffffffu, n_term);
+    const unsigned v_pix = __reduce_add_sync(0xffffffffu, active ? 1u : 0u);
+    if (lane == 0 && v_pix) {
+        atomicAdd(&st[ST_SEG_NONTERMINAL], (unsigned long long)v_non);
+        atomicAdd(&st[ST_SEG_TERMINAL], (unsigned long long)v_term);
+        atomicAdd(&st[ST_RAYS_CLOSEST], (unsigned long long)(v_non + v_term));
+        atomicAdd(&st[ST_PIXELS], (unsigned long long)v_pix);
+        atomicAdd(&st[ST_PRIMARY], (unsigned long long)v_pix);
+        atomicAdd(&st[ST_JITTERED], (unsigned long long)v_pix * (unsigned)(p.AA - 1));
+    }
+}
+
+cudaError_t launch_ao_phased(const FrameParams &p, const TraceOut &o, cudaStream_t s)
+{
+    dim3 grid((p.W + PH_TILE_W - 1) / PH_TILE_W, (p.rows + PH_TILE_H - 1) / PH_TILE_H);
+    rt_ao_phased_kernel<<<grid, PH_THREADS, 0, s>>>(p, o);
+    return cudaGetLastError();
+}
+
+} // namespace rt

@@ -5,6 +5,7 @@
 // (src/main.cpp:476-480, 598-602, 613-617).  No CPU fallback: every entry point needs a CUDA device.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -32,7 +33,7 @@ struct rt_ctx {
     void *staging = nullptr; // npix * 16 bytes, layout conversions
     unsigned long long *stats = nullptr;
     unsigned *work = nullptr; // streaming AO kernel's unit counters
-    bool tile_kernel = true; // RT_AO_KERNEL=stream selects the persistent streaming kernel, =tile the tile kernel
+    int ao_kernel = AO_KERNEL_PHASED; // RT_AO_KERNEL=tile|stream selects the earlier kernels (A/B profiling)
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
     int nshapes = 0;
@@ -139,7 +140,15 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0(&c->staging, c->npix * sizeof(float4));
     alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     alloc0((void **)&c->work, 2 * sizeof(unsigned));
-    { const char *k = getenv("RT_AO_KERNEL"); if (k) c->tile_kernel = (strcmp(k, "stream") != 0); }
+    if (const char *k = getenv("RT_AO_KERNEL")) {
+        if (!strcmp(k, "tile")) c->ao_kernel = AO_KERNEL_TILE;
+        else if (!strcmp(k, "stream")) c->ao_kernel = AO_KERNEL_STREAM;
+        else if (strcmp(k, "phased")) {
+            fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected phased, tile or stream)", k);
+            free_all(c);
+            return RT_EINVAL;
+        }
+    }
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width));
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
@@ -205,6 +214,26 @@ int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
 
 static inline float3 f3(const rt_vec4 &v) { return make_float3(v.x, v.y, v.z); }
 
+// What sphere_eval_ray / plane_eval_ray (ao_compute.glsl:75-117) compute from `pos` alone, for pos = the
+// camera: one binary32 operation per shader operation, dot = multiply then fused multiply-adds (rt_math.cuh).
+// volatile keeps the host compiler from contracting or reassociating anything.
+static float4 camera_constants(const DevShape &s, float3 cam)
+{
+    if (s.id == SPHERE_ID) {
+        volatile float px = cam.x - s.s0.x, py = cam.y - s.s0.y, pz = cam.z - s.s0.z;
+        volatile float xx = px * px;
+        volatile float dd = fmaf(pz, pz, fmaf(py, py, xx));
+        return make_float4(px, py, pz, dd);
+    }
+    if (s.id == PLANE_ID) {
+        volatile float qx = s.s3.x - cam.x, qy = s.s3.y - cam.y, qz = s.s3.z - cam.z;
+        volatile float xx = s.s0.x * qx;
+        volatile float num = fmaf(s.s0.z, qz, fmaf(s.s0.y, qy, xx));
+        return make_float4(num, 0.0f, 0.0f, 0.0f);
+    }
+    return make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
 int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand_buffer)
 {
     if (!c) return RT_EINVAL;
@@ -232,6 +261,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     p.cam = f3(u->camera_location); p.light = f3(u->light_pos);
     p.bg = make_float4(u->background.x, u->background.y, u->background.z, u->background.w);
     memcpy(p.shapes, c->shapes, sizeof p.shapes);
+    for (int i = 0; i < nobj; i++) p.prim[i] = camera_constants(c->shapes[i], p.cam);
     if (rand_buffer) {
         memcpy(p.rand, rand_buffer, (size_t)c->cfg.aa * 2 * sizeof(float4));
         c->rand_last = p.rand[2 * c->cfg.aa - 1];
@@ -245,7 +275,8 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     o.depth_w = c->ring_depth_w + off;
     o.hit = c->hit;
     o.stats = c->stats;
-    o.work = c->tile_kernel ? nullptr : c->work;
+    o.work = c->work;
+    o.ao_kernel = c->ao_kernel;
     if (c->timing) CU(c, cudaEventRecord(c->ev[0], c->stream));
     CU(c, launch_trace(p, o, c->stream));
     if (c->timing) { CU(c, cudaEventRecord(c->ev[1], c->stream)); c->ev_trace_valid = true; }

@@ -188,9 +188,8 @@ __device__ __forceinline__ bool shadow_ray(const FrameParams &p, float3 pos)
     float len = length3(lv);
     float3 new_pos = add3(pos, scale3(0.01f, l));
     bool lit = true;
-#pragma unroll
-    for (int i = 0; i < RT_MAX_SHAPES; i++) {
-        if (i >= p.nshapes) break;
+#pragma unroll 1
+    for (int i = 0; i < p.nshapes; i++) {
         double t = (double)eval_ray(p.shapes[i], new_pos, l);
         if (lit && t > (double)0.0001f) {
             double ln = dlength3(__dmul_rn(t, (double)l.x), __dmul_rn(t, (double)l.y), __dmul_rn(t, (double)l.z));
@@ -318,7 +317,8 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
     dim3 grid((p.W + TILE_W - 1) / TILE_W, (p.rows + TILE_H - 1) / TILE_H);
     dim3 block(TRACE_THREADS);
     if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO) {
-        if (o.work) return launch_ao_stream(p, o, s); // persistent streaming kernel (rt_ao_stream.cu)
+        if (o.ao_kernel == AO_KERNEL_PHASED) return launch_ao_phased(p, o, s);  // default (rt_ao_phased.cu)
+        if (o.ao_kernel == AO_KERNEL_STREAM) return launch_ao_stream(p, o, s);  // persistent ray queue (rt_ao_stream.cu)
         rt_ao_trace_kernel<<<grid, block, 0, s>>>(p, o); // first-generation tile kernel, kept for A/B profiling
     }
     else if (p.mode == RT_MODE_PHONG)
@@ -619,7 +619,7 @@ __global__ void rt_eval_math_kernel(int kind, const float *a, const float *b, fl
     else if (kind == 3) out[i] = inv_sqrt_ieee(a[i]);   // must equal 1.0f / sqrtf(a)
     else {                                               // must equal sqrtf(a) for a > 0
         float im = sqrt_fast(a[i]);
-        if (!sqrt_fast_ok(a[i])) im = (a[i] > 0.0f) ? __fsqrt_rn(a[i]) : 0.0f;
+        if (!sqrt_fast_ok(a[i])) im = sqrt_slow(a[i]);
         out[i] = im;
     }
 }

@@ -37,6 +37,9 @@ struct FrameParams {
     float3 llc, horiz, vert, cam, light;
     float4 bg;
     DevShape shapes[RT_MAX_SHAPES];
+    // camera-ray constants per shape, formed by rt_render_frame with the shader's operation order:
+    // sphere (cam - centre, dot(cam - centre, cam - centre)); plane (dot(n, p0 - cam), 0, 0, 0)
+    float4 prim[RT_MAX_SHAPES];
     float4 rand[2 * RT_MAX_AA];
 };
 
@@ -58,6 +61,8 @@ enum StatIdx {
     ST_COUNT
 };
 
+enum { AO_KERNEL_PHASED = 0, AO_KERNEL_TILE = 1, AO_KERNEL_STREAM = 2 };
+
 // output planes of one trace dispatch; all row-major [rows][W] of this band
 struct TraceOut {
     float4 *color;    // ring colour plane of the slot, or the raw plane in mode 1
@@ -67,6 +72,7 @@ struct TraceOut {
     int *hit;         // hit-index plane
     unsigned long long *stats; // [STAT_STRIPES][ST_COUNT]
     unsigned *work;   // [2] unit counter + finished-warp counter of the streaming AO kernel (self re-arming)
+    int ao_kernel;    // AO_KERNEL_*
 };
 
 // a halo record row: three consecutive arrays of W elements
@@ -104,6 +110,7 @@ struct PostParams {
 // launchers (rt_kernels.cu)
 cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream_t s);
+cudaError_t launch_ao_phased(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s);
 cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s);
 cudaError_t launch_transpose(const void *src, void *dst, int W, int rows, int elem_bytes, bool to_reference, cudaStream_t s);

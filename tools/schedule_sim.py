@@ -1,0 +1,71 @@
+"""Analysis aid (not product, not test): per-(pixel, sample) AO path lengths from the CPU oracle, and
+the lane utilisation different GPU schedules of the same work would reach.  Feeds DESIGN.md section 5."""
+import ctypes as C
+import sys, os
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import oracle as orc
+from bench import Frames
+
+def pathlens(workload="config2_ao_1080p", scale=1):
+    fr = Frames(workload)
+    W, H, AA = fr.W // scale, fr.H // scale, fr.AA
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(fr.shapes, fr.n)
+    buf = np.zeros((H, W, AA), np.uint8)
+    o.L.rto_set_pathlen_buffer.argtypes = [C.c_void_p, C.c_void_p]
+    o.L.rto_set_pathlen_buffer(o.h, buf.ctypes.data_as(C.c_void_p))
+    slot, u, rb = fr.next()
+    o.render(fr.mode if fr.mode in (1, 2) else 2, u, rb)
+    o.L.rto_set_pathlen_buffer(o.h, None)
+    return buf
+
+def tiles(buf, tw=8, th=4):
+    H, W, AA = buf.shape
+    Hc, Wc = H // th * th, W // tw * tw
+    b = buf[:Hc, :Wc].reshape(Hc // th, th, Wc // tw, tw, AA).transpose(0, 2, 1, 3, 4)
+    return b.reshape(-1, th * tw, AA)   # [warp][lane][aa]
+
+if __name__ == "__main__":
+    wl = sys.argv[1] if len(sys.argv) > 1 else "config2_ao_1080p"
+    scale = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+    buf = pathlens(wl, scale)
+    L = buf.astype(np.int64)
+    print("pixels", L.shape, "mean segs/sample", L.mean(), "hist", np.bincount(L.ravel(), minlength=21))
+    t = tiles(L)                      # [warp][32][AA]
+    nw = t.shape[0]
+    total = t.sum()
+    # A: flattened per-lane loop: warp iterations = max over lanes of the lane's total
+    itA = t.sum(2).max(1)
+    print("A flattened per-lane: lane util %.3f  (iters/warp mean %.1f)" % (total / (itA.sum() * 32), itA.mean()))
+    # A': same but the primary segment of every sample done converged (4 iterations), bounces flattened
+    bn = t - 1
+    itB = bn.sum(2).max(1)
+    print("B primary converged + per-lane bounces: bounce util %.3f (bounce iters/warp %.1f, primary 4)" % (bn.sum() / max(1, itB.sum() * 32), itB.mean()))
+    # C: primary converged + per-warp task pulling (greedy list scheduling of the tile's bounce paths on 32 lanes)
+    def greedy(tasks, lanes=32):
+        tasks = [x for x in tasks if x > 0]
+        if not tasks: return 0
+        load = np.zeros(lanes, np.int64)
+        for x in tasks:            # tasks taken in order by the first free lane
+            k = load.argmin(); load[k] += x
+        return load.max()
+    sel = np.random.default_rng(0).choice(nw, size=min(nw, 4000), replace=False)
+    itC = np.array([greedy(bn[w].ravel()) for w in sel])
+    print("C primary converged + warp task pulling: bounce util %.3f (iters/warp %.1f)" % (bn[sel].sum() / max(1, itC.sum() * 32), itC.mean()))
+    # D: block-level pulling (4 warps = 128 lanes share 512 tasks)
+    nb = len(sel) // 4 * 4
+    bb = bn[sel[:nb]].reshape(nb // 4, -1)
+    itD = np.array([greedy(r, 128) for r in bb])
+    print("D block task pulling (128 lanes): bounce util %.3f" % (bb.sum() / max(1, itD.sum() * 128)))
+    print("bounce segs per pixel %.2f ; fraction of samples with bounces %.3f" % (bn.sum() / (t.shape[0] * 32), (bn > 0).mean()))
+    # E: first S segments of every sample in sample-synchronous order (warp executes segment s of sample k if ANY lane
+    # needs it), the rest flattened per lane
+    for S in (1, 2, 3, 4, 20):
+        sync_iters = sum(((t >= s).any(1)).sum() for s in range(1, S + 1))      # over warps and samples
+        sync_work = sum((t >= s).sum() for s in range(1, S + 1))
+        rest = np.maximum(t - S, 0)
+        rest_iters = rest.sum(2).max(1).sum()
+        print("E S=%d: sync util %.3f (iters/warp %.2f), rest util %.3f (iters/warp %.2f), overall %.3f" % (
+            S, sync_work / (sync_iters * 32), sync_iters / nw, rest.sum() / max(1, rest_iters * 32), rest_iters / nw,
+            total / ((sync_iters + rest_iters) * 32)))
