@@ -13,6 +13,8 @@
 //         memory; each lane then walks its own survivors in sample order in ONE flattened loop whose body
 //         is bounce + closest hit + classify, adding the finished samples of the head on the way so the
 //         colour sum keeps the shader's order  ((s0 + s1) + s2) + s3.
+//   Head and tail are iterations of ONE loop (a warp-uniform `it < nch` selects the front part), so the
+//   bounce and the general closest hit appear once in the instruction stream.
 //
 // The first-generation kernel (rt_ao_trace_kernel, one flattened loop over everything) ran all of that in
 // one loop body: lanes out of phase made the warp execute camera-ray setup, random vector, both bounce
@@ -27,7 +29,7 @@ constexpr int PH_TILE_W = 16, PH_TILE_H = 8, PH_THREADS = 128;
 constexpr int AO_CHUNK = 4;     // samples whose state is parked in shared memory at a time
 constexpr int ST_FIELDS = 8;    // survivor: dir.xyz, t, ids, ru.xyz   finished: colour.rgb, terminal depth
 
-__global__ void __launch_bounds__(PH_THREADS) rt_ao_phased_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(PH_THREADS, 8) rt_ao_phased_kernel(const __grid_constant__ FrameParams p, TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     __shared__ float4 s_rand[2 * RT_MAX_AA];
@@ -59,142 +61,130 @@ __global__ void __launch_bounds__(PH_THREADS) rt_ao_phased_kernel(const __grid_c
 
         for (int c0 = 0; c0 < p.AA; c0 += AO_CHUNK) {
             const int nch = min(AO_CHUNK, p.AA - c0);
-            unsigned pending = 0;
-
-            // ---------------------------------------------------------------- HEAD (sample-synchronous)
-#pragma unroll 1
-            for (int k = 0; k < nch; k++) {
-                const int aa = c0 + k;
-                const float4 rf = s_rand[2 * aa], rs = s_rand[2 * aa + 1];
-                float hp, vp;
-                if (aa == 0) {
-                    hp = div_const(fx, p.fW, p.invW);
-                    vp = div_const(fy, p.fH, p.invH);
-                } else {
-                    // ao_compute.glsl:310-323, seeds cross-wired exactly as written there
-                    float s1x = rs.x, s1y = rf.y, s2x = rf.z, s2y = rs.w;
-                    float s3x = rf.x, s3y = rs.y, s4x = rs.z, s4y = rf.w;
-                    float ax = ((s1x + fx * s2x) - fx) + s3x;
-                    float ay = ((s1y + fy * s2y) - fy) + s3y;
-                    float bx = s4x * fx - (s3x * fx) * s2x;
-                    float by = s4y * fy - (s3y * fy) * s2y;
-                    float r1 = random2(ax, ay), r2 = random2(bx, by);
-                    float inv = inv_sqrt_ieee(dot2(r1, r2, r1, r2));
-                    float jx = div_const(r1 * inv, 6.0f, RT_INV6) - 0.08333f;
-                    float jy = div_const(r2 * inv, 6.0f, RT_INV6) - 0.08333f;
-                    hp = div_const(fx + jx, p.fW, p.invW);
-                    vp = div_const(fy + jy, p.fH, p.invH);
-                }
-                float3 dir = primary_dir(p, hp, vp);
-                float t;
-                int ind = closest_hit_primary(p, dir, 0.0001f, t);
-                const bool first = (aa == 0);
-                if (first) hit0 = ind;
-
-                // finished-sample record: colour and RD - i of the terminating segment (-1: ran out of depth)
-                float f_r = p.bg.x, f_g = p.bg.y, f_b = p.bg.z, f_term = 0.0f;
-                bool bounce = false;
-                if (ind >= 0) {
-                    const DevShape &s = s_shapes[ind];
-                    if (s.emissive > 0.9f) {
-                        f_r = s.col.x; f_g = s.col.y; f_b = s.col.z;
-                        if (first) {
-                            // the shader returns before touching normals/depth: the slot keeps what an
-                            // earlier frame left there (ao_compute.glsl:199-208 precede :222-229)
-                            keep_normal = true;
-                            dx = o.depth_xy[pix].x;
-                            dw = o.depth_w[pix];
-                        }
-                    } else {
-                        bounce = true;
-                    }
-                }
-                if (!bounce) n_term++; else n_nonterm++;
-
-                if (bounce) {
-                    const DevShape &s = s_shapes[ind];
-                    const float3 ru = get_pt_within_unit_sphere(rf, rs, fx, fy);
-                    float3 pos, normal;
-                    ao_bounce(p, s, t, ru, dir, pos, normal);
-                    if (first) { nrm = normal; nrm_w = 1.0f; dx = t; dw = 1.0f; }
-                    f_r = s.col.x; f_g = s.col.y; f_b = s.col.z;    // 1 * a0 == a0
-                    f_term = -1.0f;
-                    if (RD > 1) {
-                        // ---- second segment
-                        float t2;
-                        const int ind2 = closest_hit(p, pos, dir, 0.0001f, t2);
-                        if (ind2 < 0) {
-                            f_r *= p.bg.x; f_g *= p.bg.y; f_b *= p.bg.z;
-                            f_term = 1.0f;
-                            n_term++;
-                        } else {
-                            const DevShape &s2 = s_shapes[ind2];
-                            if (s2.emissive > 0.9f) {
-                                f_r *= s2.col.x; f_g *= s2.col.y; f_b *= s2.col.z;
-                                f_term = 1.0f;
-                                n_term++;
-                            } else {
-                                n_nonterm++;
-                                if (RD > 2) {
-                                    // survivor: the tail re-forms its colour from the two ids
-                                    pending |= 1u << k;
-                                    s_state[k][0][tid] = dir.x; s_state[k][1][tid] = dir.y; s_state[k][2][tid] = dir.z;
-                                    s_state[k][3][tid] = t2;
-                                    s_state[k][4][tid] = __int_as_float(ind | (ind2 << 8));
-                                    s_state[k][5][tid] = ru.x; s_state[k][6][tid] = ru.y; s_state[k][7][tid] = ru.z;
-                                } else {
-                                    f_r *= s2.col.x; f_g *= s2.col.y; f_b *= s2.col.z;
-                                }
-                            }
-                        }
-                    }
-                }   // a miss on the first segment leaves normal = 0, depth = (0, 0, 0, 0): the initial values
-                if (!((pending >> k) & 1u)) {
-                    s_state[k][0][tid] = f_r; s_state[k][1][tid] = f_g; s_state[k][2][tid] = f_b;
-                    s_state[k][3][tid] = f_term;
-                }
-            }
-
-            // ---------------------------------------------------------------- TAIL (flattened per lane)
-            int k = 0, i = 0, ind = -1;
+            unsigned pending = 0;       // samples of this chunk parked in shared memory as survivors
+            int k = 0;                  // tail cursor: next sample of the chunk to add to the colour sum
             bool need_load = true;
             float3 dir = p.cam, ru = p.cam;
             float t = 0.0f, cr = 0.0f, cg = 0.0f, cb = 0.0f;
-            for (;;) {
-                if (need_load) {
-                    while (k < nch && !((pending >> k) & 1u)) {
-                        ar += s_state[k][0][tid]; ag += s_state[k][1][tid]; ab += s_state[k][2][tid];
-                        const float ft = s_state[k][3][tid];
-                        if (ft >= 0.0f) dy = ft;
-                        k++;
+            int ind = -1, i = 0;
+
+            // ONE loop for head and tail so that the bounce and the general closest hit exist once in the
+            // instruction stream (the kernel has to stay inside the 32 KB instruction cache).  `it < nch` is
+            // warp-uniform: iterations 0 .. nch-1 are the head of sample c0 + it, the rest is the tail.
+#pragma unroll 1
+            for (int it = 0;; it++) {
+                const bool head = it < nch;
+                bool live, first = false;
+                int ind0 = -1;
+                if (head) {
+                    // ------------------------------------------------ camera ray of sample aa, converged
+                    const int aa = c0 + it;
+                    const float4 rf = s_rand[2 * aa], rs = s_rand[2 * aa + 1];
+                    float hp, vp;
+                    if (aa == 0) {
+                        hp = div_const(fx, p.fW, p.invW);
+                        vp = div_const(fy, p.fH, p.invH);
+                    } else {
+                        // ao_compute.glsl:310-323, seeds cross-wired exactly as written there
+                        float s1x = rs.x, s1y = rf.y, s2x = rf.z, s2y = rs.w;
+                        float s3x = rf.x, s3y = rs.y, s4x = rs.z, s4y = rf.w;
+                        float ax = ((s1x + fx * s2x) - fx) + s3x;
+                        float ay = ((s1y + fy * s2y) - fy) + s3y;
+                        float bx = s4x * fx - (s3x * fx) * s2x;
+                        float by = s4y * fy - (s3y * fy) * s2y;
+                        float r1 = random2(ax, ay), r2 = random2(bx, by);
+                        float inv = inv_sqrt_ieee(dot2(r1, r2, r1, r2));
+                        float jx = div_const(r1 * inv, 6.0f, RT_INV6) - 0.08333f;
+                        float jy = div_const(r2 * inv, 6.0f, RT_INV6) - 0.08333f;
+                        hp = div_const(fx + jx, p.fW, p.invW);
+                        vp = div_const(fy + jy, p.fH, p.invH);
                     }
-                    if (k >= nch) break;
-                    dir = mk3(s_state[k][0][tid], s_state[k][1][tid], s_state[k][2][tid]);
-                    t = s_state[k][3][tid];
-                    const int ids = __float_as_int(s_state[k][4][tid]);
-                    ru = mk3(s_state[k][5][tid], s_state[k][6][tid], s_state[k][7][tid]);
-                    ind = ids >> 8;
-                    const DevShape &a = s_shapes[ids & 0xff], &b = s_shapes[ind];
-                    cr = a.col.x * b.col.x; cg = a.col.y * b.col.y; cb = a.col.z * b.col.z;
-                    i = RD - 2;
-                    need_load = false;
+                    dir = primary_dir(p, hp, vp);
+                    ind = closest_hit_primary(p, dir, 0.0001f, t);
+                    first = (aa == 0);
+                    if (first) hit0 = ind;
+                    cr = p.bg.x; cg = p.bg.y; cb = p.bg.z;      // 1 * a0 == a0
+                    live = false;
+                    if (ind >= 0) {
+                        const DevShape &s = s_shapes[ind];
+                        cr = s.col.x; cg = s.col.y; cb = s.col.z;
+                        if (s.emissive > 0.9f) {
+                            if (first) {
+                                // the shader returns before touching normals/depth: the slot keeps what an
+                                // earlier frame left there (ao_compute.glsl:199-208 precede :222-229)
+                                keep_normal = true;
+                                dx = o.depth_xy[pix].x;
+                                dw = o.depth_w[pix];
+                            }
+                        } else {
+                            live = true;
+                            ru = get_pt_within_unit_sphere(rf, rs, fx, fy);
+                        }
+                    }
+                    if (live) n_nonterm++; else n_term++;
+                    i = RD - 1;
+                    ind0 = ind;
+                } else {
+                    // ------------------------------------------------ tail: next survivor of this lane
+                    if (need_load) {
+                        while (k < nch && !((pending >> k) & 1u)) {
+                            ar += s_state[k][0][tid]; ag += s_state[k][1][tid]; ab += s_state[k][2][tid];
+                            const float ft = s_state[k][3][tid];
+                            if (ft >= 0.0f) dy = ft;
+                            k++;
+                        }
+                        if (k >= nch) break;
+                        dir = mk3(s_state[k][0][tid], s_state[k][1][tid], s_state[k][2][tid]);
+                        t = s_state[k][3][tid];
+                        const int ids = __float_as_int(s_state[k][4][tid]);
+                        ru = mk3(s_state[k][5][tid], s_state[k][6][tid], s_state[k][7][tid]);
+                        ind = ids >> 8;
+                        const DevShape &a = s_shapes[ids & 0xff], &b = s_shapes[ind];
+                        cr = a.col.x * b.col.x; cg = a.col.y * b.col.y; cb = a.col.z * b.col.z;
+                        i = RD - 2;
+                        need_load = false;
+                    }
+                    live = true;
                 }
-                // one path segment: bounce off (ind, t), closest hit, classify (ao_compute.glsl:161-261)
-                float3 pos, normal;
-                ao_bounce(p, s_shapes[ind], t, ru, dir, pos, normal);
-                ind = closest_hit(p, pos, dir, 0.0001f, t);
-                bool stop = true;
-                float a0r = p.bg.x, a0g = p.bg.y, a0b = p.bg.z;
-                if (ind >= 0) {
-                    const DevShape &s = s_shapes[ind];
-                    a0r = s.col.x; a0g = s.col.y; a0b = s.col.z;
-                    stop = s.emissive > 0.9f;
+
+                // ---------------------------------------------------- bounce off (ind, t), trace, classify:
+                // the body of ambient_occlusion_helper, ao_compute.glsl:161-261
+                bool done = true, stop = !live;   // a dead head lane: the camera ray ended the sample
+                float term = 0.0f;                // RECURSION_DEPTH - i of the terminating segment
+                if (live) {
+                    float3 pos, normal;
+                    ao_bounce(p, s_shapes[ind], t, ru, dir, pos, normal);
+                    if (first) { nrm = normal; nrm_w = 1.0f; dx = t; dw = 1.0f; }
+                    if (i > 0) {                  // false only for recursion_depth == 1
+                        ind = closest_hit(p, pos, dir, 0.0001f, t);
+                        stop = true;
+                        float a0r = p.bg.x, a0g = p.bg.y, a0b = p.bg.z;
+                        if (ind >= 0) {
+                            const DevShape &s = s_shapes[ind];
+                            a0r = s.col.x; a0g = s.col.y; a0b = s.col.z;
+                            stop = s.emissive > 0.9f;
+                        }
+                        cr *= a0r; cg *= a0g; cb *= a0b;
+                        if (stop) n_term++; else n_nonterm++;
+                        term = (float)(RD - i);
+                        i--;
+                        done = stop || i == 0;
+                    }
                 }
-                cr *= a0r; cg *= a0g; cb *= a0b;
-                if (stop) n_term++; else n_nonterm++;
-                const float term = (float)(RD - i);
-                i--;
-                if (stop || i == 0) {
+                if (head) {
+                    if (done) {
+                        // finished in the head: parked so the tail adds it in sample order
+                        s_state[it][0][tid] = cr; s_state[it][1][tid] = cg; s_state[it][2][tid] = cb;
+                        s_state[it][3][tid] = stop ? term : -1.0f;
+                    } else {
+                        // survivor of two segments; the tail re-forms its colour from the two hit ids
+                        pending |= 1u << it;
+                        s_state[it][0][tid] = dir.x; s_state[it][1][tid] = dir.y; s_state[it][2][tid] = dir.z;
+                        s_state[it][3][tid] = t;
+                        s_state[it][4][tid] = __int_as_float(ind0 | (ind << 8));
+                        s_state[it][5][tid] = ru.x; s_state[it][6][tid] = ru.y; s_state[it][7][tid] = ru.z;
+                    }
+                } else if (done) {
                     ar += cr; ag += cg; ab += cb;
                     if (stop) dy = term;
                     k++;

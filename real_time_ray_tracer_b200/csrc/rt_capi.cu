@@ -214,24 +214,32 @@ int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
 
 static inline float3 f3(const rt_vec4 &v) { return make_float3(v.x, v.y, v.z); }
 
-// What sphere_eval_ray / plane_eval_ray (ao_compute.glsl:75-117) compute from `pos` alone, for pos = the
-// camera: one binary32 operation per shader operation, dot = multiply then fused multiply-adds (rt_math.cuh).
+// Splits the scene table into the traversal lists of FrameParams.  The camera constants are what
+// sphere_eval_ray / plane_eval_ray (ao_compute.glsl:75-117) compute from `pos` alone, for pos = the camera:
+// one binary32 operation per shader operation, dot = multiply then fused multiply-adds (rt_math.cuh).
 // volatile keeps the host compiler from contracting or reassociating anything.
-static float4 camera_constants(const DevShape &s, float3 cam)
+static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n)
 {
-    if (s.id == SPHERE_ID) {
-        volatile float px = cam.x - s.s0.x, py = cam.y - s.s0.y, pz = cam.z - s.s0.z;
-        volatile float xx = px * px;
-        volatile float dd = fmaf(pz, pz, fmaf(py, py, xx));
-        return make_float4(px, py, pz, dd);
+    p.nsph = p.npl = 0;
+    const float3 cam = p.cam;
+    for (int i = 0; i < n; i++) {
+        const DevShape &s = shapes[i];
+        if (s.id == SPHERE_ID) {
+            volatile float px = cam.x - s.s0.x, py = cam.y - s.s0.y, pz = cam.z - s.s0.z;
+            volatile float xx = px * px;
+            volatile float dd = fmaf(pz, pz, fmaf(py, py, xx));
+            p.sph[p.nsph] = make_float4(s.s0.x, s.s0.y, s.s0.z, s.r2);
+            p.sph_cam[p.nsph] = make_float4(px, py, pz, dd);
+            p.sph_idx[p.nsph++] = i;
+        } else if (s.id == PLANE_ID) {
+            volatile float qx = s.s3.x - cam.x, qy = s.s3.y - cam.y, qz = s.s3.z - cam.z;
+            volatile float xx = s.s0.x * qx;
+            volatile float num = fmaf(s.s0.z, qz, fmaf(s.s0.y, qy, xx));
+            p.pl_n[p.npl] = make_float4(s.s0.x, s.s0.y, s.s0.z, num);
+            p.pl_p0[p.npl] = make_float4(s.s3.x, s.s3.y, s.s3.z, 0.0f);
+            p.pl_idx[p.npl++] = i;
+        } // any other id (rectangle = 3) is never intersected: ao_compute.glsl:130-135
     }
-    if (s.id == PLANE_ID) {
-        volatile float qx = s.s3.x - cam.x, qy = s.s3.y - cam.y, qz = s.s3.z - cam.z;
-        volatile float xx = s.s0.x * qx;
-        volatile float num = fmaf(s.s0.z, qz, fmaf(s.s0.y, qy, xx));
-        return make_float4(num, 0.0f, 0.0f, 0.0f);
-    }
-    return make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
 int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand_buffer)
@@ -261,7 +269,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     p.cam = f3(u->camera_location); p.light = f3(u->light_pos);
     p.bg = make_float4(u->background.x, u->background.y, u->background.z, u->background.w);
     memcpy(p.shapes, c->shapes, sizeof p.shapes);
-    for (int i = 0; i < nobj; i++) p.prim[i] = camera_constants(c->shapes[i], p.cam);
+    build_traversal_tables(p, c->shapes, nobj);
     if (rand_buffer) {
         memcpy(p.rand, rand_buffer, (size_t)c->cfg.aa * 2 * sizeof(float4));
         c->rand_last = p.rand[2 * c->cfg.aa - 1];

@@ -37,9 +37,17 @@ struct FrameParams {
     float3 llc, horiz, vert, cam, light;
     float4 bg;
     DevShape shapes[RT_MAX_SHAPES];
-    // camera-ray constants per shape, formed by rt_render_frame with the shader's operation order:
-    // sphere (cam - centre, dot(cam - centre, cam - centre)); plane (dot(n, p0 - cam), 0, 0, 0)
-    float4 prim[RT_MAX_SHAPES];
+    // Traversal tables, rebuilt per frame by rt_render_frame from shapes[0 .. nshapes): spheres and planes
+    // in separate lists (each keeps its position in the scene as *_idx, which decides ties exactly like the
+    // shader's in-order `res_t < t`), plus what the intersection tests compute from `pos` alone when pos is
+    // the camera (formed on the host with the shader's operation order).
+    int nsph, npl, pad1, pad2;
+    float4 sph[RT_MAX_SHAPES];     // centre.xyz, radius * radius
+    float4 sph_cam[RT_MAX_SHAPES]; // cam - centre, dot(cam - centre, cam - centre)
+    float4 pl_n[RT_MAX_SHAPES];    // normal.xyz, dot(normal, p0 - cam)
+    float4 pl_p0[RT_MAX_SHAPES];   // p0.xyz, 0
+    int sph_idx[RT_MAX_SHAPES];
+    int pl_idx[RT_MAX_SHAPES];
     float4 rand[2 * RT_MAX_AA];
 };
 

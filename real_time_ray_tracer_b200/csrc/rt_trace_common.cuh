@@ -52,55 +52,89 @@ __device__ __forceinline__ float eval_ray(const DevShape &s, float3 pos, float3 
     return -1.0f;
 }
 
-// closest hit over the object table, read from the constant bank with warp-uniform indices
-// (ao_compute.glsl:183-194 / p_compute.glsl:177-188 / h_compute.glsl:199-210)
-__device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, float3 dir, float tmin, float &t_out)
+// ---------------------------------------------------------------------------------------------
+// closest hit (ao_compute.glsl:183-194 / p_compute.glsl:177-188 / h_compute.glsl:199-210)
+// ---------------------------------------------------------------------------------------------
+// The shader walks simple_shapes in order and keeps `res_t > tmin && (res_t < t || t < 0)`.  Candidates are
+// positive, so they order like unsigned integers and "no hit yet" is the all-ones pattern.  Here spheres and
+// planes are walked as two lists (FrameParams); the result is the same for every input because a candidate
+// replaces the current one when it is nearer, or equally near and EARLIER in the scene -- which is what the
+// in-order strict `<` decides.  Within a list the order is the scene's, so the index test is only needed
+// where the lists interleave (the plane list, walked second).
+//
+// The sphere list is unrolled: its operands are then immediate constant-bank addresses (no loads, no
+// induction variables, no id dispatch), 16 instructions per miss.  The ncu runs behind this: the fully
+// generic unrolled loop (both tests, ten times, per call site) overflowed the instruction cache
+// (sm__icc_request_hit_rate 64 %); the rolled loop fixed that but spent 23 instructions per sphere, five of
+// them indexed constant loads on the ADU pipe (44 % busy).
+struct Closest { unsigned tb; int ind; };
+
+__device__ __forceinline__ void sphere_candidate(float b, float del, int idx, float tmin, Closest &c)
 {
-    // `res_t > tmin && (res_t < t || t < 0)` with t starting at -1: candidates are positive, so they order
-    // like unsigned integers and "no hit yet" can be the all-ones pattern (above +inf, like the shader's t < 0)
-    unsigned tb = 0xffffffffu;
-    int ind = -1;
-    // NOT unrolled: ncu on the unrolled build showed the kernels fetch-bound (sm__icc_request_hit_rate 64 %,
-    // GPC instruction-cache requests at 93 % of peak) -- ten copies of both intersection tests per call site
-    // do not fit the 32 KB L1.5 instruction cache
-#pragma unroll 1
-    for (int i = 0; i < p.nshapes; i++) {
-        float res_t = eval_ray(p.shapes[i], pos, dir);
-        if (res_t > tmin && __float_as_uint(res_t) < tb) {
-            tb = __float_as_uint(res_t);
-            ind = i;
+    if (del >= 0.0f) {
+        float im = sqrt_fast(del);
+        if (!sqrt_fast_ok(del)) im = sqrt_slow(del); // 0, subnormal, +inf
+        const float t1 = -b + im;
+        const float t2 = -b - im;
+        // sphere_eval_ray's `t2 >= 0 ? t2 : (t1 >= 0 ? t1 : -1)`; a negative t1 fails `> tmin` like the -1 does
+        const float res_t = (t2 < 0.0f) ? t1 : t2;
+        if (res_t > tmin && __float_as_uint(res_t) < c.tb) {
+            c.tb = __float_as_uint(res_t);
+            c.ind = idx;
         }
     }
-    t_out = (ind < 0) ? -1.0f : __uint_as_float(tb);
-    return ind;
 }
 
-// The same loop for rays that leave the camera: `pos - centre`, its squared length and the plane numerator
-// dot(n, p0 - pos) do not depend on the pixel, so rt_render_frame forms them once per frame with the
-// shader's operation order (FrameParams::prim) and the per-pixel test starts at `b = dot(dir, pmc)`.
+__device__ __forceinline__ void plane_candidate(float num, float denom, int idx, float tmin, Closest &c)
+{
+    if (denom < 0.001f && denom > -0.001f) return;
+    const float res_t = __fdiv_rn(num, denom);
+    const unsigned bits = __float_as_uint(res_t);
+    if (res_t > tmin && (bits < c.tb || (bits == c.tb && idx < c.ind))) {
+        c.tb = bits;
+        c.ind = idx;
+    }
+}
+
+__device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, float3 dir, float tmin, float &t_out)
+{
+    Closest c = { 0xffffffffu, -1 };
+#pragma unroll
+    for (int i = 0; i < RT_MAX_SHAPES; i++) {
+        if (i >= p.nsph) break;
+        const float4 s = p.sph[i];
+        const float3 pmc = sub3(pos, xyz(s));
+        const float b = dot3(dir, pmc);
+        sphere_candidate(b, b * b - dot3(pmc, pmc) + s.w, p.sph_idx[i], tmin, c);
+    }
+#pragma unroll 1
+    for (int j = 0; j < p.npl; j++) {
+        const float3 n = xyz(p.pl_n[j]);
+        plane_candidate(dot3(n, sub3(xyz(p.pl_p0[j]), pos)), dot3(n, dir), p.pl_idx[j], tmin, c);
+    }
+    t_out = (c.ind < 0) ? -1.0f : __uint_as_float(c.tb);
+    return c.ind;
+}
+
+// The same for rays that leave the camera: `pos - centre`, its squared length and the plane numerator
+// dot(n, p0 - pos) do not depend on the pixel (FrameParams::sph_cam, pl_n.w).
 __device__ __forceinline__ int closest_hit_primary(const FrameParams &p, float3 dir, float tmin, float &t_out)
 {
-    unsigned tb = 0xffffffffu;
-    int ind = -1;
-#pragma unroll 1
-    for (int i = 0; i < p.nshapes; i++) {
-        const DevShape &s = p.shapes[i];
-        const float4 c = p.prim[i];
-        float res_t = -1.0f;
-        if (s.id == SPHERE_ID) {
-            float b = dot3(dir, xyz(c));
-            res_t = sphere_roots(b, b * b - c.w + s.r2);
-        } else if (s.id == PLANE_ID) {
-            float denom = dot3(xyz(s.s0), dir);
-            if (!(denom < 0.001f && denom > -0.001f)) res_t = __fdiv_rn(c.x, denom);
-        }
-        if (res_t > tmin && __float_as_uint(res_t) < tb) {
-            tb = __float_as_uint(res_t);
-            ind = i;
-        }
+    Closest c = { 0xffffffffu, -1 };
+#pragma unroll
+    for (int i = 0; i < RT_MAX_SHAPES; i++) {
+        if (i >= p.nsph) break;
+        const float4 k = p.sph_cam[i];
+        const float b = dot3(dir, xyz(k));
+        sphere_candidate(b, b * b - k.w + p.sph[i].w, p.sph_idx[i], tmin, c);
     }
-    t_out = (ind < 0) ? -1.0f : __uint_as_float(tb);
-    return ind;
+#pragma unroll 1
+    for (int j = 0; j < p.npl; j++) {
+        const float4 n = p.pl_n[j];
+        plane_candidate(n.w, dot3(xyz(n), dir), p.pl_idx[j], tmin, c);
+    }
+    t_out = (c.ind < 0) ? -1.0f : __uint_as_float(c.tb);
+    return c.ind;
 }
 
 __device__ __forceinline__ float3 shape_normal(const DevShape &s, float3 pt)

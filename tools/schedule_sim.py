@@ -69,3 +69,10 @@ if __name__ == "__main__":
         print("E S=%d: sync util %.3f (iters/warp %.2f), rest util %.3f (iters/warp %.2f), overall %.3f" % (
             S, sync_work / (sync_iters * 32), sync_iters / nw, rest.sum() / max(1, rest_iters * 32), rest_iters / nw,
             total / ((sync_iters + rest_iters) * 32)))
+    # F: S=2 head, tail with warp-level task stealing (any lane runs any survivor of the warp's tile)
+    rest = np.maximum(t - 2, 0)
+    sel = np.random.default_rng(1).choice(nw, size=min(nw, 6000), replace=False)
+    itF = np.array([greedy(rest[w].T.ravel()) for w in sel])      # tasks ordered by sample then lane
+    itE = rest[sel].sum(2).max(1)
+    print("F tail stealing: tail iters/warp %.2f (own-samples-only %.2f), tail util %.3f" % (
+        itF.mean(), itE.mean(), rest[sel].sum() / max(1, itF.sum() * 32)))
