@@ -181,6 +181,22 @@ int rt_download_async(rt_ctx *ctx, int buffer, int slot, void *pinned_host, size
 /* raw device pointer of a row-major plane of this band (for NCCL / framework interop) */
 int rt_device_ptr(rt_ctx *ctx, int buffer, int slot, void **out_ptr, size_t *out_bytes);
 
+/* Direct gather for row bands (replaces the final "gather to rank 0" pass; no reference counterpart: the
+ * reference renders the whole image on one GPU, src/main.cpp:604).  A frame image is float4[height][width],
+ * row-major, y = 0 at the bottom.  While a target is set, the kernel that produces a frame's final colour
+ * (the trace kernel in modes 2-4, the post-processing kernel in mode 1) stores every pixel of this band
+ * into rows [band_y0, band_y0 + band_rows) of the target as well as into the ring slot.  The target may be
+ * memory of another GPU of the box (rt_frame_import maps it over NVLink/NVSwitch with peer access), so the
+ * gather costs no extra pass: the stores travel while the band is still being computed.  The caller fences
+ * the ranks (any stream-ordered collective) before it reads the assembled frame. */
+int rt_frame_create(int device, int width, int height, void **out_frame);
+int rt_frame_destroy(int device, void *frame);
+#define RT_FRAME_HANDLE_BYTES 64
+int rt_frame_export(int device, void *frame, unsigned char handle[RT_FRAME_HANDLE_BYTES]);
+int rt_frame_import(int device, const unsigned char handle[RT_FRAME_HANDLE_BYTES], void **out_frame);
+int rt_frame_release(int device, void *imported_frame);
+int rt_set_frame_target(rt_ctx *ctx, void *frame); /* NULL = off; takes effect with the next rt_render_frame */
+
 int rt_get_stats(rt_ctx *ctx, rt_stats *out); /* synchronises */
 int rt_reset_stats(rt_ctx *ctx);
 

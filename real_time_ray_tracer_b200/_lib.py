@@ -40,6 +40,8 @@ EXPORTS = (
     "rt_synchronize", "rt_set_timing", "rt_upload_scene", "rt_render_frame", "rt_halo_pack", "rt_get_halo",
     "rt_postprocess", "rt_download", "rt_upload", "rt_download_async", "rt_device_ptr", "rt_get_stats",
     "rt_reset_stats", "rt_debug_eval_math", "rt_measure_fp32_peak",
+    "rt_set_frame_target", "rt_frame_create", "rt_frame_destroy", "rt_frame_export", "rt_frame_import",
+    "rt_frame_release",
 )
 
 _lib = None
@@ -77,5 +79,11 @@ def load():
     L.rt_reset_stats.argtypes = [vp]
     L.rt_debug_eval_math.argtypes = [i32, i32, vp, vp, vp, sz]
     L.rt_measure_fp32_peak.argtypes = [i32, C.POINTER(C.c_double)]
+    L.rt_set_frame_target.argtypes = [vp, vp]
+    L.rt_frame_create.argtypes = [i32, i32, i32, C.POINTER(vp)]
+    L.rt_frame_destroy.argtypes = [i32, vp]
+    L.rt_frame_export.argtypes = [i32, vp, C.c_char_p]
+    L.rt_frame_import.argtypes = [i32, C.c_char_p, C.POINTER(vp)]
+    L.rt_frame_release.argtypes = [i32, vp]
     _lib = L
     return L

@@ -93,6 +93,11 @@ class RayTracer:
         self._check(self.lib.rt_render_frame(self.h, lighting_mode, u.ctypes.data_as(C.c_void_p),
                                              r.ctypes.data_as(C.c_void_p) if r is not None else None))
 
+    def set_frame_target(self, frame_ptr: Optional[int]):
+        """rt_set_frame_target: following frames also store this band's final colour into the whole-frame
+        image at ``frame_ptr`` (a ``Frame``'s pointer, local or imported from another rank); None = off."""
+        self._check(self.lib.rt_set_frame_target(self.h, C.c_void_p(frame_ptr or 0)))
+
     def halo_pack(self):
         self._check(self.lib.rt_halo_pack(self.h))
 
@@ -139,6 +144,51 @@ class RayTracer:
 
     def reset_stats(self):
         self._check(self.lib.rt_reset_stats(self.h))
+
+
+class Frame:
+    """A whole-frame image float4[H][W] on one GPU that row bands of other contexts -- other processes, other
+    GPUs of the box -- write into directly (rt_frame_* in include/rt.h).  ``Frame.create`` allocates and can
+    ``export()`` a 64-byte handle; ``Frame.open`` maps such a handle in another process (peer access over
+    NVLink when the devices differ)."""
+
+    def __init__(self, ptr: int, width: int, height: int, device: int, imported: bool):
+        self.ptr, self.W, self.H, self.device, self.imported = ptr, width, height, device, imported
+        self.lib = L.load()
+
+    @staticmethod
+    def _ok(lib, rc):
+        if rc != L.RT_OK:
+            raise RtError(rc, lib.rt_last_error(None).decode())
+
+    @classmethod
+    def create(cls, width: int, height: int, device: int = 0) -> "Frame":
+        lib = L.load()
+        p = C.c_void_p()
+        cls._ok(lib, lib.rt_frame_create(device, width, height, C.byref(p)))
+        return cls(p.value, width, height, device, False)
+
+    def export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._ok(self.lib, self.lib.rt_frame_export(self.device, C.c_void_p(self.ptr), buf))
+        return buf.raw
+
+    @classmethod
+    def open(cls, handle: bytes, width: int, height: int, device: int = 0) -> "Frame":
+        lib = L.load()
+        p = C.c_void_p()
+        cls._ok(lib, lib.rt_frame_import(device, C.create_string_buffer(handle, 64), C.byref(p)))
+        return cls(p.value, width, height, device, True)
+
+    @property
+    def nbytes(self) -> int:
+        return self.W * self.H * 16
+
+    def close(self):
+        if self.ptr:
+            f = self.lib.rt_frame_release if self.imported else self.lib.rt_frame_destroy
+            f(self.device, C.c_void_p(self.ptr))
+            self.ptr = 0
 
 
 def debug_eval_math(kind: str, a, b=None, device: int = 0) -> np.ndarray:

@@ -4,7 +4,11 @@ The trace kernels need no exchange (pixels are independent).  The post-processin
 the four neighbours of the CURRENT frame (aop_postprocessing.glsl:81-171), so each band needs one record
 row from the band below and one from the band above; under the literal FLAT32 border semantics image row
 0 additionally reads image row H-1 (``[f][x][y-1]`` with y = 0 wraps), which turns the exchange into a
-ring.  Temporal history stays rank-local.  Bands are finally gathered on rank 0.
+ring.  Temporal history stays rank-local.  Bands are finally gathered on rank 0 -- either by NCCL
+point-to-point receives (``gather_start``) or, on the GPU box, by ``DirectGather``: rank 0 owns the frame
+image, the other ranks map it over NVLink (CUDA IPC + peer access) and their kernels store each pixel's
+final colour straight into it, so the gather is fused into the kernel that produces the colour and only a
+one-element all-reduce remains as the per-frame fence.
 
 The exchange is written against ``torch.distributed`` point-to-point ops, so it runs over NCCL/NVLink on
 the GPU box and over gloo in the CPU tests; the per-band engine is duck-typed (``GpuBandEngine`` here, a
@@ -86,6 +90,9 @@ class GpuBandEngine:
     def render_frame(self, mode, uniforms, rand_buffer):
         self.rt.render_frame(mode, uniforms, rand_buffer)
 
+    def set_frame_target(self, ptr):
+        self.rt.set_frame_target(ptr)
+
     def halo_pack(self):
         self.rt.halo_pack()
 
@@ -97,13 +104,60 @@ class GpuBandEngine:
         return self._color[slot]
 
 
+class DirectGather:
+    """Whole-frame images on rank 0 that every rank's kernels write their band into (rt_set_frame_target).
+
+    ``nbuf`` images alternate so that frame k can be consumed on rank 0 while frame k+1 is rendered.  Rank 0
+    allocates them (``api.Frame.create``), the 64-byte IPC handles travel through ``broadcast_object_list``,
+    and the other ranks map them with peer access.  ``fence()`` is a one-element all-reduce on the current
+    stream: when it has completed on rank 0, every rank's kernels of the frame have completed (stream order on
+    each rank), so all bands are in the image."""
+
+    def __init__(self, width: int, height: int, rank: int, world: int, device: int, nbuf: int = 2, group=None):
+        import torch
+        import torch.distributed as dist
+
+        from . import api
+
+        self.rank, self.world, self.device, self.group = rank, world, device, group
+        handles = None
+        if rank == 0:
+            self.frames = [api.Frame.create(width, height, device) for _ in range(nbuf)]
+            handles = [f.export() for f in self.frames]
+        box = [handles]
+        if world > 1:
+            dist.broadcast_object_list(box, src=0, group=group)
+        if rank != 0:
+            self.frames = [api.Frame.open(h, width, height, device) for h in box[0]]
+        self.token = torch.zeros(1, dtype=torch.float32, device=f"cuda:{device}")
+        self.tensors = [device_tensor(f.ptr, f.nbytes, device) for f in self.frames] if rank == 0 else None
+
+    def target(self, k: int) -> int:
+        return self.frames[k % len(self.frames)].ptr
+
+    def fence(self):
+        import torch.distributed as dist
+
+        if self.world > 1:
+            dist.all_reduce(self.token, group=self.group)
+
+    def frame(self, k: int):
+        """rank 0: float32 tensor [H*W*4] of the image frame k was gathered into"""
+        return self.tensors[k % len(self.tensors)] if self.rank == 0 else None
+
+    def close(self):
+        for f in self.frames:
+            f.close()
+
+
 class BandedRenderer:
     """Drives one band per rank: trace -> (mode 1: pack, ring halo exchange, post-process) -> gather."""
 
     def __init__(self, engine, width: int, height: int, bands: List[Tuple[int, int]], rank: int, world: int,
-                 group=None):
+                 group=None, direct: Optional[DirectGather] = None):
         self.e, self.W, self.H = engine, width, height
         self.bands, self.rank, self.world, self.group = bands, rank, world, group
+        self.direct, self.frame_k = direct, 0
 
     def exchange_halo(self):
         """send_hi -> recv_lo of band (r+1) % n (the last band's send_hi is the wrapped row image row 0
@@ -123,6 +177,8 @@ class BandedRenderer:
             w.wait()
 
     def render(self, mode: int, uniforms, rand_buffer):
+        if self.direct is not None:
+            self.e.set_frame_target(self.direct.target(self.frame_k))
         self.e.render_frame(mode, uniforms, rand_buffer)
         if mode == 1:
             if self.world > 1:
@@ -137,6 +193,11 @@ class BandedRenderer:
         slot is not rewritten for NF-1 frames) and calls ``gather_finish`` before it reuses ``out``."""
         import torch.distributed as dist
 
+        if self.direct is not None:
+            # the bands are already in (or on their way into) rank 0's image direct.frame(frame_k): fence only
+            self.direct.fence()
+            self.frame_k += 1
+            return []
         mine = self.e.band_color(slot)
         if self.world == 1:
             if out is not None:

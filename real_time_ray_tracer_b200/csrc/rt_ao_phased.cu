@@ -194,7 +194,9 @@ __global__ void __launch_bounds__(PH_THREADS, 8) rt_ao_phased_kernel(const __gri
         }
 
         const float fAA = (float)p.AA;
-        o.color[pix] = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+        const float4 c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+        o.color[pix] = c;
+        if (o.gather) o.gather[pix] = c;   // rt_set_frame_target: the assembled frame, maybe over NVLink
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
         o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
         o.depth_w[pix] = __fdiv_rn(dw, fAA);

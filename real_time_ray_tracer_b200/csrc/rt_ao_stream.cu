@@ -266,7 +266,8 @@ __global__ void __launch_bounds__(STREAM_THREADS) rt_ao_stream_kernel(const __gr
 }
 
 // divide by AA and gamma (ao_compute.glsl:330-335), in place, fully converged and coalesced
-__global__ void __launch_bounds__(256) rt_ao_epilogue_kernel(float4 *color, float2 *depth_xy, float *depth_w, size_t n, int AA)
+__global__ void __launch_bounds__(256) rt_ao_epilogue_kernel(float4 *color, float2 *depth_xy, float *depth_w, size_t n, int AA,
+                                                             float4 *gather)
 {
     const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
@@ -274,7 +275,9 @@ __global__ void __launch_bounds__(256) rt_ao_epilogue_kernel(float4 *color, floa
     const float4 c = color[k];
     const float2 d = depth_xy[k];
     const float w = depth_w[k];
-    color[k] = gamma_correct(__fdiv_rn(c.x, fAA), __fdiv_rn(c.y, fAA), __fdiv_rn(c.z, fAA));
+    const float4 g = gamma_correct(__fdiv_rn(c.x, fAA), __fdiv_rn(c.y, fAA), __fdiv_rn(c.z, fAA));
+    color[k] = g;
+    if (gather) gather[k] = g;
     depth_xy[k] = make_float2(__fdiv_rn(d.x, fAA), __fdiv_rn(d.y, fAA));
     depth_w[k] = __fdiv_rn(w, fAA);
 }
@@ -304,7 +307,7 @@ cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const size_t n = (size_t)p.rows * p.W;
-    rt_ao_epilogue_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(o.color, o.depth_xy, o.depth_w, n, p.AA);
+    rt_ao_epilogue_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(o.color, o.depth_xy, o.depth_w, n, p.AA, o.gather);
     return cudaGetLastError();
 }
 

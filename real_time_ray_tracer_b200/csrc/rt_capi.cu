@@ -41,6 +41,8 @@ struct rt_ctx {
     int last_mode = 0, last_slot = 0;
     bool frame_pending_post = false, halo_packed = false;
     float4 rand_last{};
+    float4 *frame_target = nullptr; // rt_set_frame_target: whole-frame image, maybe peer memory
+    float4 *frame_target_post = nullptr; // the target the pending mode-1 frame was rendered for
     bool timing = false;
     cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
     bool ev_trace_valid = false, ev_post_valid = false;
@@ -285,6 +287,10 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     o.stats = c->stats;
     o.work = c->work;
     o.ao_kernel = c->ao_kernel;
+    // mode 1: the trace output is raw; the post-processing pass writes the frame
+    float4 *band_in_frame = c->frame_target ? c->frame_target + (size_t)c->cfg.band_y0 * c->cfg.width : nullptr;
+    o.gather = (mode == RT_MODE_AO_PP) ? nullptr : band_in_frame;
+    c->frame_target_post = (mode == RT_MODE_AO_PP) ? band_in_frame : nullptr;
     if (c->timing) CU(c, cudaEventRecord(c->ev[0], c->stream));
     CU(c, launch_trace(p, o, c->stream));
     if (c->timing) { CU(c, cudaEventRecord(c->ev[1], c->stream)); c->ev_trace_valid = true; }
@@ -306,6 +312,7 @@ static void fill_post(rt_ctx *c, PostParams &q)
     q.send_lo = c->halo[0]; q.send_hi = c->halo[1];
     q.halo_lo = c->halo[2]; q.halo_hi = c->halo[3];
     q.rand_last = c->rand_last;
+    q.gather = c->frame_target_post;
     q.stats = c->stats;
 }
 
@@ -354,6 +361,81 @@ int rt_postprocess(rt_ctx *c)
     if (c->timing) { CU(c, cudaEventRecord(c->ev[3], c->stream)); c->ev_post_valid = true; }
     c->frame_pending_post = false;
     return RT_OK;
+}
+
+// ---- direct gather ---------------------------------------------------------------------------
+int rt_set_frame_target(rt_ctx *c, void *frame)
+{
+    if (!c) return RT_EINVAL;
+    c->frame_target = (float4 *)frame;
+    return RT_OK;
+}
+
+static int frame_fail(int code, const char *what, cudaError_t e)
+{
+    fail(nullptr, code, "%s: %s", what, cudaGetErrorString(e));
+    cudaGetLastError();
+    return code;
+}
+
+int rt_frame_create(int device, int width, int height, void **out_frame)
+{
+    if (!out_frame || width <= 0 || height <= 0) return fail(nullptr, RT_EINVAL, "rt_frame_create: bad argument");
+    *out_frame = nullptr;
+    if (device < 0 || device >= rt_device_count()) return fail(nullptr, RT_ENODEVICE, "rt_frame_create: device %d", device);
+    cudaError_t e = cudaSetDevice(device);
+    const size_t bytes = (size_t)width * height * sizeof(float4);
+    if (e == cudaSuccess) e = cudaMalloc(out_frame, bytes);
+    if (e == cudaSuccess) e = cudaMemset(*out_frame, 0, bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        if (*out_frame) cudaFree(*out_frame);
+        *out_frame = nullptr;
+        return frame_fail(e == cudaErrorMemoryAllocation ? RT_ENOMEM : RT_ECUDA, "rt_frame_create", e);
+    }
+    return RT_OK;
+}
+
+int rt_frame_destroy(int device, void *frame)
+{
+    if (!frame) return RT_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaFree(frame);
+    return e == cudaSuccess ? RT_OK : frame_fail(RT_ECUDA, "rt_frame_destroy", e);
+}
+
+int rt_frame_export(int device, void *frame, unsigned char handle[RT_FRAME_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_FRAME_HANDLE_BYTES, "handle size");
+    if (!frame || !handle) return fail(nullptr, RT_EINVAL, "rt_frame_export: null argument");
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, frame);
+    if (e != cudaSuccess) return frame_fail(RT_ECUDA, "rt_frame_export", e);
+    memcpy(handle, &h, sizeof h);
+    return RT_OK;
+}
+
+int rt_frame_import(int device, const unsigned char handle[RT_FRAME_HANDLE_BYTES], void **out_frame)
+{
+    if (!handle || !out_frame) return fail(nullptr, RT_EINVAL, "rt_frame_import: null argument");
+    *out_frame = nullptr;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    cudaError_t e = cudaSetDevice(device);
+    // maps the exporting process's allocation; when it lives on another GPU the runtime enables peer access
+    // (NVLink) between the two devices for this mapping
+    if (e == cudaSuccess) e = cudaIpcOpenMemHandle(out_frame, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return frame_fail(RT_ECUDA, "rt_frame_import", e);
+    return RT_OK;
+}
+
+int rt_frame_release(int device, void *imported_frame)
+{
+    if (!imported_frame) return RT_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaIpcCloseMemHandle(imported_frame);
+    return e == cudaSuccess ? RT_OK : frame_fail(RT_ECUDA, "rt_frame_release", e);
 }
 
 // ---- buffers ---------------------------------------------------------------------------------

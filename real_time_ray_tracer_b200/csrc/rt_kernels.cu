@@ -165,6 +165,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid
         const float fAA = (float)p.AA;
         float4 c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
         o.color[pix] = c;
+        if (o.gather) o.gather[pix] = c;
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
         o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
         o.depth_w[pix] = __fdiv_rn(dw, fAA);
@@ -241,7 +242,9 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_co
             col = phong_shade(p, att, curr_pos, dir, normal, lit);
         }
         // result_color = vec4(0) + phong(dir)
-        o.color[pix] = gamma_correct(0.0f + col.x, 0.0f + col.y, 0.0f + col.z);
+        const float4 c = gamma_correct(0.0f + col.x, 0.0f + col.y, 0.0f + col.z);
+        o.color[pix] = c;
+        if (o.gather) o.gather[pix] = c;
         o.hit[pix] = ind;
     }
     const int idx[5] = { ST_RAYS_CLOSEST, ST_RAYS_SHADOW, ST_SHADED, ST_PIXELS, ST_PRIMARY };
@@ -304,7 +307,9 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_c
             }
             if (stop) break;
         }
-        o.color[pix] = gamma_correct(0.0f + result.x, 0.0f + result.y, 0.0f + result.z);
+        const float4 c = gamma_correct(0.0f + result.x, 0.0f + result.y, 0.0f + result.z);
+        o.color[pix] = c;
+        if (o.gather) o.gather[pix] = c;
         o.hit[pix] = first_ind;
     }
     const int idx[6] = { ST_RAYS_CLOSEST, ST_RAYS_SHADOW, ST_SHADED, ST_REFLECTIVE, ST_PIXELS, ST_PRIMARY };
@@ -512,6 +517,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, 8) rt_ao_postprocess_k
             color = div4(add4(scale4(0.9f, color), color_sum), denominator);
         }
         q.ring_color[(size_t)q.slot * plane + pix] = color; // pixels[new_frame] and img_output
+        if (q.gather) q.gather[pix] = color;                // rt_set_frame_target: the assembled frame, maybe over NVLink
     }
     // per-warp flush, no block barrier: a warp of background pixels must not wait for its block-mates
     const int idx[3] = { ST_PP_NONBACKGROUND, ST_PP_HIST_EVALUATED, ST_PP_HIST_ACCEPTED };

@@ -81,6 +81,7 @@ struct TraceOut {
     unsigned long long *stats; // [STAT_STRIPES][ST_COUNT]
     unsigned *work;   // [2] unit counter + finished-warp counter of the streaming AO kernel (self re-arming)
     int ao_kernel;    // AO_KERNEL_*
+    float4 *gather;   // rt_set_frame_target: this band's rows inside a whole-frame image (maybe peer memory), or null
 };
 
 // a halo record row: three consecutive arrays of W elements
@@ -111,6 +112,7 @@ struct PostParams {
     const float *ring_depth_w;
     void *halo_lo, *halo_hi;   // received records: row y0-1 (or the wrapped row) / row y0+rows
     void *send_lo, *send_hi;   // packed by the pack kernel
+    float4 *gather;            // like TraceOut::gather, for the post-processed colour of mode 1
     float4 rand_last;          // rand_buffer[2*AA-1]: what pixels[0][0][-1] aliases (FLAT32)
     unsigned long long *stats;
 };

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import real_time_ray_tracer_b200 as rtb
-from real_time_ray_tracer_b200 import api
+from real_time_ray_tracer_b200 import api, host
 from oracle import oracle as orc
 from tests.util import Scenario, diff_report, same_bits
 
@@ -276,12 +276,142 @@ def test_row_bands_on_one_gpu_equal_the_whole_frame(edge_mode, cuts):
         o.close()
 
 
-@pytest.mark.parametrize("kernel", ["tile", "stream"])
-def test_both_ao_kernels(kernel, monkeypatch):
-    """the tile kernel and the persistent streaming kernel are two schedules of the same arithmetic"""
+@pytest.mark.parametrize("kernel", ["phased", "stream"])
+def test_frame_target_assembles_the_bands(kernel, monkeypatch):
+    """rt_set_frame_target: three band contexts store their final colour straight into one whole-frame image
+    (here on the same GPU; across ranks the same pointer is a peer mapping) -- it must equal the oracle's
+    image in every mode, and mode 1 must deliver the post-processed colour, not the raw trace output."""
+    import torch
+
+    from real_time_ray_tracer_b200 import bands
+
+    monkeypatch.setenv("RT_AO_KERNEL", kernel)
+    W, H, AA = 101, 57, 4
+    cuts = [0, 9, 30, 57]
+    n = len(cuts) - 1
+    frame = api.Frame.create(W, H, 0)
+    img = bands.device_tensor(frame.ptr, frame.nbytes, 0)
+    rts = [rtb.RayTracer(W, H, AA, band_y0=cuts[i], band_rows=cuts[i + 1] - cuts[i], band_index=i, band_count=n)
+           for i in range(n)]
+    engs = [bands.GpuBandEngine(rt) for rt in rts]
+    sc = Scenario("scene6", keys=("a",))
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(sc.shapes, sc.n)
+    for rt in rts:
+        rt.upload_scene(sc.shapes, sc.n)
+        rt.set_frame_target(frame.ptr)
+    for k, mode in enumerate((2, 3, 4, 1, 1, 2)):
+        slot, u, rb = sc.next(mode, AA)
+        for e in engs:
+            e.render_frame(mode, u, rb)
+            if mode == 1:
+                e.halo_pack()
+        if mode == 1:
+            for rt in rts:
+                rt.synchronize()
+            for i, e in enumerate(engs):
+                engs[(i + 1) % n].recv_lo.copy_(e.send_hi)
+                if i > 0:
+                    engs[i - 1].recv_hi.copy_(e.send_lo)
+            torch.cuda.synchronize()
+            for e in engs:
+                e.postprocess()
+        for rt in rts:
+            rt.synchronize()
+        o.render(mode, u, rb)
+        if mode == 1:
+            o.postprocess()
+        got = img.cpu().numpy().reshape(H, W, 4)
+        assert same_bits(got, o.get(orc.IMAGE)), f"frame {k} mode {mode}: {diff_report(got, o.get(orc.IMAGE))}"
+    # switched off again: the image keeps the last frame
+    for rt in rts:
+        rt.set_frame_target(None)
+    before = img.clone()
+    slot, u, rb = sc.next(2, AA)
+    for rt in rts:
+        rt.render_frame(2, u, rb)
+        rt.synchronize()
+    assert torch.equal(img, before)
+    for rt in rts:
+        rt.close()
+    frame.close()
+    o.close()
+
+
+def _ipc_worker(rank, world, port, W, H, AA, cuts, q):
+    import os
+
+    import torch
+    import torch.distributed as dist
+
+    from real_time_ray_tracer_b200 import bands
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.cuda.set_device(0)
+    try:
+        dg = bands.DirectGather(W, H, rank, world, 0)
+        y0, rows = cuts[rank], cuts[rank + 1] - cuts[rank]
+        sc = Scenario("scene1", keys=("d",))
+        with rtb.RayTracer(W, H, AA, band_y0=y0, band_rows=rows, band_index=rank, band_count=world) as rt:
+            rt.upload_scene(sc.shapes, sc.n)
+            br = bands.BandedRenderer(bands.GpuBandEngine(rt), W, H, [(cuts[i], cuts[i + 1] - cuts[i]) for i in range(world)],
+                                      rank, world, direct=dg)
+            out = []
+            for k, mode in enumerate((2, 4, 3)):
+                slot, u, rb = sc.next(mode, AA)
+                br.render(mode, u, rb)
+                rt.synchronize()
+                kf = br.frame_k
+                br.gather_start(slot)          # gloo all-reduce of a CUDA tensor: the fence
+                dist.barrier()
+                if rank == 0:
+                    torch.cuda.synchronize()
+                    out.append(dg.frame(kf).cpu().numpy().reshape(H, W, 4).copy())
+            dist.barrier()
+        if rank == 0:
+            q.put(out)
+        dist.barrier()
+        dg.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_direct_gather_across_processes_over_cuda_ipc():
+    """Two processes (one band each, both on cuda:0 -- the box of the GPU test tier has one GPU): rank 1 maps
+    rank 0's images through the IPC handle and its kernels store the band into them; rank 0 reads whole frames
+    that must equal the oracle's.  Across GPUs the only difference is that the mapping goes over NVLink."""
+    import torch.multiprocessing as mp
+
+    W, H, AA = 88, 50, 4
+    cuts = [0, 21, 50]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29650 + (np.random.default_rng().integers(0, 200))
+    procs = [ctx.Process(target=_ipc_worker, args=(r, 2, int(port), W, H, AA, cuts, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    sc = Scenario("scene1", keys=("d",))
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(sc.shapes, sc.n)
+    for k, mode in enumerate((2, 4, 3)):
+        slot, u, rb = sc.next(mode, AA)
+        o.render(mode, u, rb)
+        assert same_bits(out[k], o.get(orc.IMAGE)), f"frame {k} mode {mode}: {diff_report(out[k], o.get(orc.IMAGE))}"
+    o.close()
+
+
+@pytest.mark.parametrize("kernel", ["phased", "tile", "stream"])
+def test_all_ao_kernels(kernel, monkeypatch):
+    """the phased (default), tile and persistent streaming kernels are three schedules of the same arithmetic;
+    recursion depths 1, 2 and 3 exercise the phased kernel's head-only, no-survivor and first-survivor paths"""
     monkeypatch.setenv("RT_AO_KERNEL", kernel)
     W, H, AA = 203, 117, 4
-    for scene, rd in (("scene1", 20), ("scene6", 20), ("scene1", 1), ("scene5", 3)):
+    for scene, rd in (("scene1", 20), ("scene6", 20), ("scene1", 1), ("scene1", 2), ("scene5", 3)):
         sc = Scenario(scene, keys=("e",))
         with rtb.RayTracer(W, H, AA, recursion_depth=rd) as rt:
             o = orc.Oracle(W, H, AA, recursion_depth=rd)
@@ -298,6 +428,49 @@ def test_both_ao_kernels(kernel, monkeypatch):
             for kk in so:
                 assert so[kk] == sg[kk], (kernel, kk, so[kk], sg[kk])
             o.close()
+
+
+def _custom_scenario(shapes):
+    sc = Scenario("scene1")
+    sc.scene = host.scene(shapes=list(shapes))
+    sc.n = len(shapes)
+    sc.shapes = host.load_shape_buffer(sc.scene)
+    return sc
+
+
+@pytest.mark.parametrize("order", ["plane_first", "sphere_first"])
+@pytest.mark.parametrize("mode", [2, 3, 4])
+def test_equal_distance_tie_goes_to_the_earlier_shape(order, mode):
+    """The kernels walk spheres and planes as two lists; the shader walks one list with a strict `<`, so of two
+    shapes hit at exactly the same t the EARLIER one wins.  From the default camera the centre ray of a
+    440x330 image is exactly (0,0,-1): the sphere (0,0,0) r=2 and the plane z=2 are both hit at t = 12.
+    A rectangle (never intersected, ao_compute.glsl:130-133) and more planes sit between them in the list."""
+    W, H, AA = 440, 330, 4
+    sph = host.make_sphere((0, 0, 0), 2.0, (0.8, 0.2, 0.5), reflectivity=0.5)
+    pl = host.make_plane((0, 0, 1), 2.0, (0.3, 0.9, 0.5))
+    rect = host.make_rectangle((-1, -1, 5), (2, 0, 0), (0, 2, 0), (1, 1, 1))
+    floor = host.make_plane((0, 1, 0), -4.0, (0.3, 0.0, 0.5))
+    far = host.make_sphere((-4.5, 4, -15), 4.0, (0.2, 0.8, 0.1), reflectivity=0.2)
+    shapes = [floor, pl, rect, far, sph] if order == "plane_first" else [far, sph, rect, floor, pl]
+    sc = _custom_scenario(shapes)
+    with rtb.RayTracer(W, H, AA) as rt:
+        o = orc.Oracle(W, H, AA)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        slot, u, rb = sc.next(mode, AA)
+        rt.render_frame(mode, u, rb)
+        o.render(mode, u, rb)
+        want = o.get(orc.HIT_INDEX)
+        d = o.get(orc.DEPTH, slot)
+        if mode == 2:
+            assert d[165, 220, 0] * AA == 12.0          # the tie really happens on the centre ray
+        assert want[165, 220] == 1 and (want[165, 218] == 4) == (order == "sphere_first")  # index 1 wins the tie
+        assert np.array_equal(rt.download(rtb.BUF_HIT_INDEX), want)
+        assert same_bits(rt.download(rtb.BUF_COLOR, slot), o.get(orc.PIXELS, slot))
+        so, sg = o.stats(), rt.stats()
+        for k in so:
+            assert so[k] == sg[k], (k, so[k], sg[k])
+        o.close()
 
 
 def test_full_size_properties_1080p():
