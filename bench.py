@@ -199,7 +199,8 @@ def run_b200(args) -> None:
     # N > 1: the frame is assembled on rank 0.  Default = direct gather: every rank's kernels store their band
     # straight into rank 0's image over NVLink (rt_set_frame_target) and a one-element all-reduce fences the
     # frame; --nccl-gather = the bands travel as NCCL point-to-point messages after the kernels.
-    direct = bands.DirectGather(W, H, rank, world, local) if (world > 1 and not args.nccl_gather) else None
+    direct = bands.DirectGather(W, H, rank, world, local, tracer=rt, fence=args.fence) \
+        if (world > 1 and not args.nccl_gather) else None
     br = bands.BandedRenderer(eng, W, H, plan, rank, world, direct=direct)
     # rank 0 assembles frames in two alternating buffers so the gather of frame k overlaps the trace of k+1
     fulls = [torch.empty(W * H * 4, dtype=torch.float32, device=f"cuda:{local}") for _ in range(2)] \
@@ -251,6 +252,8 @@ def run_b200(args) -> None:
     barrier()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
+    if direct is not None and direct.halo_direct and rt.fence_timed_out():
+        raise SystemExit("bench.py: an rt_fence timed out waiting for a peer rank; the run is invalid")
     st = rt.stats()
     keys = list(L.STAT_COUNTERS)
     cnt = torch.tensor([float(st[k]) for k in keys], dtype=torch.float64, device=f"cuda:{local}")
@@ -306,7 +309,7 @@ def run_b200(args) -> None:
                        "recursion_depth": host.RECURSION_DEPTH, "ring_frames": host.NUM_FRAMES,
                        "parallelism": f"row-bands x{world}", "bands": plan,
                        "gather": ("none" if world == 1 else "nccl p2p" if direct is None else
-                                  "direct NVLink stores into rank 0's image + all-reduce fence"),
+                                  f"direct NVLink stores into rank 0's image, halo rows stored into the neighbours, fence = {args.fence}"),
                        "l2": "no input reuse: ~1.4 KB of kernel parameters in, each frame writes a different "
                              "ring slot (8 x %.0f MB > 126 MB L2)" % (W * H * 44 / 1e6)},
             "rays_per_frame": rays / K,
@@ -544,6 +547,9 @@ def main():
     ap.add_argument("--no-e2e", dest="e2e", action="store_false")
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     ap.add_argument("--even-bands", action="store_true", help="equal-height bands instead of cost-weighted")
+    ap.add_argument("--fence", default="flags", choices=["flags", "allreduce"],
+                    help="N > 1, direct gather: per-frame fence = rt_fence (peer-memory flags, no host-side "
+                         "communication call) or a one-element NCCL all-reduce")
     ap.add_argument("--nccl-gather", action="store_true",
                     help="N > 1: gather bands with NCCL point-to-point instead of direct NVLink stores")
     ap.add_argument("--replan", type=int, default=3, help="band re-cut rounds from measured times (N > 1)")

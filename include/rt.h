@@ -181,21 +181,46 @@ int rt_download_async(rt_ctx *ctx, int buffer, int slot, void *pinned_host, size
 /* raw device pointer of a row-major plane of this band (for NCCL / framework interop) */
 int rt_device_ptr(rt_ctx *ctx, int buffer, int slot, void **out_ptr, size_t *out_bytes);
 
-/* Direct gather for row bands (replaces the final "gather to rank 0" pass; no reference counterpart: the
- * reference renders the whole image on one GPU, src/main.cpp:604).  A frame image is float4[height][width],
- * row-major, y = 0 at the bottom.  While a target is set, the kernel that produces a frame's final colour
- * (the trace kernel in modes 2-4, the post-processing kernel in mode 1) stores every pixel of this band
- * into rows [band_y0, band_y0 + band_rows) of the target as well as into the ring slot.  The target may be
- * memory of another GPU of the box (rt_frame_import maps it over NVLink/NVSwitch with peer access), so the
- * gather costs no extra pass: the stores travel while the band is still being computed.  The caller fences
- * the ranks (any stream-ordered collective) before it reads the assembled frame. */
+/* ---- row bands across the GPUs of one box, over peer memory (no reference counterpart: the reference
+ * renders the whole image on one GPU, src/main.cpp:604) ------------------------------------------------
+ *
+ * Direct gather.  A frame image is float4[height][width], row-major, y = 0 at the bottom.  While a target
+ * is set, the kernel that produces a frame's final colour (the trace kernel in modes 2-4, the
+ * post-processing kernel in mode 1) stores every pixel of this band into rows [band_y0, band_y0 +
+ * band_rows) of the target as well as into the ring slot.  The target may be memory of another GPU
+ * (rt_peer_import maps it over NVLink/NVSwitch), so the gather costs no extra pass.
+ *
+ * Peer mappings.  rt_peer_export turns a device allocation of this library (a frame, a mailbox, a halo row
+ * of rt_get_halo) into a 64-byte handle another PROCESS passes to rt_peer_import; the mapping enables peer
+ * access between the two devices.
+ *
+ * Linked bands.  rt_link_peers gives a context (a) the mailboxes of all ranks, which makes rt_fence
+ * available: a barrier on the context's stream, one small kernel that signals every peer's mailbox and
+ * spins on its own until every peer has signalled (each rank must own its GPU; after rt_fence returns on
+ * the stream, everything the other ranks enqueued before THEIR rt_fence is complete and visible); and
+ * (b) the neighbours' halo rows, so that rt_halo_pack stores this band's edge rows straight into
+ * recv_lo of band (i+1) % count and recv_hi of band i-1.  A mode-1 frame then is
+ *     rt_render_frame; rt_halo_pack; rt_fence; rt_postprocess; rt_fence
+ * with no host-side communication call at all. */
 int rt_frame_create(int device, int width, int height, void **out_frame);
 int rt_frame_destroy(int device, void *frame);
-#define RT_FRAME_HANDLE_BYTES 64
-int rt_frame_export(int device, void *frame, unsigned char handle[RT_FRAME_HANDLE_BYTES]);
-int rt_frame_import(int device, const unsigned char handle[RT_FRAME_HANDLE_BYTES], void **out_frame);
-int rt_frame_release(int device, void *imported_frame);
 int rt_set_frame_target(rt_ctx *ctx, void *frame); /* NULL = off; takes effect with the next rt_render_frame */
+
+#define RT_PEER_HANDLE_BYTES 64
+#define RT_MAX_RANKS 16
+int rt_peer_export(int device, void *allocation, unsigned char handle[RT_PEER_HANDLE_BYTES]);
+int rt_peer_import(int device, const unsigned char handle[RT_PEER_HANDLE_BYTES], void **out_ptr);
+int rt_peer_release(int device, void *imported_ptr);
+
+int rt_mailbox_create(int device, void **out_mailbox); /* zero-filled; RT_MAX_RANKS epochs + a status word */
+int rt_mailbox_destroy(int device, void *mailbox);
+/* mailboxes[world]: entry `rank` is this context's own (rt_mailbox_create), the others are imported.
+ * next_recv_lo / prev_recv_hi: imported halo rows of the neighbouring bands, or NULL to keep packing into
+ * this context's own send rows (prev_recv_hi is NULL for band 0). */
+int rt_link_peers(rt_ctx *ctx, int rank, int world, void *const *mailboxes, void *next_recv_lo, void *prev_recv_hi);
+int rt_fence(rt_ctx *ctx);
+/* synchronises; *timed_out = 1 if a fence gave up waiting for a peer (10 s): the frame data is not valid */
+int rt_fence_status(rt_ctx *ctx, int *timed_out);
 
 int rt_get_stats(rt_ctx *ctx, rt_stats *out); /* synchronises */
 int rt_reset_stats(rt_ctx *ctx);

@@ -40,8 +40,8 @@ EXPORTS = (
     "rt_synchronize", "rt_set_timing", "rt_upload_scene", "rt_render_frame", "rt_halo_pack", "rt_get_halo",
     "rt_postprocess", "rt_download", "rt_upload", "rt_download_async", "rt_device_ptr", "rt_get_stats",
     "rt_reset_stats", "rt_debug_eval_math", "rt_measure_fp32_peak",
-    "rt_set_frame_target", "rt_frame_create", "rt_frame_destroy", "rt_frame_export", "rt_frame_import",
-    "rt_frame_release",
+    "rt_set_frame_target", "rt_frame_create", "rt_frame_destroy", "rt_peer_export", "rt_peer_import",
+    "rt_peer_release", "rt_mailbox_create", "rt_mailbox_destroy", "rt_link_peers", "rt_fence", "rt_fence_status",
 )
 
 _lib = None
@@ -82,8 +82,13 @@ def load():
     L.rt_set_frame_target.argtypes = [vp, vp]
     L.rt_frame_create.argtypes = [i32, i32, i32, C.POINTER(vp)]
     L.rt_frame_destroy.argtypes = [i32, vp]
-    L.rt_frame_export.argtypes = [i32, vp, C.c_char_p]
-    L.rt_frame_import.argtypes = [i32, C.c_char_p, C.POINTER(vp)]
-    L.rt_frame_release.argtypes = [i32, vp]
+    L.rt_peer_export.argtypes = [i32, vp, C.c_char_p]
+    L.rt_peer_import.argtypes = [i32, C.c_char_p, C.POINTER(vp)]
+    L.rt_peer_release.argtypes = [i32, vp]
+    L.rt_mailbox_create.argtypes = [i32, C.POINTER(vp)]
+    L.rt_mailbox_destroy.argtypes = [i32, vp]
+    L.rt_link_peers.argtypes = [vp, i32, i32, C.POINTER(vp), vp, vp]
+    L.rt_fence.argtypes = [vp]
+    L.rt_fence_status.argtypes = [vp, C.POINTER(i32)]
     _lib = L
     return L

@@ -98,6 +98,21 @@ class RayTracer:
         image at ``frame_ptr`` (a ``Frame``'s pointer, local or imported from another rank); None = off."""
         self._check(self.lib.rt_set_frame_target(self.h, C.c_void_p(frame_ptr or 0)))
 
+    def link_peers(self, rank: int, world: int, mailboxes, next_recv_lo: Optional[int] = None,
+                   prev_recv_hi: Optional[int] = None):
+        """rt_link_peers: ``mailboxes`` = world device pointers (own + imported)."""
+        arr = (C.c_void_p * world)(*[C.c_void_p(int(m)) for m in mailboxes])
+        self._check(self.lib.rt_link_peers(self.h, rank, world, arr, C.c_void_p(next_recv_lo or 0),
+                                           C.c_void_p(prev_recv_hi or 0)))
+
+    def fence(self):
+        self._check(self.lib.rt_fence(self.h))
+
+    def fence_timed_out(self) -> bool:
+        v = C.c_int(0)
+        self._check(self.lib.rt_fence_status(self.h, C.byref(v)))
+        return bool(v.value)
+
     def halo_pack(self):
         self._check(self.lib.rt_halo_pack(self.h))
 
@@ -146,6 +161,44 @@ class RayTracer:
         self._check(self.lib.rt_reset_stats(self.h))
 
 
+class PeerMem:
+    """A device allocation of the library shared between the processes of one box (rt_peer_* in include/rt.h):
+    ``export(ptr)`` gives the 64-byte handle, ``PeerMem.open(handle)`` maps it in another process."""
+
+    def __init__(self, ptr: int, device: int):
+        self.ptr, self.device, self.lib = ptr, device, L.load()
+
+    @staticmethod
+    def export(ptr: int, device: int) -> bytes:
+        lib = L.load()
+        buf = C.create_string_buffer(64)
+        Frame._ok(lib, lib.rt_peer_export(device, C.c_void_p(ptr), buf))
+        return buf.raw
+
+    @classmethod
+    def open(cls, handle: bytes, device: int) -> "PeerMem":
+        lib = L.load()
+        p = C.c_void_p()
+        Frame._ok(lib, lib.rt_peer_import(device, C.create_string_buffer(handle, 64), C.byref(p)))
+        return cls(p.value, device)
+
+    def close(self):
+        if self.ptr:
+            self.lib.rt_peer_release(self.device, C.c_void_p(self.ptr))
+            self.ptr = 0
+
+
+def mailbox_create(device: int) -> int:
+    lib = L.load()
+    p = C.c_void_p()
+    Frame._ok(lib, lib.rt_mailbox_create(device, C.byref(p)))
+    return p.value
+
+
+def mailbox_destroy(device: int, ptr: int):
+    L.load().rt_mailbox_destroy(device, C.c_void_p(ptr))
+
+
 class Frame:
     """A whole-frame image float4[H][W] on one GPU that row bands of other contexts -- other processes, other
     GPUs of the box -- write into directly (rt_frame_* in include/rt.h).  ``Frame.create`` allocates and can
@@ -170,14 +223,14 @@ class Frame:
 
     def export(self) -> bytes:
         buf = C.create_string_buffer(64)
-        self._ok(self.lib, self.lib.rt_frame_export(self.device, C.c_void_p(self.ptr), buf))
+        self._ok(self.lib, self.lib.rt_peer_export(self.device, C.c_void_p(self.ptr), buf))
         return buf.raw
 
     @classmethod
     def open(cls, handle: bytes, width: int, height: int, device: int = 0) -> "Frame":
         lib = L.load()
         p = C.c_void_p()
-        cls._ok(lib, lib.rt_frame_import(device, C.create_string_buffer(handle, 64), C.byref(p)))
+        cls._ok(lib, lib.rt_peer_import(device, C.create_string_buffer(handle, 64), C.byref(p)))
         return cls(p.value, width, height, device, True)
 
     @property
@@ -186,7 +239,7 @@ class Frame:
 
     def close(self):
         if self.ptr:
-            f = self.lib.rt_frame_release if self.imported else self.lib.rt_frame_destroy
+            f = self.lib.rt_peer_release if self.imported else self.lib.rt_frame_destroy
             f(self.device, C.c_void_p(self.ptr))
             self.ptr = 0
 

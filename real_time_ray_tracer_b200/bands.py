@@ -93,6 +93,9 @@ class GpuBandEngine:
     def set_frame_target(self, ptr):
         self.rt.set_frame_target(ptr)
 
+    def fence(self):
+        self.rt.fence()
+
     def halo_pack(self):
         self.rt.halo_pack()
 
@@ -113,13 +116,19 @@ class DirectGather:
     stream: when it has completed on rank 0, every rank's kernels of the frame have completed (stream order on
     each rank), so all bands are in the image."""
 
-    def __init__(self, width: int, height: int, rank: int, world: int, device: int, nbuf: int = 2, group=None):
+    def __init__(self, width: int, height: int, rank: int, world: int, device: int, nbuf: int = 2, group=None,
+                 tracer=None, fence: str = "allreduce"):
+        """``fence="flags"`` (needs ``tracer``, one GPU per rank): the ranks exchange mailbox and halo-row
+        handles once, ``rt_link_peers`` wires them into the context, and from then on a frame needs no
+        host-side communication call: ``rt_fence`` is a kernel that signals and polls peer memory, and
+        ``rt_halo_pack`` stores the edge rows straight into the neighbours' halo rows."""
         import torch
         import torch.distributed as dist
 
         from . import api
 
         self.rank, self.world, self.device, self.group = rank, world, device, group
+        self.fence_kind, self.tracer, self.mailbox, self.maps = fence, tracer, None, []
         handles = None
         if rank == 0:
             self.frames = [api.Frame.create(width, height, device) for _ in range(nbuf)]
@@ -131,14 +140,52 @@ class DirectGather:
             self.frames = [api.Frame.open(h, width, height, device) for h in box[0]]
         self.token = torch.zeros(1, dtype=torch.float32, device=f"cuda:{device}")
         self.tensors = [device_tensor(f.ptr, f.nbytes, device) for f in self.frames] if rank == 0 else None
+        if fence == "flags":
+            if tracer is None:
+                raise ValueError("fence='flags' needs the band's RayTracer")
+            self.mailbox = api.mailbox_create(device)
+            info = tracer.halo_info()
+            mine = {"mb": api.PeerMem.export(self.mailbox, device),
+                    "recv_lo": api.PeerMem.export(info.recv_lo, device),
+                    "recv_hi": api.PeerMem.export(info.recv_hi, device)}
+            allh = [None] * world
+            if world > 1:
+                dist.all_gather_object(allh, mine, group=group)
+            else:
+                allh[0] = mine
+            boxes = []
+            for j in range(world):
+                if j == rank:
+                    boxes.append(self.mailbox)
+                else:
+                    self.maps.append(api.PeerMem.open(allh[j]["mb"], device))
+                    boxes.append(self.maps[-1].ptr)
+            nxt = prv = None
+            if world > 1:
+                nxt = api.PeerMem.open(allh[(rank + 1) % world]["recv_lo"], device)
+                self.maps.append(nxt)
+                if rank > 0:
+                    prv = api.PeerMem.open(allh[rank - 1]["recv_hi"], device)
+                    self.maps.append(prv)
+            tracer.link_peers(rank, world, boxes, nxt.ptr if nxt else None, prv.ptr if prv else None)
+            if world > 1:
+                dist.barrier(group=group)   # every rank is linked before the first fence kernel runs
+        elif fence != "allreduce":
+            raise ValueError("fence must be 'allreduce' or 'flags'")
 
     def target(self, k: int) -> int:
         return self.frames[k % len(self.frames)].ptr
 
+    @property
+    def halo_direct(self) -> bool:
+        return self.fence_kind == "flags"
+
     def fence(self):
         import torch.distributed as dist
 
-        if self.world > 1:
+        if self.fence_kind == "flags":
+            self.tracer.fence()
+        elif self.world > 1:
             dist.all_reduce(self.token, group=self.group)
 
     def frame(self, k: int):
@@ -146,8 +193,16 @@ class DirectGather:
         return self.tensors[k % len(self.tensors)] if self.rank == 0 else None
 
     def close(self):
+        for m in self.maps:
+            m.close()
+        self.maps = []
         for f in self.frames:
             f.close()
+        if self.mailbox:
+            from . import api
+
+            api.mailbox_destroy(self.device, self.mailbox)
+            self.mailbox = None
 
 
 class BandedRenderer:
@@ -183,7 +238,10 @@ class BandedRenderer:
         if mode == 1:
             if self.world > 1:
                 self.e.halo_pack()
-                self.exchange_halo()
+                if self.direct is not None and self.direct.halo_direct:
+                    self.direct.fence()     # the pack kernels stored into the neighbours' halo rows
+                else:
+                    self.exchange_halo()
             self.e.postprocess()
 
     def gather_start(self, slot: int, out=None):

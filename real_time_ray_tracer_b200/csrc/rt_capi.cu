@@ -41,6 +41,11 @@ struct rt_ctx {
     int last_mode = 0, last_slot = 0;
     bool frame_pending_post = false, halo_packed = false;
     float4 rand_last{};
+    PeerBoxes peers{};           // rt_link_peers
+    int link_rank = -1, link_world = 0;
+    unsigned long long fence_epoch = 0;
+    void *peer_next_recv_lo = nullptr, *peer_prev_recv_hi = nullptr;
+    bool halo_direct = false;
     float4 *frame_target = nullptr; // rt_set_frame_target: whole-frame image, maybe peer memory
     float4 *frame_target_post = nullptr; // the target the pending mode-1 frame was rendered for
     bool timing = false;
@@ -327,6 +332,10 @@ int rt_halo_pack(rt_ctx *c)
         // the wrapped row goes straight into this band's own lower halo
         q.send_lo = nullptr;
         q.send_hi = c->halo[2];
+    } else if (c->halo_direct) {
+        // rt_link_peers: the edge rows go straight into the neighbours' halo rows over NVLink
+        q.send_lo = c->peer_prev_recv_hi; // null on band 0: nobody below
+        q.send_hi = c->peer_next_recv_lo;
     }
     CU(c, launch_halo_pack(q, c->stream));
     c->halo_packed = true;
@@ -371,6 +380,48 @@ int rt_set_frame_target(rt_ctx *c, void *frame)
     return RT_OK;
 }
 
+int rt_link_peers(rt_ctx *c, int rank, int world, void *const *mailboxes, void *next_recv_lo, void *prev_recv_hi)
+{
+    if (!c) return RT_EINVAL;
+    if (world < 1 || world > RT_MAX_RANKS || rank < 0 || rank >= world || !mailboxes)
+        return fail(c, RT_EINVAL, "rt_link_peers: rank %d of %d (at most %d ranks)", rank, world, RT_MAX_RANKS);
+    for (int i = 0; i < world; i++)
+        if (!mailboxes[i]) return fail(c, RT_EINVAL, "rt_link_peers: mailbox %d is null", i);
+    if (prev_recv_hi && !next_recv_lo) return fail(c, RT_EINVAL, "rt_link_peers: prev_recv_hi given without next_recv_lo");
+    for (int i = 0; i < world; i++) c->peers.box[i] = (unsigned long long *)mailboxes[i];
+    c->link_rank = rank;
+    c->link_world = world;
+    c->peer_next_recv_lo = next_recv_lo;
+    c->peer_prev_recv_hi = prev_recv_hi;
+    c->halo_direct = next_recv_lo != nullptr;
+    // epochs continue from what this rank's mailbox already shows for itself (a second context of the
+    // same rank keeps counting instead of starting below the peers' expectations)
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, cudaMemcpy(&c->fence_epoch, c->peers.box[rank] + rank, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+int rt_fence(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence: call rt_link_peers first");
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, launch_fence(c->peers, c->link_rank, c->link_world, ++c->fence_epoch, c->stream));
+    return RT_OK;
+}
+
+int rt_fence_status(rt_ctx *c, int *timed_out)
+{
+    if (!c || !timed_out) return RT_EINVAL;
+    if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence_status: call rt_link_peers first");
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    unsigned long long st = 0;
+    CU(c, cudaMemcpy(&st, c->peers.box[c->link_rank] + RT_MAX_RANKS, sizeof st, cudaMemcpyDeviceToHost));
+    *timed_out = st != 0;
+    return RT_OK;
+}
+
 static int frame_fail(int code, const char *what, cudaError_t e)
 {
     fail(nullptr, code, "%s: %s", what, cudaGetErrorString(e));
@@ -396,6 +447,22 @@ int rt_frame_create(int device, int width, int height, void **out_frame)
     return RT_OK;
 }
 
+int rt_mailbox_create(int device, void **out_mailbox)
+{
+    if (!out_mailbox) return fail(nullptr, RT_EINVAL, "rt_mailbox_create: null argument");
+    *out_mailbox = nullptr;
+    if (device < 0 || device >= rt_device_count()) return fail(nullptr, RT_ENODEVICE, "rt_mailbox_create: device %d", device);
+    cudaError_t e = cudaSetDevice(device);
+    const size_t bytes = MAILBOX_WORDS * sizeof(unsigned long long);
+    if (e == cudaSuccess) e = cudaMalloc(out_mailbox, bytes);
+    if (e == cudaSuccess) e = cudaMemset(*out_mailbox, 0, bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return frame_fail(RT_ECUDA, "rt_mailbox_create", e);
+    return RT_OK;
+}
+
+int rt_mailbox_destroy(int device, void *mailbox) { return rt_frame_destroy(device, mailbox); }
+
 int rt_frame_destroy(int device, void *frame)
 {
     if (!frame) return RT_OK;
@@ -404,21 +471,21 @@ int rt_frame_destroy(int device, void *frame)
     return e == cudaSuccess ? RT_OK : frame_fail(RT_ECUDA, "rt_frame_destroy", e);
 }
 
-int rt_frame_export(int device, void *frame, unsigned char handle[RT_FRAME_HANDLE_BYTES])
+int rt_peer_export(int device, void *frame, unsigned char handle[RT_PEER_HANDLE_BYTES])
 {
-    static_assert(sizeof(cudaIpcMemHandle_t) == RT_FRAME_HANDLE_BYTES, "handle size");
-    if (!frame || !handle) return fail(nullptr, RT_EINVAL, "rt_frame_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_PEER_HANDLE_BYTES, "handle size");
+    if (!frame || !handle) return fail(nullptr, RT_EINVAL, "rt_peer_export: null argument");
     cudaIpcMemHandle_t h;
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, frame);
-    if (e != cudaSuccess) return frame_fail(RT_ECUDA, "rt_frame_export", e);
+    if (e != cudaSuccess) return frame_fail(RT_ECUDA, "rt_peer_export", e);
     memcpy(handle, &h, sizeof h);
     return RT_OK;
 }
 
-int rt_frame_import(int device, const unsigned char handle[RT_FRAME_HANDLE_BYTES], void **out_frame)
+int rt_peer_import(int device, const unsigned char handle[RT_PEER_HANDLE_BYTES], void **out_frame)
 {
-    if (!handle || !out_frame) return fail(nullptr, RT_EINVAL, "rt_frame_import: null argument");
+    if (!handle || !out_frame) return fail(nullptr, RT_EINVAL, "rt_peer_import: null argument");
     *out_frame = nullptr;
     cudaIpcMemHandle_t h;
     memcpy(&h, handle, sizeof h);
@@ -426,16 +493,16 @@ int rt_frame_import(int device, const unsigned char handle[RT_FRAME_HANDLE_BYTES
     // maps the exporting process's allocation; when it lives on another GPU the runtime enables peer access
     // (NVLink) between the two devices for this mapping
     if (e == cudaSuccess) e = cudaIpcOpenMemHandle(out_frame, h, cudaIpcMemLazyEnablePeerAccess);
-    if (e != cudaSuccess) return frame_fail(RT_ECUDA, "rt_frame_import", e);
+    if (e != cudaSuccess) return frame_fail(RT_ECUDA, "rt_peer_import", e);
     return RT_OK;
 }
 
-int rt_frame_release(int device, void *imported_frame)
+int rt_peer_release(int device, void *imported_frame)
 {
     if (!imported_frame) return RT_OK;
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaIpcCloseMemHandle(imported_frame);
-    return e == cudaSuccess ? RT_OK : frame_fail(RT_ECUDA, "rt_frame_release", e);
+    return e == cudaSuccess ? RT_OK : frame_fail(RT_ECUDA, "rt_peer_release", e);
 }
 
 // ---- buffers ---------------------------------------------------------------------------------

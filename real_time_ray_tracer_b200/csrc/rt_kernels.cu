@@ -547,6 +547,42 @@ cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s)
 }
 
 // ---------------------------------------------------------------------------------------------
+// rt_fence: barrier between the ranks of one box over peer memory (one GPU per rank)
+// ---------------------------------------------------------------------------------------------
+// Thread j signals rank j (epoch -> slot `rank` of ITS mailbox, a peer mapping over NVLink) and then waits
+// for rank j's signal in slot j of this rank's own mailbox.  The release/acquire pair at system scope
+// together with stream order (this kernel runs after everything enqueued before it on its rank) makes
+// every band row, halo row or frame pixel a peer stored before its fence visible to what follows here.
+// A peer that never arrives (crashed process) ends the wait after 10 s with the status word set.
+__global__ void rt_fence_kernel(const __grid_constant__ PeerBoxes peers, int rank, int world, unsigned long long epoch)
+{
+    const int j = threadIdx.x;
+    if (j >= world) return;
+    unsigned long long *dst = peers.box[j] + rank;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(epoch) : "memory");
+    const unsigned long long *src = peers.box[rank] + j;
+    unsigned long long t0 = 0, now = 0, seen = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(src) : "memory");
+        if (seen >= epoch) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 > 10000000000ull) {
+            peers.box[rank][RT_MAX_RANKS] = 1ull;
+            break;
+        }
+        __nanosleep(64);
+    }
+}
+
+cudaError_t launch_fence(const PeerBoxes &peers, int rank, int world, unsigned long long epoch, cudaStream_t s)
+{
+    rt_fence_kernel<<<1, 32, 0, s>>>(peers, rank, world, epoch);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
 // layout helpers for rt_download / rt_upload
 // ---------------------------------------------------------------------------------------------
 // row-major [rows][W] <-> the reference's x-major [W][rows] (src/main.cpp:81-84), tiled through

@@ -117,6 +117,11 @@ struct PostParams {
     unsigned long long *stats;
 };
 
+// mailboxes of rt_fence: RT_MAX_RANKS 64-bit epochs (slot j = last epoch signalled by rank j) + a status word
+constexpr int MAILBOX_WORDS = RT_MAX_RANKS + 1;
+struct PeerBoxes { unsigned long long *box[RT_MAX_RANKS]; };
+cudaError_t launch_fence(const PeerBoxes &peers, int rank, int world, unsigned long long epoch, cudaStream_t s);
+
 // launchers (rt_kernels.cu)
 cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream_t s);

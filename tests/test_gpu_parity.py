@@ -338,7 +338,7 @@ def test_frame_target_assembles_the_bands(kernel, monkeypatch):
     o.close()
 
 
-def _ipc_worker(rank, world, port, W, H, AA, cuts, q):
+def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q):
     import os
 
     import torch
@@ -348,47 +348,46 @@ def _ipc_worker(rank, world, port, W, H, AA, cuts, q):
 
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    torch.cuda.set_device(0)
+    dev = 0 if one_gpu else rank
+    torch.cuda.set_device(dev)
     try:
-        dg = bands.DirectGather(W, H, rank, world, 0)
         y0, rows = cuts[rank], cuts[rank + 1] - cuts[rank]
         sc = Scenario("scene1", keys=("d",))
-        with rtb.RayTracer(W, H, AA, band_y0=y0, band_rows=rows, band_index=rank, band_count=world) as rt:
+        with rtb.RayTracer(W, H, AA, device=dev, band_y0=y0, band_rows=rows, band_index=rank, band_count=world) as rt:
+            dg = bands.DirectGather(W, H, rank, world, dev, tracer=rt, fence=fence)
             rt.upload_scene(sc.shapes, sc.n)
             br = bands.BandedRenderer(bands.GpuBandEngine(rt), W, H, [(cuts[i], cuts[i + 1] - cuts[i]) for i in range(world)],
                                       rank, world, direct=dg)
             out = []
-            for k, mode in enumerate((2, 4, 3)):
+            for k, mode in enumerate(modes):
                 slot, u, rb = sc.next(mode, AA)
                 br.render(mode, u, rb)
-                rt.synchronize()
                 kf = br.frame_k
-                br.gather_start(slot)          # gloo all-reduce of a CUDA tensor: the fence
+                br.gather_start(slot)          # the fence
+                rt.synchronize()
                 dist.barrier()
                 if rank == 0:
                     torch.cuda.synchronize()
                     out.append(dg.frame(kf).cpu().numpy().reshape(H, W, 4).copy())
+            if fence == "flags":
+                assert not rt.fence_timed_out()
             dist.barrier()
-        if rank == 0:
-            q.put(out)
-        dist.barrier()
-        dg.close()
+            if rank == 0:
+                q.put(out)
+            dist.barrier()
+            dg.close()
     finally:
         dist.destroy_process_group()
 
 
-def test_direct_gather_across_processes_over_cuda_ipc():
-    """Two processes (one band each, both on cuda:0 -- the box of the GPU test tier has one GPU): rank 1 maps
-    rank 0's images through the IPC handle and its kernels store the band into them; rank 0 reads whole frames
-    that must equal the oracle's.  Across GPUs the only difference is that the mapping goes over NVLink."""
+def _run_ranks(world, W, H, AA, cuts, modes, fence, one_gpu):
     import torch.multiprocessing as mp
 
-    W, H, AA = 88, 50, 4
-    cuts = [0, 21, 50]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29650 + (np.random.default_rng().integers(0, 200))
-    procs = [ctx.Process(target=_ipc_worker, args=(r, 2, int(port), W, H, AA, cuts, q)) for r in range(2)]
+    port = 29650 + int(np.random.default_rng().integers(0, 200))
+    procs = [ctx.Process(target=_ipc_worker, args=(r, world, port, W, H, AA, cuts, modes, fence, one_gpu, q))
+             for r in range(world)]
     for p in procs:
         p.start()
     out = q.get(timeout=300)
@@ -398,11 +397,34 @@ def test_direct_gather_across_processes_over_cuda_ipc():
     sc = Scenario("scene1", keys=("d",))
     o = orc.Oracle(W, H, AA)
     o.set_scene(sc.shapes, sc.n)
-    for k, mode in enumerate((2, 4, 3)):
+    for k, mode in enumerate(modes):
         slot, u, rb = sc.next(mode, AA)
         o.render(mode, u, rb)
+        if mode == 1:
+            o.postprocess()
         assert same_bits(out[k], o.get(orc.IMAGE)), f"frame {k} mode {mode}: {diff_report(out[k], o.get(orc.IMAGE))}"
     o.close()
+
+
+def test_direct_gather_across_processes_over_cuda_ipc():
+    """Two processes (one band each, both on cuda:0 -- the box of the GPU test tier has one GPU): rank 1 maps
+    rank 0's images through the IPC handle and its kernels store the band into them; rank 0 reads whole frames
+    that must equal the oracle's.  Across GPUs the only difference is that the mapping goes over NVLink.
+    The fence here is a gloo all-reduce: two ranks sharing one GPU must not spin on each other (rt_fence)."""
+    _run_ranks(2, 88, 50, 4, [0, 21, 50], (2, 4, 3), "allreduce", True)
+
+
+def test_linked_bands_fence_and_direct_halo_on_separate_gpus():
+    """One GPU per rank: rt_link_peers + rt_fence (peer-memory flags) + halo rows stored straight into the
+    neighbours, for mode-1 sequences (ring wrap of the FLAT32 border included) and the single-pass modes."""
+    import torch
+
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs one GPU per rank (run under gpurun --gpus 2)")
+    world = min(n, 4)
+    cuts = {2: [0, 21, 50], 3: [0, 9, 30, 50], 4: [0, 9, 10, 33, 50]}[world]
+    _run_ranks(world, 88, 50, 4, cuts, (1, 1, 1, 2, 1, 1, 4, 1, 1, 1, 1), "flags", False)
 
 
 @pytest.mark.parametrize("kernel", ["phased", "tile", "stream"])
