@@ -44,6 +44,16 @@ def flops_from_counters(st: dict, n_spheres: int, n_planes: int) -> float:
             + st["shaded"] * 64 + st["reflective"] * 38 + st["pixels"] * 11)
 
 
+def ncu_traffic(kernel: str, workload: str):
+    """DRAM bytes per launch of `kernel` on `workload` from the committed ncu capture, or None."""
+    path = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    try:
+        e = json.load(open(path)).get(f"{kernel}@{workload}")
+        return (e["read"] + e["write"]) if e else None
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def pp_bytes_from_counters(st: dict) -> float:
     """Algorithmic HBM bytes of the post-processing pass: every pixel reads raw colour 16 + normal 16
     and writes the ring colour 16 (the image IS the ring slot: no second store); a non-background pixel
@@ -95,6 +105,13 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.samples, self.stop_flag, self.proc = index, [], False, None
+        self.t0 = self.t1 = None
+
+    def mark_start(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def start(self):
         try:
@@ -108,7 +125,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.samples.append(line.strip())
+            self.samples.append((time.perf_counter(), line.strip()))
 
     def stop(self) -> dict:
         if not self.proc:
@@ -120,7 +137,15 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
+        # samples inside the timed region; a region shorter than a few sampling periods (multi-GPU runs of small
+        # frames last tens of milliseconds) is widened to the per-kernel timing legs that follow it under load
+        t0 = self.t0 or 0.0
+        inside = [l for (t, l) in self.samples if t >= t0 and (self.t1 is None or t <= self.t1 + 0.05)]
+        window = "timed region"
+        if len(inside) < 3:
+            inside = [l for (t, l) in self.samples if t >= t0]
+            window = "timed region + per-kernel timing legs"
+        for s in inside:
             f = [t.strip() for t in s.split(",")]
             if len(f) < 6:
                 continue
@@ -133,7 +158,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "window": window}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -244,14 +269,15 @@ def run_b200(args) -> None:
     rt.reset_stats()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.mark_start()
     e0.record()
     for _ in range(K):
         step()
     drain()
     e1.record()
     barrier()
+    sampler.mark_end()
     ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if rank == 0 else None
     if direct is not None and direct.halo_direct and rt.fence_timed_out():
         raise SystemExit("bench.py: an rt_fence timed out waiting for a peer rank; the run is invalid")
     st = rt.stats()
@@ -280,6 +306,7 @@ def run_b200(args) -> None:
             pp_ms.append((s1["ms_post_last"], pp_bytes_from_counters(s1)))
     rt.set_timing(False)
     barrier()
+    clocks = sampler.stop() if rank == 0 else None
 
     # ---- end to end through the public API with HOST buffers -----------------------------------
     e2e = None
@@ -292,10 +319,13 @@ def run_b200(args) -> None:
         fl = float(np.mean([f for _, f, _ in tr_ms]))
         kr = float(np.mean([r for _, _, r in tr_ms]))
         ach = fl / (t_ms * 1e-3) / 1e12
-        roof = {"bound": "fp32", "kernel": {1: "rt_ao_trace_kernel", 2: "rt_ao_trace_kernel", 3: "rt_phong_kernel",
-                                             4: "rt_hybrid_kernel"}[mode],
+        ao_name = {"tile": "rt_ao_trace_kernel", "stream": "rt_ao_stream_kernel"}.get(
+            os.environ.get("RT_AO_KERNEL", "phased"), "rt_ao_phased_kernel")
+        kname = {1: ao_name, 2: ao_name, 3: "rt_phong_kernel", 4: "rt_hybrid_kernel"}[mode]
+        roof = {"bound": "fp32", "kernel": kname,
                 "achieved": round(ach, 4), "peak": round(peak_tf, 3), "unit": "TFLOP/s",
-                "frac": round(ach / peak_tf, 5), "traffic": None,
+                "frac": round(ach / peak_tf, 5), "traffic": ncu_traffic(kname, args.workload) if world == 1 else None,
+                "algorithmic_bytes_written": int(W * H * (48 if mode in (1, 2) else 20)) if world == 1 else None,
                 "peak_source": "FFMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)",
                 "kernel_ms": round(t_ms, 5), "kernel_mrays_per_s": round(kr / (t_ms * 1e-3) / 1e6, 1),
                 "flops_per_launch": fl, "per_rank_band": world > 1}
@@ -324,7 +354,9 @@ def run_b200(args) -> None:
             p_b = float(np.mean([b for _, b in pp_ms]))
             out["roofline_postprocess"] = {
                 "bound": "hbm", "kernel": "rt_ao_postprocess_kernel", "achieved": round(p_b / (p_ms * 1e-3) / 1e9, 1),
-                "peak": hbm, "unit": "GB/s", "frac": round(p_b / (p_ms * 1e-3) / 1e9 / hbm, 4), "traffic": None,
+                "peak": hbm, "unit": "GB/s", "frac": round(p_b / (p_ms * 1e-3) / 1e9 / hbm, 4),
+                "traffic": ncu_traffic("rt_ao_postprocess_kernel", args.workload) if world == 1 else None,
+                "algorithmic_bytes": p_b,
                 "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback", "kernel_ms": round(p_ms, 5)}
         if e2e:
             out["e2e"] = e2e
@@ -451,7 +483,7 @@ def cpu_baseline(workload: str, budget_s: float = 12.0) -> dict:
     est = (time.perf_counter() - t) * fr.H / (y1 - y0)
     o.reset_stats()
     if est * 3 <= budget_s:
-        rows, frames = (0, fr.H), max(3, min(32, int(budget_s / est)))
+        rows, frames = (0, fr.H), max(3, min(512, int(budget_s / est)))
     else:
         rows, frames = _band_for_budget(fr.H, est, budget_s / 3), 3
     t = time.perf_counter()

@@ -25,9 +25,13 @@ for f in sorted(os.listdir(d)):
             ins.append((loc, m.group(2).strip()))
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
+# a report may hold several kernels: take the section whose kernel name matches
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+sec = next(i for i in starts if pat in rows[i][1])
+hi = sec + 1
 h = rows[hi]
-body = rows[hi + 1:]
+end = next((i for i in starts if i > sec), len(rows))
+body = [r for r in rows[hi + 1:end] if r]
 ci, cs, ct = h.index("Instructions Executed"), h.index("# Samples"), h.index("Thread Instructions Executed")
 assert len(body) == len(ins), (len(body), len(ins))
 by_line = collections.defaultdict(lambda: [0, 0, 0])
