@@ -39,6 +39,13 @@ __global__ void __launch_bounds__(PH_THREADS, 8) rt_ao_phased_kernel(const __gri
     for (int i = tid; i < p.nshapes; i += PH_THREADS) s_shapes[i] = p.shapes[i];
 #pragma unroll 1
     for (int i = tid; i < 2 * p.AA; i += PH_THREADS) s_rand[i] = p.rand[i];
+    // Gamma of a pixel whose samples ALL returned the background (sky): its colour sum is one fixed value per
+    // (background, AA), so rt_sky_gamma_kernel forms the sum and its three pow() once -- when the background
+    // changes, not per frame -- and sky pixels (40 % of config 2, whole warps of them) compare and skip their
+    // own (pow is 9 % of this kernel's instructions).  pow is a pure function of the sum, so a non-sky pixel
+    // that happens to have the same sum gets the same bits.
+    __shared__ float s_sky[6];   // sum.rgb, gamma.rgb
+    if (tid < 6) s_sky[tid] = o.sky[tid];
     __syncthreads();
 
     const int lane = tid & 31, warp = tid >> 5;
@@ -194,7 +201,9 @@ __global__ void __launch_bounds__(PH_THREADS, 8) rt_ao_phased_kernel(const __gri
         }
 
         const float fAA = (float)p.AA;
-        const float4 c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+        float4 c = make_float4(s_sky[3], s_sky[4], s_sky[5], 0.0f);
+        if (!(ar == s_sky[0] && ag == s_sky[1] && ab == s_sky[2]))
+            c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
         o.color[pix] = c;
         if (o.gather) o.gather[pix] = c;   // rt_set_frame_target: the assembled frame, maybe over NVLink
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
@@ -217,6 +226,26 @@ __global__ void __launch_bounds__(PH_THREADS, 8) rt_ao_phased_kernel(const __gri
         atomicAdd(&st[ST_PRIMARY], (unsigned long long)v_pix);
         atomicAdd(&st[ST_JITTERED], (unsigned long long)v_pix * (unsigned)(p.AA - 1));
     }
+}
+
+// the colour sum of an all-background pixel and its gamma, for the shortcut above: same operations as the
+// per-pixel path (0 + bg + ... + bg in sample order, / AA, pow)
+__global__ void rt_sky_gamma_kernel(float4 bg, int AA, float *sky)
+{
+    const int c = threadIdx.x;
+    if (c >= 3) return;
+    const float b = (c == 0) ? bg.x : (c == 1) ? bg.y : bg.z;
+    float sum = 0.0f;
+#pragma unroll 1
+    for (int k = 0; k < AA; k++) sum += b;
+    sky[c] = sum;
+    sky[3 + c] = pow_f32(__fdiv_rn(sum, (float)AA), __fdiv_rn(1.0f, 2.2f));
+}
+
+cudaError_t launch_sky_gamma(float4 bg, int AA, float *sky, cudaStream_t s)
+{
+    rt_sky_gamma_kernel<<<1, 32, 0, s>>>(bg, AA, sky);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_ao_phased(const FrameParams &p, const TraceOut &o, cudaStream_t s)

@@ -33,6 +33,9 @@ struct rt_ctx {
     void *staging = nullptr; // npix * 16 bytes, layout conversions
     unsigned long long *stats = nullptr;
     unsigned *work = nullptr; // streaming AO kernel's unit counters
+    float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
+    float4 sky_bg{};
+    bool sky_valid = false;
     int ao_kernel = AO_KERNEL_PHASED; // RT_AO_KERNEL=tile|stream selects the earlier kernels (A/B profiling)
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
@@ -92,7 +95,7 @@ static void free_all(rt_ctx *c)
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
-    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->work);
+    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->work); cudaFree(c->sky);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
@@ -147,6 +150,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0(&c->staging, c->npix * sizeof(float4));
     alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     alloc0((void **)&c->work, 2 * sizeof(unsigned));
+    alloc0((void **)&c->sky, 6 * sizeof(float));
     if (const char *k = getenv("RT_AO_KERNEL")) {
         if (!strcmp(k, "tile")) c->ao_kernel = AO_KERNEL_TILE;
         else if (!strcmp(k, "stream")) c->ao_kernel = AO_KERNEL_STREAM;
@@ -176,7 +180,9 @@ void rt_destroy(rt_ctx *ctx) { free_all(ctx); }
 int rt_set_stream(rt_ctx *c, void *cuda_stream)
 {
     if (!c) return RT_EINVAL;
-    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    cudaStream_t ns = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    if (ns != c->stream) c->sky_valid = false; // rt_sky_gamma_kernel was ordered on the old stream
+    c->stream = ns;
     return RT_OK;
 }
 
@@ -292,6 +298,13 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     o.stats = c->stats;
     o.work = c->work;
     o.ao_kernel = c->ao_kernel;
+    o.sky = c->sky;
+    if (ao && (!c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0)) {
+        // first AO frame, or the background changed (scene toggle, src/main.cpp:229-255)
+        CU(c, launch_sky_gamma(p.bg, p.AA, c->sky, c->stream));
+        c->sky_bg = p.bg;
+        c->sky_valid = true;
+    }
     // mode 1: the trace output is raw; the post-processing pass writes the frame
     float4 *band_in_frame = c->frame_target ? c->frame_target + (size_t)c->cfg.band_y0 * c->cfg.width : nullptr;
     o.gather = (mode == RT_MODE_AO_PP) ? nullptr : band_in_frame;

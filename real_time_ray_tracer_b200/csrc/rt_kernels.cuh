@@ -81,6 +81,7 @@ struct TraceOut {
     unsigned long long *stats; // [STAT_STRIPES][ST_COUNT]
     unsigned *work;   // [2] unit counter + finished-warp counter of the streaming AO kernel (self re-arming)
     int ao_kernel;    // AO_KERNEL_*
+    const float *sky; // [6] all-background colour sum and its gamma (rt_sky_gamma_kernel), phased AO kernel
     float4 *gather;   // rt_set_frame_target: this band's rows inside a whole-frame image (maybe peer memory), or null
 };
 
@@ -126,6 +127,7 @@ cudaError_t launch_fence(const PeerBoxes &peers, int rank, int world, unsigned l
 cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_phased(const FrameParams &p, const TraceOut &o, cudaStream_t s);
+cudaError_t launch_sky_gamma(float4 bg, int AA, float *sky, cudaStream_t s);
 cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s);
 cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s);
 cudaError_t launch_transpose(const void *src, void *dst, int W, int rows, int elem_bytes, bool to_reference, cudaStream_t s);

@@ -165,13 +165,15 @@ __device__ __forceinline__ void ao_bounce(const FrameParams &p, const DevShape &
     pos = add3(p.cam, scale3(t, dir));
     normal = shape_normal(s, pos);
     const float refl = s.s3.w;
+    float3 v;   // one normalize for both flavours: a tile edge has lanes of both in one warp
     if (refl > 0.999f) {
-        dir = normalize3(add3(ru, normal));
+        v = add3(ru, normal);
     } else {
         float dn = dot3(dir, normal);
         float3 R = normalize3(sub3(dir, scale3(2.0f, scale3(dn, normal))));
-        dir = normalize3(add3(R, scale3(refl, ru)));
+        v = add3(R, scale3(refl, ru));
     }
+    dir = normalize3(v);
 }
 
 __device__ __forceinline__ float4 gamma_correct(float r, float g, float b)
