@@ -395,8 +395,25 @@ __device__ __forceinline__ float nb_weight(float4 nn, float nd, float nb, const 
 }
 
 constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 4;
+// tuning knobs, swept on B200 at config 4 (tools/gpu_pp_variants.sh; kernel ms):
+//   colours after the records, batch 4,  8 blocks/SM (64 regs)  0.398   <- the round's earlier version
+//   speculative colours,       batch 4,  6 blocks/SM (79 regs)  0.444
+//   speculative colours,       batch 2,  8 blocks/SM            0.355
+//   speculative colours,       batch 2, 10 blocks/SM (48 regs)  0.313   <- default
+//   speculative colours,       batch 1, 12 blocks/SM (40 regs)  0.318
+// The kernel is latency-bound on HBM (ncu: long_scoreboard 11 stall cycles per issue): resident warps buy more
+// than loads in flight per warp.
+#ifndef PP_SPECULATE
+#define PP_SPECULATE 1
+#endif
+#ifndef PP_MIN_BLOCKS
+#define PP_MIN_BLOCKS 10
+#endif
+#ifndef PP_BATCH
+#define PP_BATCH 2
+#endif
 
-__global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, 8) rt_ao_postprocess_kernel(const __grid_constant__ PostParams q)
+__global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_postprocess_kernel(const __grid_constant__ PostParams q)
 {
     const int x = blockIdx.x * PP_BLOCK_X + threadIdx.x;
     const int yl = blockIdx.y * PP_BLOCK_Y + threadIdx.y;
@@ -469,30 +486,35 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, 8) rt_ao_postprocess_k
 
             // temporal blend over the previous NF-1 ring slots (:175-201).  The shader walks the ring one
             // frame at a time and stops at the first rejected frame; done literally that is a chain of up to
-            // NF-1 dependent round trips to HBM.  Here the normal/depth records of up to four frames are
-            // requested together, their coefficients evaluated in ring order, and the colours of the accepted
-            // ones requested together: two round trips per batch, same arithmetic in the same order.
+            // NF-1 dependent round trips to HBM.  Here the normal/depth records AND the colours of PP_BATCH frames
+            // are requested together and the coefficients evaluated in ring order: one round trip per batch, same
+            // arithmetic in the same order (a colour whose frame is rejected is simply not used).
             float4 color_sum = z4;
             float denominator = 0.9f;
             bool go = true;
-            for (int i0 = 1; go && i0 < q.NF; i0 += 4) {
-                float4 cn[4];
-                float2 cd[4];
-                size_t off[4];
-                float coeff[4];
+            for (int i0 = 1; go && i0 < q.NF; i0 += PP_BATCH) {
+                float4 cn[PP_BATCH], hc[PP_BATCH];
+                float2 cd[PP_BATCH];
+                size_t off[PP_BATCH];
+                float coeff[PP_BATCH];
 #pragma unroll
-                for (int b = 0; b < 4; b++) {
+                for (int b = 0; b < PP_BATCH; b++) {
                     int cf = q.slot - (i0 + b);
                     if (cf < 0) cf += q.NF;
                     off[b] = (size_t)cf * plane + pix;
                     if (i0 + b < q.NF) {
                         cn[b] = q.ring_normal[off[b]];
                         cd[b] = q.ring_depth_xy[off[b]];
+#if PP_SPECULATE
+                        // 94 % of the evaluated history frames are accepted (config 4): ask for the colour with the
+                        // record instead of after it -- one round trip to HBM per batch instead of two
+                        hc[b] = q.ring_color[off[b]];
+#endif
                     }
                 }
                 int acc = 0;
 #pragma unroll
-                for (int b = 0; b < 4; b++) {
+                for (int b = 0; b < PP_BATCH; b++) {
                     if (go && i0 + b < q.NF) {
                         n_eval++;
                         float normal_dot = dot3(xyz(nn), xyz(cn[b]));
@@ -502,12 +524,13 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, 8) rt_ao_postprocess_k
                         if (coeff[b] > 0.85f) acc = b + 1; else go = false;
                     }
                 }
-                float4 hc[4];
+#if !PP_SPECULATE
 #pragma unroll
-                for (int b = 0; b < 4; b++)
+                for (int b = 0; b < PP_BATCH; b++)
                     if (b < acc) hc[b] = q.ring_color[off[b]];
+#endif
 #pragma unroll
-                for (int b = 0; b < 4; b++)
+                for (int b = 0; b < PP_BATCH; b++)
                     if (b < acc) {
                         color_sum = add4(color_sum, scale4(coeff[b], hc[b]));
                         denominator += coeff[b];

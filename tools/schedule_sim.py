@@ -76,3 +76,33 @@ if __name__ == "__main__":
     itE = rest[sel].sum(2).max(1)
     print("F tail stealing: tail iters/warp %.2f (own-samples-only %.2f), tail util %.3f" % (
         itF.mean(), itE.mean(), rest[sel].sum() / max(1, itF.sum() * 32)))
+    # G: S=2 head, tail pooled per BLOCK (4 warps = 16x8 pixels): survivors compacted into a block queue,
+    # lanes pull the next survivor when theirs ends (greedy list scheduling on 128 lanes)
+    H2, W2, AA2 = L.shape
+    Hb, Wb = H2 // 8 * 8, W2 // 16 * 16
+    blk = np.maximum(L[:Hb, :Wb] - 2, 0).reshape(Hb // 8, 8, Wb // 16, 16, AA2).transpose(0, 2, 1, 3, 4).reshape(-1, 128 * AA2)
+    selb = np.random.default_rng(2).choice(len(blk), size=min(len(blk), 3000), replace=False)
+    itG = np.array([greedy(r, 128) for r in blk[selb]])
+    # same but lanes keep to batches: each warp takes 32 survivors, runs them all to the end, then the next 32
+    def batched(tasks):
+        tasks = [x for x in tasks if x > 0]
+        warps = np.zeros(4, np.int64)
+        for i in range(0, len(tasks), 32):
+            k = warps.argmin(); warps[k] += max(tasks[i:i + 32])
+        return warps.max() if len(tasks) else 0
+    itGb = np.array([batched(r) for r in blk[selb]])
+    per_warp_now = rest.sum(2).max(1).mean()
+    print("G block-pooled tail: rounds/warp %.2f (refill) / %.2f (batches of 32)   vs per-lane now %.2f ; perfect %.2f" % (
+        itG.mean(), itGb.mean(), per_warp_now, blk[selb].sum() / 128 / len(selb)))
+    # H: total WARP-rounds per block (what costs issue slots): now vs survivors compacted into few warps
+    def one_warp_refill(tasks):
+        return greedy([x for x in tasks if x > 0], 32)
+    def batches_total(tasks):
+        tasks = [x for x in tasks if x > 0]
+        return sum(max(tasks[i:i + 32]) for i in range(0, len(tasks), 32))
+    now_b = np.maximum(L[:Hb, :Wb] - 2, 0).reshape(Hb // 8, 2, 4, Wb // 16, 2, 8, AA2).transpose(0, 3, 1, 4, 2, 5, 6).reshape(-1, 4, 32, AA2)
+    now_total = now_b.sum(3).max(2).sum(1)            # per block: sum over its 4 warps of max-over-lanes
+    cw = np.array([one_warp_refill(r) for r in blk[selb]])
+    cb = np.array([batches_total(r) for r in blk[selb]])
+    print("H warp-rounds per block: now %.2f | compacted, batches of 32 (no refill) %.2f | one warp with refill %.2f | perfect %.2f" % (
+        now_total.mean(), cb.mean(), cw.mean(), blk[selb].sum() / 32 / len(selb)))
