@@ -178,6 +178,17 @@ int rt_download(rt_ctx *ctx, int buffer, int slot, int layout, void *host, size_
 int rt_upload(rt_ctx *ctx, int buffer, int slot, int layout, const void *host, size_t bytes);
 /* asynchronous row-major download into pinned host memory on the context's stream */
 int rt_download_async(rt_ctx *ctx, int buffer, int slot, void *pinned_host, size_t bytes);
+/* "Selective copying back from the GPU" (the reference's README to-do; src/main.cpp:613-617 maps the whole
+ * 55.8 MB struct back every frame).  The displayable image of pixels[slot] as 8-bit RGBA, row-major, y = 0 at
+ * the bottom: byte = (unsigned char)(min(max(c, 0), 1) * 255 + 0.5), NaN -> 0, alpha 255 -- the quantisation
+ * the colour-parity metric is defined on.  Converted on the device on the context's stream, then copied into
+ * pinned host memory on an internal copy stream, so the transfer (4 bytes per pixel instead of 16) overlaps
+ * the kernels of the next frame; two device staging halves alternate, so up to two read-backs may be in
+ * flight.  bytes = band_rows * width * 4.  rt_synchronize waits for outstanding read-backs too. */
+int rt_download_rgba8_async(rt_ctx *ctx, int slot, void *pinned_host, size_t bytes);
+/* blocks the host until the read-backs issued so far have landed, except the newest `keep_in_flight` (0 or 1)
+ * -- the consumer of a double-buffered pinned ring calls it with 1 before it reuses the older buffer */
+int rt_readback_wait(rt_ctx *ctx, int keep_in_flight);
 /* raw device pointer of a row-major plane of this band (for NCCL / framework interop) */
 int rt_device_ptr(rt_ctx *ctx, int buffer, int slot, void **out_ptr, size_t *out_bytes);
 

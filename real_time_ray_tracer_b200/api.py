@@ -144,6 +144,20 @@ class RayTracer:
     def download_async(self, buffer: int, slot: int, pinned_ptr: int, nbytes: int):
         self._check(self.lib.rt_download_async(self.h, buffer, slot, C.c_void_p(pinned_ptr), nbytes))
 
+    def download_rgba8_async(self, slot: int, pinned_ptr: int, nbytes: int):
+        """rt_download_rgba8_async: the 8-bit image of pixels[slot] into pinned host memory, on the stream"""
+        self._check(self.lib.rt_download_rgba8_async(self.h, slot, C.c_void_p(pinned_ptr), nbytes))
+
+    def readback_wait(self, keep_in_flight: int = 0):
+        self._check(self.lib.rt_readback_wait(self.h, keep_in_flight))
+
+    def download_rgba8(self, slot: int) -> np.ndarray:
+        """uint8 [rows, W, 4] image of pixels[slot] (synchronises)"""
+        out = np.empty((self.rows, self.W, 4), dtype=np.uint8)
+        self.download_rgba8_async(slot, out.ctypes.data, out.nbytes)
+        self.synchronize()
+        return out
+
     def device_ptr(self, buffer: int, slot: int = 0):
         p, n = C.c_void_p(), C.c_size_t()
         self._check(self.lib.rt_device_ptr(self.h, buffer, slot, C.byref(p), C.byref(n)))

@@ -51,6 +51,10 @@ struct rt_ctx {
     bool halo_direct = false;
     float4 *frame_target = nullptr; // rt_set_frame_target: whole-frame image, maybe peer memory
     float4 *frame_target_post = nullptr; // the target the pending mode-1 frame was rendered for
+    int rgba8_flip = 0;
+    cudaStream_t copy_stream = nullptr;   // read-backs of rt_download_rgba8_async overlap the next frame
+    cudaEvent_t ev_quant[2] = { nullptr, nullptr }, ev_copy[2] = { nullptr, nullptr };
+    bool copy_pending[2] = { false, false };
     bool timing = false;
     cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
     bool ev_trace_valid = false, ev_post_valid = false;
@@ -99,6 +103,11 @@ static void free_all(rt_ctx *c)
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
+    for (int i = 0; i < 2; i++) {
+        if (c->ev_quant[i]) cudaEventDestroy(c->ev_quant[i]);
+        if (c->ev_copy[i]) cudaEventDestroy(c->ev_copy[i]);
+    }
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -139,6 +148,11 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
         if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
     };
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+        e = cudaEventCreateWithFlags(&c->ev_quant[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming);
+    }
     c->stream = c->own_stream;
     // value-initialised like the reference's ssbo_CPUMEM (src/main.cpp:810): the ring starts at zero
     alloc0((void **)&c->ring_color, ring * sizeof(float4));
@@ -191,6 +205,8 @@ int rt_synchronize(rt_ctx *c)
     if (!c) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
     CU(c, cudaStreamSynchronize(c->stream));
+    CU(c, cudaStreamSynchronize(c->copy_stream)); // outstanding rt_download_rgba8_async read-backs
+    c->copy_pending[0] = c->copy_pending[1] = false;
     return RT_OK;
 }
 
@@ -602,6 +618,39 @@ int rt_download_async(rt_ctx *c, int buffer, int slot, void *pinned_host, size_t
     if (rc != RT_OK) return rc;
     if (bytes != c->npix * elem) return fail(c, RT_EINVAL, "rt_download_async: expected %zu bytes, got %zu", c->npix * elem, bytes);
     CU(c, cudaMemcpyAsync(pinned_host, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    return RT_OK;
+}
+
+int rt_download_rgba8_async(rt_ctx *c, int slot, void *pinned_host, size_t bytes)
+{
+    if (!c || !pinned_host) return RT_EINVAL;
+    if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
+    if (bytes != c->npix * 4) return fail(c, RT_EINVAL, "rt_download_rgba8_async: expected %zu bytes, got %zu", c->npix * 4, bytes);
+    CU(c, cudaSetDevice(c->cfg.device));
+    // Two alternating halves of the staging plane.  The conversion runs on the context's stream (after the
+    // frame's kernels); the PCIe copy runs on an internal copy stream behind an event, so it overlaps the next
+    // frame's kernels; a half is converted into again only after the copy that last read it has finished.
+    const int h = c->rgba8_flip;
+    c->rgba8_flip ^= 1;
+    uchar4 *dst = (uchar4 *)c->staging + (size_t)h * ((c->npix + 3) & ~(size_t)3); // 16-byte aligned halves
+    if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));
+    CU(c, launch_quantize_rgba8(c->ring_color + (size_t)slot * c->npix, dst, c->npix, c->stream));
+    CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    CU(c, cudaMemcpyAsync(pinned_host, dst, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
+    c->copy_pending[h] = true;
+    return RT_OK;
+}
+
+int rt_readback_wait(rt_ctx *c, int keep_in_flight)
+{
+    if (!c) return RT_EINVAL;
+    if (keep_in_flight < 0 || keep_in_flight > 1) return fail(c, RT_EINVAL, "rt_readback_wait: keep_in_flight must be 0 or 1");
+    CU(c, cudaSetDevice(c->cfg.device));
+    const int newest = c->rgba8_flip ^ 1, older = c->rgba8_flip;
+    if (c->copy_pending[older]) { CU(c, cudaEventSynchronize(c->ev_copy[older])); c->copy_pending[older] = false; }
+    if (keep_in_flight == 0 && c->copy_pending[newest]) { CU(c, cudaEventSynchronize(c->ev_copy[newest])); c->copy_pending[newest] = false; }
     return RT_OK;
 }
 

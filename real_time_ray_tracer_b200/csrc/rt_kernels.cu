@@ -671,6 +671,31 @@ cudaError_t launch_split_depth(const float4 *in, float2 *xy, float *w, size_t n,
     return cudaGetLastError();
 }
 
+// float4 colour -> 8-bit RGBA for rt_download_rgba8_async (one thread = four pixels: 64 B in, 16 B out)
+__device__ __forceinline__ unsigned quant8(float c)
+{
+    float x = (c > 0.0f) ? c : 0.0f; // NaN -> 0
+    x = (x < 1.0f) ? x : 1.0f;
+    return (unsigned)(x * 255.0f + 0.5f);
+}
+__device__ __forceinline__ unsigned quant_px(float4 c) { return quant8(c.x) | (quant8(c.y) << 8) | (quant8(c.z) << 16) | 0xff000000u; }
+__global__ void __launch_bounds__(256) rt_quantize_rgba8_kernel(const float4 *__restrict__ src, unsigned *__restrict__ dst, size_t n)
+{
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i + 3 < n) {
+        uint4 o;
+        o.x = quant_px(src[i]); o.y = quant_px(src[i + 1]); o.z = quant_px(src[i + 2]); o.w = quant_px(src[i + 3]);
+        *reinterpret_cast<uint4 *>(dst + i) = o;
+    } else {
+        for (size_t k = i; k < n; k++) dst[k] = quant_px(src[k]);
+    }
+}
+cudaError_t launch_quantize_rgba8(const float4 *src, uchar4 *dst, size_t n, cudaStream_t s)
+{
+    rt_quantize_rgba8_kernel<<<(unsigned)((n + 1023) / 1024), 256, 0, s>>>(src, (unsigned *)dst, n);
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------------
 // diagnostics
 // ---------------------------------------------------------------------------------------------

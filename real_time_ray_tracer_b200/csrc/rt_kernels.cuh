@@ -134,6 +134,7 @@ cudaError_t launch_transpose(const void *src, void *dst, int W, int rows, int el
 cudaError_t launch_expand_depth(const float2 *xy, const float *w, float4 *out, size_t n, cudaStream_t s);
 cudaError_t launch_split_depth(const float4 *in, float2 *xy, float *w, size_t n, cudaStream_t s);
 cudaError_t launch_eval_math(int kind, const float *a, const float *b, float *out, size_t n, cudaStream_t s);
+cudaError_t launch_quantize_rgba8(const float4 *src, uchar4 *dst, size_t n, cudaStream_t s);
 cudaError_t launch_fp32_peak(float *sink, int blocks, int iters, cudaStream_t s);
 
 } // namespace rt

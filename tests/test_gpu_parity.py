@@ -495,6 +495,27 @@ def test_equal_distance_tie_goes_to_the_earlier_shape(order, mode):
         o.close()
 
 
+def test_rgba8_read_back_is_the_quantised_colour_plane():
+    """rt_download_rgba8_async: byte = (uint8)(min(max(c, 0), 1) * 255 + 0.5), alpha 255; scene6 has emissive
+    colours far above 1 (clamped) and the odd pixel count exercises the kernel's 4-pixel tail."""
+    W, H, AA = 203, 117, 4
+    sc = Scenario("scene6")
+    with rtb.RayTracer(W, H, AA) as rt:
+        rt.upload_scene(sc.shapes, sc.n)
+        for k in range(3):      # consecutive calls alternate the device staging halves
+            slot, u, rb = sc.next(2, AA)
+            rt.render_frame(2, u, rb)
+            c = rt.download(rtb.BUF_COLOR, slot)
+            want = (np.minimum(np.maximum(np.nan_to_num(c[..., :3], nan=0.0), 0.0), 1.0) * np.float32(255.0)
+                    + np.float32(0.5)).astype(np.uint8)
+            got = rt.download_rgba8(slot)
+            assert got.shape == (H, W, 4) and (got[..., 3] == 255).all()
+            assert np.array_equal(got[..., :3], want)
+            assert want.max() == 255 and want.min() == 0
+        with pytest.raises(rtb.RtError):
+            rt.download_rgba8_async(0, 1, 12)
+
+
 def test_full_size_properties_1080p():
     """BASELINE config 2 at full size, where the oracle is too slow for a tight loop: determinism (same inputs,
     same bits), ray-counter identities, and agreement of the un-jittered hit index between modes 2 and 3."""
