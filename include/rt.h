@@ -60,6 +60,15 @@ enum {
     RT_EDGE_CLEAN = 1   /* intended: x + 1 < WIDTH, y > 0 */
 };
 
+/* rt_config.flags */
+enum {
+    /* Extension (reference README, "phong shaders should store normals and depth like AO shaders"): modes 3
+     * and 4 also write normals_buffer[slot] = (n, 1) and depth_buffer[slot] = (t, path segments after the
+     * first, 0, 1) of the camera ray's hit, zeros on a miss.  Off (0) = the shaders' behaviour: modes 3/4
+     * leave both buffers as the last AO frame wrote them (p_compute.glsl:223-246). */
+    RT_FLAG_PHONG_GBUFFER = 1
+};
+
 /* buffers of rt_download / rt_upload / rt_device_ptr */
 enum {
     RT_BUF_COLOR = 0,     /* pixels[slot]          float4 per pixel */
@@ -112,7 +121,8 @@ typedef struct rt_config {
     int32_t band_rows;       /* rows owned; 0 = height - band_y0 (whole image when band_y0 = 0) */
     int32_t band_index;      /* position of this band in the frame, 0 .. band_count-1 */
     int32_t band_count;      /* number of bands the frame is split into (1 = no halo exchange) */
-    int32_t reserved[5];     /* must be 0 */
+    int32_t flags;           /* RT_FLAG_* */
+    int32_t reserved[4];     /* must be 0 */
 } rt_config;
 
 /* ray / work counters accumulated since rt_reset_stats; "ray" = one closest-hit traversal of the

@@ -76,6 +76,7 @@ typedef struct rto_ctx {
     int nshapes;
     rto_stats stats;
     int nthreads;
+    int phong_gbuffer;      /* extension (README to-do): modes 3/4 also write normals/depth of the first hit */
     unsigned char *pathlen; /* optional analysis aid: segments walked per (pixel, sample), [y][x][aa] */
 } rto_ctx;
 
@@ -130,6 +131,12 @@ void rto_destroy(rto_ctx *c)
     if (!c) return;
     free(c->base); free(c->raw); free(c->image); free(c->hit_index); free(c);
 }
+
+/* Extension beyond the shaders (reference README: "phong shaders should store normals and depth like AO
+ * shaders"): with on != 0 modes 3/4 write normals_buffer = (n, 1) and depth_buffer = (t, segments after the
+ * first, 0, 1) of the un-jittered first hit, zeros on a miss -- the records ao_compute.glsl:222-229,249-253
+ * write, with one sample. */
+void rto_set_phong_gbuffer(rto_ctx *c, int on) { if (c) c->phong_gbuffer = on; }
 
 /* analysis aid (schedule simulations in DESIGN.md): caller-owned buffer of W*H*AA bytes, or NULL */
 void rto_set_pathlen_buffer(rto_ctx *c, unsigned char *buf) { if (c) c->pathlen = buf; }
@@ -402,6 +409,14 @@ static void phong_pixel(rto_ctx *c, unsigned x, unsigned y, rto_stats *st)
         att.w = 0.0f; /* p_compute builds vec4(xyz * k, 0) */
         col = phong_shade(c, att, curr_pos, dir, normal, lit);
         st->shaded++;
+        if (c->phong_gbuffer) {
+            c->base[c->normals_off + gidx(c, frame, x, y)] = rtr_mk4(normal.x, normal.y, normal.z, 1.0f);
+            c->base[c->depth_off + gidx(c, frame, x, y)] = rtr_mk4(t, 0.0f, 0.0f, 1.0f);
+        }
+    }
+    if (c->phong_gbuffer && ind == -1) {
+        c->base[c->normals_off + gidx(c, frame, x, y)] = rtr_mk4(0, 0, 0, 0);
+        c->base[c->depth_off + gidx(c, frame, x, y)] = rtr_mk4(0, 0, 0, 0);
     }
     rtr_v4 zero = rtr_mk4(0, 0, 0, 0);
     col = gamma_correct(rtr_add4(zero, col));
@@ -426,10 +441,13 @@ static void hybrid_pixel(rto_ctx *c, unsigned x, unsigned y, rto_stats *st)
     float cw = 0.0f;     /* c in hybrid() */
     float a2w = 0.0f;    /* lighting_buffer[2].w */
     int first_ind = -1;
+    int segments = 0;
+    rtr_v4 g_normal = rtr_mk4(0, 0, 0, 0), g_depth = rtr_mk4(0, 0, 0, 0);
     for (int i = RD; i > 0; i--) {
         float t;
         int ind = closest_hit(c, pos, dir, 0.001f, &t);
         st->rays_closest++;
+        segments++;
         if (i == RD) first_ind = ind;
         rtr_v4 a0;
         int stop = 0;
@@ -443,6 +461,10 @@ static void hybrid_pixel(rto_ctx *c, unsigned x, unsigned y, rto_stats *st)
             rtr_v3 normal = shape_normal(c, ind, curr_pos);
             a0 = phong_shade(c, att, curr_pos, dir, normal, lit);
             st->shaded++;
+            if (i == RD) {
+                g_normal = rtr_mk4(normal.x, normal.y, normal.z, 1.0f);
+                g_depth = rtr_mk4(t, 0.0f, 0.0f, 1.0f);
+            }
             float reflectivity = 1.0f - SHAPE(c, ind, 3).w;
             if (reflectivity < 0.001f) {
                 stop = 1;
@@ -464,6 +486,11 @@ static void hybrid_pixel(rto_ctx *c, unsigned x, unsigned y, rto_stats *st)
             cw = cw * a2w;
         }
         if (stop) break;
+    }
+    if (c->phong_gbuffer) {
+        if (first_ind != -1) g_depth.y = (float)(segments - 1);
+        c->base[c->normals_off + gidx(c, frame, x, y)] = g_normal;
+        c->base[c->depth_off + gidx(c, frame, x, y)] = g_depth;
     }
     rtr_v4 zero = rtr_mk4(0, 0, 0, 0);
     result = gamma_correct(rtr_add4(zero, result));

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "librt_b200.so")
 RT_OK, RT_EINVAL, RT_ENODEVICE, RT_ENOMEM, RT_ECUDA, RT_ESTATE = 0, -1, -2, -3, -4, -5
 MODE_AO_PP, MODE_AO, MODE_PHONG, MODE_HYBRID = 1, 2, 3, 4
 EDGE_FLAT32, EDGE_CLEAN = 0, 1
+FLAG_PHONG_GBUFFER = 1
 BUF_COLOR, BUF_NORMAL, BUF_DEPTH, BUF_HIT_INDEX, BUF_IMAGE, BUF_RAW_COLOR, BUF_DEPTH_XY, BUF_DEPTH_W = range(8)
 LAYOUT_ROW_MAJOR, LAYOUT_REFERENCE = 0, 1
 MAX_SHAPES, MAX_AA, MAX_FRAMES = 10, 16, 16
@@ -19,7 +20,7 @@ MAX_SHAPES, MAX_AA, MAX_FRAMES = 10, 16, 16
 class rt_config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("width", "height", "aa", "recursion_depth", "num_frames", "edge_mode",
                                          "device", "band_y0", "band_rows", "band_index", "band_count")] + \
-               [("reserved", C.c_int32 * 5)]
+               [("flags", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 STAT_COUNTERS = ("rays_closest", "rays_shadow", "primary", "jittered", "seg_nonterminal", "seg_terminal",

@@ -122,6 +122,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     if (cfg->num_frames < 1 || cfg->num_frames > RT_MAX_FRAMES) return fail(nullptr, RT_EINVAL, "rt_create: num_frames must be 1..%d", RT_MAX_FRAMES);
     if (cfg->edge_mode != RT_EDGE_FLAT32 && cfg->edge_mode != RT_EDGE_CLEAN) return fail(nullptr, RT_EINVAL, "rt_create: bad edge_mode");
     for (int r : cfg->reserved) if (r != 0) return fail(nullptr, RT_EINVAL, "rt_create: reserved fields must be 0");
+    if (cfg->flags & ~RT_FLAG_PHONG_GBUFFER) return fail(nullptr, RT_EINVAL, "rt_create: unknown flags 0x%x", cfg->flags);
     int rows = cfg->band_rows ? cfg->band_rows : cfg->height - cfg->band_y0;
     if (cfg->band_y0 < 0 || rows <= 0 || cfg->band_y0 + rows > cfg->height) return fail(nullptr, RT_EINVAL, "rt_create: band outside the image");
     int bcount = cfg->band_count ? cfg->band_count : 1;
@@ -294,6 +295,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     }
     p.slot = slot; p.nshapes = nobj; p.edge_mode = c->cfg.edge_mode; p.mode = mode;
     p.band_index = c->cfg.band_index; p.band_count = c->cfg.band_count;
+    p.pad0 = c->cfg.flags;   // FrameParams::pad0 carries rt_config.flags
     p.llc = f3(u->llc_minus_campos); p.horiz = f3(u->horizontal); p.vert = f3(u->vertical);
     p.cam = f3(u->camera_location); p.light = f3(u->light_pos);
     p.bg = make_float4(u->background.x, u->background.y, u->background.z, u->background.w);

@@ -230,6 +230,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_co
         float t;
         int ind = closest_hit(p, p.cam, dir, 0.0f, t);
         float4 col;
+        float4 g_normal = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         if (ind < 0) {
             col = p.bg;
         } else {
@@ -240,6 +241,12 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_co
             float3 normal = shape_normal(s, curr_pos);
             float4 att = make_float4(s.col.x, s.col.y, s.col.z, 0.0f);
             col = phong_shade(p, att, curr_pos, dir, normal, lit);
+            g_normal = make_float4(normal.x, normal.y, normal.z, 1.0f);
+        }
+        if (p.pad0 & RT_FLAG_PHONG_GBUFFER) {   // extension: the record ao_compute.glsl:222-229,249-253 writes
+            o.normal[pix] = g_normal;
+            o.depth_xy[pix] = make_float2(ind < 0 ? 0.0f : t, 0.0f);
+            o.depth_w[pix] = ind < 0 ? 0.0f : 1.0f;
         }
         // result_color = vec4(0) + phong(dir)
         const float4 c = gamma_correct(0.0f + col.x, 0.0f + col.y, 0.0f + col.z);
@@ -269,6 +276,8 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_c
         float4 result = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         float cw = 0.0f, a2w = 0.0f;
         int first_ind = -1;
+        float4 g_normal = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float g_t = 0.0f;
         // hybrid(): h_compute.glsl:269-297, first segment peeled there, folded into the loop here
         for (int i = p.RD; i > 0; i--) {
             float t;
@@ -287,6 +296,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_c
                 float3 normal = shape_normal(s, curr_pos);
                 a0 = phong_shade(p, s.col, curr_pos, dir, normal, lit);
                 n_shaded++;
+                if (i == p.RD) { g_normal = make_float4(normal.x, normal.y, normal.z, 1.0f); g_t = t; }
                 float reflectivity = 1.0f - s.s3.w;
                 if (reflectivity < 0.001f) {
                     stop = true;
@@ -311,6 +321,11 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_c
         o.color[pix] = c;
         if (o.gather) o.gather[pix] = c;
         o.hit[pix] = first_ind;
+        if (p.pad0 & RT_FLAG_PHONG_GBUFFER) {
+            o.normal[pix] = g_normal;
+            o.depth_xy[pix] = make_float2(g_t, first_ind < 0 ? 0.0f : (float)(n_rays - 1));
+            o.depth_w[pix] = first_ind < 0 ? 0.0f : 1.0f;
+        }
     }
     const int idx[6] = { ST_RAYS_CLOSEST, ST_RAYS_SHADOW, ST_SHADED, ST_REFLECTIVE, ST_PIXELS, ST_PRIMARY };
     unsigned val[6] = { n_rays, n_shaded, n_shaded, n_refl, active ? 1u : 0u, active ? 1u : 0u };

@@ -32,7 +32,7 @@ struct FrameParams {
     int y0, rows; // row band [y0, y0 + rows)
     int slot, nshapes, edge_mode, mode;
     int band_index, band_count;
-    int pad0;
+    int pad0;   // rt_config.flags (RT_FLAG_*)
     float fW, fH, invW, invH; // (float)W, (float)H and their correctly rounded reciprocals (host-computed)
     float3 llc, horiz, vert, cam, light;
     float4 bg;

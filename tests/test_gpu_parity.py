@@ -495,6 +495,37 @@ def test_equal_distance_tie_goes_to_the_earlier_shape(order, mode):
         o.close()
 
 
+@pytest.mark.parametrize("scene", ["scene1", "scene5"])
+def test_phong_modes_gbuffer_extension(scene):
+    """RT_FLAG_PHONG_GBUFFER (the reference README's to-do "phong shaders should store normals and depth like AO
+    shaders"): modes 3/4 write the first hit's normal and (t, segments after the first, 0, 1); without the flag
+    they leave both buffers alone, like p_compute.glsl / h_compute.glsl."""
+    from real_time_ray_tracer_b200 import _lib as L
+
+    W, H, AA = 131, 77, 4
+    for flags in (L.FLAG_PHONG_GBUFFER, 0):
+        sc = Scenario(scene, light_movement=True)
+        with rtb.RayTracer(W, H, AA, flags=flags) as rt:
+            o = orc.Oracle(W, H, AA, phong_gbuffer=bool(flags))
+            rt.upload_scene(sc.shapes, sc.n)
+            o.set_scene(sc.shapes, sc.n)
+            for mode in (2, 3, 4, 3):
+                slot, u, rb = sc.next(mode, AA)
+                rt.render_frame(mode, u, rb)
+                o.render(mode, u, rb)
+                check_frame(rt, o, slot, mode, f"{scene} flags {flags}")
+            if flags:
+                n = rt.download(rtb.BUF_NORMAL, slot)
+                d = rt.download(rtb.BUF_DEPTH, slot)
+                hit = rt.download(rtb.BUF_HIT_INDEX) >= 0
+                assert np.array_equal(n[..., 3] == 1.0, hit) and np.array_equal(d[..., 3] == 1.0, hit)
+                assert np.allclose(np.linalg.norm(n[hit][:, :3], axis=1), 1.0, atol=1e-6)
+                assert (d[hit][:, 0] > 0).all() and (d[~hit] == 0).all()
+            o.close()
+    with pytest.raises(rtb.RtError):
+        rtb.RayTracer(W, H, AA, flags=0x40)
+
+
 def test_rgba8_read_back_is_the_quantised_colour_plane():
     """rt_download_rgba8_async: byte = (uint8)(min(max(c, 0), 1) * 255 + 0.5), alpha 255; scene6 has emissive
     colours far above 1 (clamped) and the odd pixel count exercises the kernel's 4-pixel tail."""

@@ -103,3 +103,35 @@ def test_ray_counter_identities():
     assert st["rays_closest"] == st["seg_terminal"] + st["seg_nonterminal"]
     assert st["seg_terminal"] <= W * H * AA  # a sample may run out of depth instead of terminating
     o.close()
+
+
+def test_phong_gbuffer_extension_is_off_by_default_and_consistent_when_on():
+    """oracle side of RT_FLAG_PHONG_GBUFFER: off = modes 3/4 never touch normals/depth (the shaders' behaviour,
+    p_compute.glsl:223-246); on = mode 3 writes the same first-hit normal and t that mode 2's un-jittered sample
+    writes (ao_compute.glsl:222-229), and mode 4 adds the reflection-segment count."""
+    from oracle import oracle as orc
+    from tests.util import Scenario, same_bits
+
+    W, H, AA = 96, 64, 1
+    sc = Scenario("scene1")
+    slot, u, rb = sc.next(2, AA)
+    ref = orc.Oracle(W, H, AA)
+    ref.set_scene(sc.shapes, sc.n)
+    ref.render(2, u, rb)
+    n_ao, d_ao = ref.get(orc.NORMALS, slot), ref.get(orc.DEPTH, slot)
+    off = orc.Oracle(W, H, AA)
+    off.set_scene(sc.shapes, sc.n)
+    off.render(3, u, None)
+    assert not off.get(orc.NORMALS, slot).any() and not off.get(orc.DEPTH, slot).any()
+    on = orc.Oracle(W, H, AA, phong_gbuffer=True)
+    on.set_scene(sc.shapes, sc.n)
+    on.render(3, u, None)
+    # AO uses t > 0.0001, Phong t > 0: identical first hits from the default camera
+    assert same_bits(on.get(orc.NORMALS, slot), n_ao)
+    assert same_bits(on.get(orc.DEPTH, slot)[..., [0, 3]], d_ao[..., [0, 3]])
+    on.render(4, u, None)
+    d4 = on.get(orc.DEPTH, slot)
+    hit = on.get(orc.HIT_INDEX) >= 0
+    assert same_bits(d4[..., 0], d_ao[..., 0]) and (d4[..., 1][hit] >= 0).all() and d4[..., 1].max() >= 1
+    for o in (ref, off, on):
+        o.close()

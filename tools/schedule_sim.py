@@ -106,3 +106,23 @@ if __name__ == "__main__":
     cb = np.array([batches_total(r) for r in blk[selb]])
     print("H warp-rounds per block: now %.2f | compacted, batches of 32 (no refill) %.2f | one warp with refill %.2f | perfect %.2f" % (
         now_total.mean(), cb.mean(), cw.mean(), blk[selb].sum() / 32 / len(selb)))
+    # I: tail in a SECOND kernel over compacted pixels: a pixel with any survivor becomes one queue entry (its
+    # four sample records), one thread per entry runs the same per-lane flattened tail; entries are queued in block
+    # order (blocks append with one atomic), so a warp of the tail kernel holds 32 spatially close pixels
+    per_px = np.maximum(L[:Hb, :Wb] - 2, 0).sum(2)                       # tail rounds per pixel
+    blocks = per_px.reshape(Hb // 8, 8, Wb // 16, 16).transpose(0, 2, 1, 3).reshape(-1, 128)
+    q = np.concatenate([b[b > 0] for b in blocks])                        # queue order
+    nq = len(q)
+    pad = (-nq) % 32
+    qq = np.concatenate([q, np.zeros(pad, q.dtype)]).reshape(-1, 32)
+    tail_rounds = qq.max(1).sum()
+    now_rounds = now_b.sum(3).max(2).sum()
+    print("I compacted-pixel tail kernel: queued pixels %.3f of all, warp-rounds %d vs now %d (x%.2f), lane util %.3f" % (
+        nq / per_px.size, tail_rounds, now_rounds, now_rounds / tail_rounds, q.sum() / (tail_rounds * 32)))
+    # with the queue sorted by cost inside each group of 1024 entries (a block of the tail kernel sorting its slice)
+    def sorted_rounds(g):
+        s = np.sort(g)[::-1]
+        s = np.concatenate([s, np.zeros((-len(s)) % 32, s.dtype)]).reshape(-1, 32)
+        return s.max(1).sum()
+    tr2 = sum(sorted_rounds(q[i:i + 1024]) for i in range(0, nq, 1024))
+    print("  ... entries sorted by remaining work within slices of 1024: warp-rounds %d (x%.2f)" % (tr2, now_rounds / tr2))
