@@ -348,7 +348,10 @@ def run_b200(args) -> None:
                              "ring slot (8 x %.0f MB > 126 MB L2)" % (W * H * 44 / 1e6)},
             "rays_per_frame": rays / K,
             "roofline": roof, "clocks": clocks,
-            "gpu_launches": K * (1 if mode != 1 else 3) * world,
+            # this library's kernels per frame and rank: trace (+ halo pack + post-process in mode 1), plus the
+            # rt_fence kernels of linked bands (one per frame, two in mode 1)
+            "gpu_launches": K * world * ((1 if mode != 1 else 3)
+                                         + ((1 if mode != 1 else 2) if (direct is not None and direct.halo_direct) else 0)),
         }
         if mode == 1 and pp_ms:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(

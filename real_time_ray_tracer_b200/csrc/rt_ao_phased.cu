@@ -25,11 +25,18 @@
 
 namespace rt {
 
-constexpr int PH_TILE_W = 16, PH_TILE_H = 8, PH_THREADS = 128;
+#ifndef PH_THREADS_N
+#define PH_THREADS_N 128
+#endif
+// block = 128 threads: 2x2 warps (16x8 pixels); 64: 2x1 warps (16x4); 32: one warp (8x4)
+constexpr int PH_THREADS = PH_THREADS_N;
+constexpr int PH_WARPS_X = (PH_THREADS >= 64) ? 2 : 1, PH_WARPS_Y = PH_THREADS / 32 / PH_WARPS_X;
+constexpr int PH_TILE_W = 8 * PH_WARPS_X, PH_TILE_H = 4 * PH_WARPS_Y;
+constexpr int PH_MIN_BLOCKS = 1024 / PH_THREADS;
 constexpr int AO_CHUNK = 4;     // samples whose state is parked in shared memory at a time
 constexpr int ST_FIELDS = 8;    // survivor: dir.xyz, t, ids, ru.xyz   finished: colour.rgb, terminal depth
 
-__global__ void __launch_bounds__(PH_THREADS, 8) rt_ao_phased_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel(const __grid_constant__ FrameParams p, TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     __shared__ float4 s_rand[2 * RT_MAX_AA];
@@ -49,8 +56,8 @@ __global__ void __launch_bounds__(PH_THREADS, 8) rt_ao_phased_kernel(const __gri
     __syncthreads();
 
     const int lane = tid & 31, warp = tid >> 5;
-    const int x = blockIdx.x * PH_TILE_W + ((warp & 1) << 3) + (lane & 7);
-    const int yl = blockIdx.y * PH_TILE_H + ((warp >> 1) << 2) + (lane >> 3);
+    const int x = blockIdx.x * PH_TILE_W + ((warp % PH_WARPS_X) << 3) + (lane & 7);
+    const int yl = blockIdx.y * PH_TILE_H + ((warp / PH_WARPS_X) << 2) + (lane >> 3);
     const bool active = (x < p.W) && (yl < p.rows);
     unsigned n_nonterm = 0, n_term = 0;
 
