@@ -311,7 +311,10 @@ def run_b200(args) -> None:
     # ---- end to end through the public API with HOST buffers -----------------------------------
     e2e = None
     if args.e2e:
-        e2e = run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, min(K, 64), barrier, direct)
+        if world > 1 and direct is not None and not args.e2e_via_rank0:
+            e2e = run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, min(K, 64), barrier)
+        else:
+            e2e = run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, min(K, 64), barrier, direct)
 
     e2e_rgba8 = None
     if args.e2e and world == 1:
@@ -462,6 +465,61 @@ def run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, steps, ba
             "d2h_bytes_per_step": int(W * H * 16),
             "what": "upload_scene + uniforms + rand_buffer from host, render (+post-process, halo, gather), float4 "
                     "colour image read back to pinned host memory; read-back of frame k overlaps frame k+1"}
+
+
+def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, barrier):
+    """e2e for row bands: the same per-frame host work as run_e2e on every rank, but the frame reaches the host
+    through ALL ranks' PCIe links: each rank reads its own band back (rt_download_color_overlapped, copy stream,
+    overlapping its next frame) into one host image the ranks share (bands.SharedHostFrames: /dev/shm,
+    page-locked in every rank).  Rank 0 plays the consumer: it waits until every rank's band of frame k-1 has
+    landed, then releases the image for frame k+1.  No NVLink gather is needed on this path."""
+    from real_time_ray_tracer_b200 import bands as _bands
+
+    W, H = fr.W, fr.H
+    box = [os.getpid()]
+    dist.broadcast_object_list(box, src=0)
+    shf = _bands.SharedHostFrames(W, H, rank, world, f"{box[0]}", barrier=dist.barrier)
+    y0, rows = plan[rank]
+    rt.reset_stats()
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(steps):
+        shapes = host.load_shape_buffer(fr.scene)
+        rt.upload_scene(shapes, fr.n)
+        slot, u, rb = fr.next()
+        br.render(fr.mode, u, rb)
+        while shf.released() < k - 1:       # image k % 2 held frame k-2: wait until the consumer released it
+            pass
+        rt.download_color_overlapped(slot, shf.band_ptr(k, y0), rows * W * 16)
+        rt.readback_wait(1)                 # this rank's band of frame k-1 is in host memory
+        shf.set_landed(k)
+        if rank == 0 and k >= 1:
+            while not shf.all_landed(k):    # frame k-1 is complete: shf.image(k-1) is what the application reads
+                pass
+            shf.release(k)
+    rt.readback_wait(0)
+    shf.set_landed(steps)
+    if rank == 0:
+        while not shf.all_landed(steps):
+            pass
+        shf.release(steps)
+    torch.cuda.synchronize()
+    barrier()
+    dt = time.perf_counter() - t0
+    st = rt.stats()
+    c0 = torch.tensor([float(st["rays_closest"] + st["rays_shadow"])], dtype=torch.float64, device=f"cuda:{local}")
+    t1 = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{local}")
+    dist.all_reduce(c0, op=dist.ReduceOp.SUM)
+    dist.all_reduce(t1, op=dist.ReduceOp.MAX)
+    rays, dt = float(c0.item()), float(t1.item())
+    shf.close(barrier=dist.barrier)
+    return {"value": round(rays / dt / 1e6, 2), "unit": "Mrays/s", "frames_per_s": round(steps / dt, 2),
+            "ms_per_step": round(dt / steps * 1e3, 4), "steps": steps,
+            "h2d_bytes_per_step": int(world * (fr.n * 80 + 112 + (8 * fr.AA * 4 if fr.mode in (1, 2) else 0))),
+            "d2h_bytes_per_step": int(W * H * 16),
+            "what": "upload_scene + uniforms + rand_buffer from host on every rank, render (+halo, post-process), each "
+                    "rank reads its band of the float4 image back over its own PCIe link into one page-locked host "
+                    "image shared by the ranks; rank 0 consumes frame k-1 while frame k renders"}
 
 
 def run_e2e_rgba8(torch, fr, rt, steps):
@@ -626,6 +684,8 @@ def main():
     ap.add_argument("--fence", default="flags", choices=["flags", "allreduce"],
                     help="N > 1, direct gather: per-frame fence = rt_fence (peer-memory flags, no host-side "
                          "communication call) or a one-element NCCL all-reduce")
+    ap.add_argument("--e2e-via-rank0", action="store_true",
+                    help="N > 1: e2e reads the assembled frame back through rank 0's PCIe link only")
     ap.add_argument("--nccl-gather", action="store_true",
                     help="N > 1: gather bands with NCCL point-to-point instead of direct NVLink stores")
     ap.add_argument("--replan", type=int, default=3, help="band re-cut rounds from measured times (N > 1)")

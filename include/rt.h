@@ -196,6 +196,10 @@ int rt_download_async(rt_ctx *ctx, int buffer, int slot, void *pinned_host, size
  * the kernels of the next frame; two device staging halves alternate, so up to two read-backs may be in
  * flight.  bytes = band_rows * width * 4.  rt_synchronize waits for outstanding read-backs too. */
 int rt_download_rgba8_async(rt_ctx *ctx, int slot, void *pinned_host, size_t bytes);
+/* The same overlapped read-back for the float4 plane pixels[slot] itself (bytes = band_rows * width * 16),
+ * straight from the ring slot (a slot is not rewritten for num_frames - 1 frames).  With row bands each
+ * rank reads its own band back over its own PCIe link, e.g. into one host buffer the ranks share. */
+int rt_download_color_overlapped(rt_ctx *ctx, int slot, void *pinned_host, size_t bytes);
 /* blocks the host until the read-backs issued so far have landed, except the newest `keep_in_flight` (0 or 1)
  * -- the consumer of a double-buffered pinned ring calls it with 1 before it reuses the older buffer */
 int rt_readback_wait(rt_ctx *ctx, int keep_in_flight);

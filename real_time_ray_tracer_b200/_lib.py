@@ -39,7 +39,7 @@ class rt_halo_info(C.Structure):
 EXPORTS = (
     "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_last_error", "rt_set_stream",
     "rt_synchronize", "rt_set_timing", "rt_upload_scene", "rt_render_frame", "rt_halo_pack", "rt_get_halo",
-    "rt_postprocess", "rt_download", "rt_upload", "rt_download_async", "rt_download_rgba8_async", "rt_readback_wait", "rt_device_ptr", "rt_get_stats",
+    "rt_postprocess", "rt_download", "rt_upload", "rt_download_async", "rt_download_rgba8_async", "rt_download_color_overlapped", "rt_readback_wait", "rt_device_ptr", "rt_get_stats",
     "rt_reset_stats", "rt_debug_eval_math", "rt_measure_fp32_peak",
     "rt_set_frame_target", "rt_frame_create", "rt_frame_destroy", "rt_peer_export", "rt_peer_import",
     "rt_peer_release", "rt_mailbox_create", "rt_mailbox_destroy", "rt_link_peers", "rt_fence", "rt_fence_status",
@@ -77,6 +77,7 @@ def load():
     L.rt_download_async.argtypes = [vp, i32, i32, vp, sz]
     L.rt_download_rgba8_async.argtypes = [vp, i32, vp, sz]
     L.rt_readback_wait.argtypes = [vp, i32]
+    L.rt_download_color_overlapped.argtypes = [vp, i32, vp, sz]
     L.rt_device_ptr.argtypes = [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]
     L.rt_get_stats.argtypes = [vp, C.POINTER(rt_stats)]
     L.rt_reset_stats.argtypes = [vp]

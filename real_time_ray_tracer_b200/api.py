@@ -148,6 +148,10 @@ class RayTracer:
         """rt_download_rgba8_async: the 8-bit image of pixels[slot] into pinned host memory, on the stream"""
         self._check(self.lib.rt_download_rgba8_async(self.h, slot, C.c_void_p(pinned_ptr), nbytes))
 
+    def download_color_overlapped(self, slot: int, pinned_ptr: int, nbytes: int):
+        """rt_download_color_overlapped: this band's float4 plane of pixels[slot] on the library's copy stream"""
+        self._check(self.lib.rt_download_color_overlapped(self.h, slot, C.c_void_p(pinned_ptr), nbytes))
+
     def readback_wait(self, keep_in_flight: int = 0):
         self._check(self.lib.rt_readback_wait(self.h, keep_in_flight))
 

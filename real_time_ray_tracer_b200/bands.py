@@ -283,3 +283,96 @@ class BandedRenderer:
         if self.world == 1 and out is None:
             return self.e.band_color(slot)
         return out if self.rank == 0 else None
+
+
+class SharedHostFrames:
+    """Whole-frame float4 images in host memory that all ranks of the box share (files under /dev/shm mapped
+    by every rank and page-locked with cudaHostRegister), so that each rank reads its own band back over its
+    own PCIe link (``rt_download_color_overlapped``) and the host consumer on rank 0 still finds one contiguous
+    frame -- the end-to-end path scales with the number of GPUs instead of funnelling every frame through rank
+    0's link.  A small header carries the hand-shake, all of it plain host memory:
+    ``landed[r]`` = number of frames rank r has completely delivered, ``consumed`` = number of frames the
+    consumer has released (image k % nbuf may be overwritten by frame k + nbuf only once frame k is released)."""
+
+    def __init__(self, width: int, height: int, rank: int, world: int, tag: str, nbuf: int = 2, register: bool = True,
+                 barrier=None):
+        import mmap
+        import os
+
+        self.W, self.H, self.rank, self.world, self.nbuf = width, height, rank, world, nbuf
+        self.nbytes = width * height * 16
+        self.paths = [f"/dev/shm/rtb200_{tag}_{i}" for i in range(nbuf)] + [f"/dev/shm/rtb200_{tag}_hdr"]
+        sizes = [self.nbytes] * nbuf + [4096]
+        if rank == 0:
+            for p, n in zip(self.paths, sizes):
+                with open(p, "wb") as f:
+                    f.truncate(n)
+        if barrier is not None:
+            barrier()
+        self.maps = []
+        for p, n in zip(self.paths, sizes):
+            fd = os.open(p, os.O_RDWR)
+            try:
+                self.maps.append(mmap.mmap(fd, n))
+            finally:
+                os.close(fd)
+        self.images = [np.frombuffer(m, dtype=np.float32, count=self.nbytes // 4) for m in self.maps[:nbuf]]
+        self.hdr = np.frombuffer(self.maps[nbuf], dtype=np.int64, count=world + 1)
+        self.registered = []
+        if register:
+            import torch
+
+            rtl = torch.cuda.cudart()
+            for img in self.images:
+                err = rtl.cudaHostRegister(img.ctypes.data, self.nbytes, 0)
+                if int(err) != 0:
+                    raise RuntimeError(f"cudaHostRegister failed: {err}")
+                self.registered.append(img.ctypes.data)
+        if barrier is not None:
+            barrier()
+
+    def band_ptr(self, k: int, y0: int) -> int:
+        """host address of row y0 of the image frame k goes into"""
+        return self.images[k % self.nbuf].ctypes.data + y0 * self.W * 16
+
+    def image(self, k: int) -> np.ndarray:
+        return self.images[k % self.nbuf].reshape(self.H, self.W, 4)
+
+    # -- hand-shake -------------------------------------------------------------------------------
+    def set_landed(self, frames: int):
+        self.hdr[self.rank] = frames
+
+    def all_landed(self, frames: int) -> bool:
+        return bool((self.hdr[:self.world] >= frames).all())
+
+    def release(self, frames: int):
+        self.hdr[self.world] = frames
+
+    def released(self) -> int:
+        return int(self.hdr[self.world])
+
+    def close(self, barrier=None):
+        import os
+
+        if self.registered:
+            import torch
+
+            rtl = torch.cuda.cudart()
+            for a in self.registered:
+                rtl.cudaHostUnregister(a)
+            self.registered = []
+        self.images, self.hdr = [], None
+        for m in self.maps:
+            try:
+                m.close()
+            except BufferError:
+                pass
+        self.maps = []
+        if barrier is not None:
+            barrier()
+        if self.rank == 0:
+            for p in self.paths:
+                try:
+                    os.unlink(p)
+                except OSError:
+                    pass

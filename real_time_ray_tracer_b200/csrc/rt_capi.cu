@@ -645,6 +645,22 @@ int rt_download_rgba8_async(rt_ctx *c, int slot, void *pinned_host, size_t bytes
     return RT_OK;
 }
 
+int rt_download_color_overlapped(rt_ctx *c, int slot, void *pinned_host, size_t bytes)
+{
+    if (!c || !pinned_host) return RT_EINVAL;
+    if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
+    if (bytes != c->npix * 16) return fail(c, RT_EINVAL, "rt_download_color_overlapped: expected %zu bytes, got %zu", c->npix * 16, bytes);
+    CU(c, cudaSetDevice(c->cfg.device));
+    const int h = c->rgba8_flip;    // same two event slots as the 8-bit read-back: rt_readback_wait covers both
+    c->rgba8_flip ^= 1;
+    CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    CU(c, cudaMemcpyAsync(pinned_host, c->ring_color + (size_t)slot * c->npix, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
+    c->copy_pending[h] = true;
+    return RT_OK;
+}
+
 int rt_readback_wait(rt_ctx *c, int keep_in_flight)
 {
     if (!c) return RT_EINVAL;

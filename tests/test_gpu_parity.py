@@ -406,6 +406,77 @@ def _run_ranks(world, W, H, AA, cuts, modes, fence, one_gpu):
     o.close()
 
 
+def _host_frames_worker(rank, world, port, W, H, AA, cuts, q):
+    import os
+
+    import torch
+    import torch.distributed as dist
+
+    from real_time_ray_tracer_b200 import bands
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.cuda.set_device(0)
+    try:
+        shf = bands.SharedHostFrames(W, H, rank, world, f"test{port}", barrier=dist.barrier)
+        y0, rows = cuts[rank], cuts[rank + 1] - cuts[rank]
+        sc = Scenario("scene6", keys=("a",))
+        out = []
+        with rtb.RayTracer(W, H, AA, band_y0=y0, band_rows=rows, band_index=rank, band_count=world) as rt:
+            rt.upload_scene(sc.shapes, sc.n)
+            for k, mode in enumerate((2, 3, 4, 2)):
+                slot, u, rb = sc.next(mode, AA)
+                rt.render_frame(mode, u, rb)
+                while shf.released() < k - 1:
+                    pass
+                rt.download_color_overlapped(slot, shf.band_ptr(k, y0), rows * W * 16)
+                rt.readback_wait(1)
+                shf.set_landed(k)
+                if rank == 0 and k >= 1:
+                    while not shf.all_landed(k):
+                        pass
+                    out.append(shf.image(k - 1).copy())
+                    shf.release(k)
+            rt.readback_wait(0)
+            shf.set_landed(4)
+            if rank == 0:
+                while not shf.all_landed(4):
+                    pass
+                out.append(shf.image(3).copy())
+                q.put(out)
+            dist.barrier()
+        shf.close(barrier=dist.barrier)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_bands_read_back_into_one_shared_host_frame():
+    """SharedHostFrames + rt_download_color_overlapped: two ranks (processes) each read their own band back into
+    one page-locked host image under /dev/shm; the consumer on rank 0 sees whole frames equal to the oracle's."""
+    import torch.multiprocessing as mp
+
+    W, H, AA = 72, 40, 4
+    cuts = [0, 17, 40]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29850 + int(np.random.default_rng().integers(0, 100))
+    procs = [ctx.Process(target=_host_frames_worker, args=(r, 2, port, W, H, AA, cuts, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    sc = Scenario("scene6", keys=("a",))
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(sc.shapes, sc.n)
+    for k, mode in enumerate((2, 3, 4, 2)):
+        slot, u, rb = sc.next(mode, AA)
+        o.render(mode, u, rb)
+        assert same_bits(out[k], o.get(orc.IMAGE)), f"frame {k} mode {mode}: {diff_report(out[k], o.get(orc.IMAGE))}"
+    o.close()
+
+
 def test_direct_gather_across_processes_over_cuda_ipc():
     """Two processes (one band each, both on cuda:0 -- the box of the GPU test tier has one GPU): rank 1 maps
     rank 0's images through the IPC handle and its kernels store the band into them; rank 0 reads whole frames
