@@ -33,6 +33,8 @@ struct rt_ctx {
     void *staging = nullptr; // npix * 16 bytes, layout conversions
     unsigned long long *stats = nullptr;
     unsigned *work = nullptr; // streaming AO kernel's unit counters
+    TailQueue tq{};           // AO_KERNEL_QUEUED (allocated when aa <= 4)
+    unsigned frame_parity = 0;
     float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
     float4 sky_bg{};
     bool sky_valid = false;
@@ -100,6 +102,7 @@ static void free_all(rt_ctx *c)
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
     cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->work); cudaFree(c->sky);
+    cudaFree(c->tq.entries); cudaFree(c->tq.results); cudaFree(c->tq.counters);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
@@ -169,13 +172,20 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     if (const char *k = getenv("RT_AO_KERNEL")) {
         if (!strcmp(k, "tile")) c->ao_kernel = AO_KERNEL_TILE;
         else if (!strcmp(k, "stream")) c->ao_kernel = AO_KERNEL_STREAM;
+        else if (!strcmp(k, "queued")) c->ao_kernel = AO_KERNEL_QUEUED;
         else if (strcmp(k, "phased")) {
-            fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected phased, tile or stream)", k);
+            fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected phased, queued, tile or stream)", k);
             free_all(c);
             return RT_EINVAL;
         }
     }
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width));
+    if (c->ao_kernel == AO_KERNEL_QUEUED && cfg->aa <= 4) {
+        // worst case every pixel of the band is queued
+        alloc0((void **)&c->tq.entries, c->npix * TQ_ENTRY_VEC4 * sizeof(float4));
+        alloc0((void **)&c->tq.results, c->npix * sizeof(float4));
+        alloc0((void **)&c->tq.counters, 8 * sizeof(unsigned));
+    }
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -317,6 +327,8 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     o.work = c->work;
     o.ao_kernel = c->ao_kernel;
     o.sky = c->sky;
+    o.tq = c->tq;
+    if (ao) { o.tq.parity = (int)(c->frame_parity & 1u); c->frame_parity++; }
     if (ao && (!c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0)) {
         // first AO frame, or the background changed (scene toggle, src/main.cpp:229-255)
         CU(c, launch_sky_gamma(p.bg, p.AA, c->sky, c->stream));

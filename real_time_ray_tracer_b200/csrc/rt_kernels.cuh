@@ -69,7 +69,17 @@ enum StatIdx {
     ST_COUNT
 };
 
-enum { AO_KERNEL_PHASED = 0, AO_KERNEL_TILE = 1, AO_KERNEL_STREAM = 2 };
+enum { AO_KERNEL_PHASED = 0, AO_KERNEL_TILE = 1, AO_KERNEL_STREAM = 2, AO_KERNEL_QUEUED = 3 };
+
+// device queue of the three-kernel AO schedule (rt_ao_queued.cu): one entry per pixel that still has path
+// segments to trace after the head: [0] = (pixel index, pending mask, depth.x, -), then two float4 per sample
+constexpr int TQ_ENTRY_VEC4 = 9;
+struct TailQueue {
+    float4 *entries;    // [capacity][TQ_ENTRY_VEC4]
+    float4 *results;    // [capacity]: colour sum rgb, depth.y
+    unsigned *counters; // [2][4]: {entries appended, entries taken, -, -} per frame parity
+    int parity;
+};
 
 // output planes of one trace dispatch; all row-major [rows][W] of this band
 struct TraceOut {
@@ -81,6 +91,7 @@ struct TraceOut {
     unsigned long long *stats; // [STAT_STRIPES][ST_COUNT]
     unsigned *work;   // [2] unit counter + finished-warp counter of the streaming AO kernel (self re-arming)
     int ao_kernel;    // AO_KERNEL_*
+    TailQueue tq;     // AO_KERNEL_QUEUED
     const float *sky; // [6] all-background colour sum and its gamma (rt_sky_gamma_kernel), phased AO kernel
     float4 *gather;   // rt_set_frame_target: this band's rows inside a whole-frame image (maybe peer memory), or null
 };
@@ -127,6 +138,7 @@ cudaError_t launch_fence(const PeerBoxes &peers, int rank, int world, unsigned l
 cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_phased(const FrameParams &p, const TraceOut &o, cudaStream_t s);
+cudaError_t launch_ao_queued(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_sky_gamma(float4 bg, int AA, float *sky, cudaStream_t s);
 cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s);
 cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s);

@@ -148,6 +148,31 @@ __device__ __forceinline__ float3 primary_dir(const FrameParams &p, float hp, fl
     return normalize3(add3(add3(p.llc, scale3(hp, p.horiz)), scale3(vp, p.vert)));
 }
 
+// direction of the camera ray of sample aa through pixel (fx, fy): ao_compute.glsl:299-301 (sample 0, un-jittered)
+// and :310-324 (jittered, seeds cross-wired exactly as written there); rf, rs = rand_buffer[2 aa], [2 aa + 1]
+__device__ __forceinline__ float3 ao_camera_ray(const FrameParams &p, int aa, float4 rf, float4 rs, float fx, float fy)
+{
+    float hp, vp;
+    if (aa == 0) {
+        hp = div_const(fx, p.fW, p.invW);
+        vp = div_const(fy, p.fH, p.invH);
+    } else {
+        float s1x = rs.x, s1y = rf.y, s2x = rf.z, s2y = rs.w;
+        float s3x = rf.x, s3y = rs.y, s4x = rs.z, s4y = rf.w;
+        float ax = ((s1x + fx * s2x) - fx) + s3x;
+        float ay = ((s1y + fy * s2y) - fy) + s3y;
+        float bx = s4x * fx - (s3x * fx) * s2x;
+        float by = s4y * fy - (s3y * fy) * s2y;
+        float r1 = random2(ax, ay), r2 = random2(bx, by);
+        float inv = inv_sqrt_ieee(dot2(r1, r2, r1, r2));
+        float jx = div_const(r1 * inv, 6.0f, RT_INV6) - 0.08333f;
+        float jy = div_const(r2 * inv, 6.0f, RT_INV6) - 0.08333f;
+        hp = div_const(fx + jx, p.fW, p.invW);
+        vp = div_const(fy + jy, p.fH, p.invH);
+    }
+    return primary_dir(p, hp, vp);
+}
+
 // ao_compute.glsl:143-158
 __device__ __forceinline__ float3 get_pt_within_unit_sphere(float4 r0, float4 r1, float fx, float fy)
 {

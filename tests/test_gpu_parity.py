@@ -276,7 +276,7 @@ def test_row_bands_on_one_gpu_equal_the_whole_frame(edge_mode, cuts):
         o.close()
 
 
-@pytest.mark.parametrize("kernel", ["phased", "stream"])
+@pytest.mark.parametrize("kernel", ["phased", "queued", "stream"])
 def test_frame_target_assembles_the_bands(kernel, monkeypatch):
     """rt_set_frame_target: three band contexts store their final colour straight into one whole-frame image
     (here on the same GPU; across ranks the same pointer is a peer mapping) -- it must equal the oracle's
@@ -498,7 +498,7 @@ def test_linked_bands_fence_and_direct_halo_on_separate_gpus():
     _run_ranks(world, 88, 50, 4, cuts, (1, 1, 1, 2, 1, 1, 4, 1, 1, 1, 1), "flags", False)
 
 
-@pytest.mark.parametrize("kernel", ["phased", "tile", "stream"])
+@pytest.mark.parametrize("kernel", ["phased", "queued", "tile", "stream"])
 def test_all_ao_kernels(kernel, monkeypatch):
     """the phased (default), tile and persistent streaming kernels are three schedules of the same arithmetic;
     recursion depths 1, 2 and 3 exercise the phased kernel's head-only, no-survivor and first-survivor paths"""
