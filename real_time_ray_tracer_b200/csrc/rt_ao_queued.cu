@@ -1,4 +1,6 @@
-// rt_ao_queued.cu -- AO trace (modes 1 and 2, AA <= 4) as three kernels: head, queued tail, tail epilogue.
+// rt_ao_queued.cu -- AO trace (modes 1 and 2, AA <= 4) as two kernels: head, queued tail.  EXPERIMENT
+// (RT_AO_KERNEL=queued), bit-exact, not faster than the fused kernel; kept as the base for overlapping the
+// tail of frame k with the head of frame k+1.
 //
 // Same arithmetic as resources/ao_compute.glsl:161-340.  The phased kernel (rt_ao_phased.cu) spends about a
 // third of its instructions in its tail -- the bounces of the 16 % of samples that survive two segments -- at
@@ -8,16 +10,23 @@
 //                          config 2) is finished on the spot.  A pixel with survivors becomes one 144-byte
 //                          entry of a device queue: its four sample records (finished: colour + terminal depth;
 //                          survivor: dir, t, hit ids, random vector), appended with one atomic per warp.
-//   rt_ao_tail_kernel      persistent warps whose LANES pull entries: a lane walks the survivors of its entry
-//                          in sample order (bounce, closest hit, classify), folds the finished samples in on
-//                          the way so the colour sum keeps the shader's order, writes the sum and takes the
-//                          next entry.  No lane waits for another lane's path; the only idle lanes are those
-//                          of the last few entries of the frame (tools/schedule_sim.py: 173.7 k warp rounds
-//                          of tail per 1080p frame in the phased kernel, 57 k when packed like this).
-//   rt_ao_tail_epilogue_kernel   gamma and the colour / depth stores of the queued pixels, converged.
+//   rt_ao_tail_flat_kernel one thread per entry: walks the entry's survivors in sample order (bounce, closest hit,
+//                          classify), folds the finished samples in on the way so the colour sum keeps the
+//                          shader's order, then finishes the pixel (gamma, colour and depth.xy stores).
+//                          Entries are in block order of the head kernel, so a warp holds 32 pixels of one
+//                          neighbourhood (tools/schedule_sim.py: 127 k warp rounds of tail per 1080p frame
+//                          against 174 k inside the phased kernel).
 //
-// The queue counters alternate between two sets by frame parity; the epilogue of frame k clears the set
-// frame k+1 will use, so no memset is needed between frames.
+// Measured (profiles/r1_launches_queued_schedule.csv, config 2): head 185 us at 87 % issue utilisation, tail 84 us
+// for 53.7 M warp instructions at 67 % -- the tail starts with dependent scattered loads of its entry and ends
+// with the few warps that hold a 20-segment path -- against 276 us for the fused phased kernel: a tie, so the
+// phased kernel stays the default.  A first version of the tail with persistent warps whose LANES pulled entries
+// (no lane waits for another lane's path) was worse: 88 us at 49 % issue utilisation and 15 lanes per
+// instruction, every lane only got about four entries and the drain at the end of the queue was a third of a
+// warp's life.
+//
+// The queue counters alternate between two sets by frame parity; a one-thread kernel at the end of frame k
+// clears the set frame k+1 will use, so no memset is needed between frames.
 #include "rt_kernels.cuh"
 #include "rt_math.cuh"
 #include "rt_trace_common.cuh"
@@ -182,113 +191,92 @@ __global__ void __launch_bounds__(QH_THREADS, 8) rt_ao_head_kernel(const __grid_
     }
 }
 
-// ---------------------------------------------------------------------------------------------
-// queued tail: persistent warps, lanes pull entries
-// ---------------------------------------------------------------------------------------------
 constexpr int QT_THREADS = 128;
 
-__global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+// ---------------------------------------------------------------------------------------------
+// flat tail: one thread per queue entry, no pulling; the thread also finishes its pixel
+// ---------------------------------------------------------------------------------------------
+// Entries are appended in block order of the head kernel, so the 32 entries of a warp are pixels of one
+// neighbourhood with similar survivors.  A warp runs max-over-lanes rounds (simulated 127 k warp rounds per 1080p
+// frame against 174 k inside the phased kernel) but pays no refill logic, no scattered pulling and no drain.
+__global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_flat_kernel(const __grid_constant__ FrameParams p, TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ float s_sky[6];
     const int tid = threadIdx.x;
 #pragma unroll 1
     for (int i = tid; i < p.nshapes; i += QT_THREADS) s_shapes[i] = p.shapes[i];
+    if (tid < 6) s_sky[tid] = o.sky[tid];
     __syncthreads();
-
-    const unsigned FULL = 0xffffffffu;
-    const int lane = tid & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
     unsigned *ctr = o.tq.counters + o.tq.parity * 4;
-    const unsigned count = ctr[0];          // final: the head kernel has completed
+    const unsigned count = ctr[0];
     const int nch = p.AA, RD = p.RD;
-
-    bool alive = true, need_entry = true;
-    unsigned e = 0, pending = 0;
-    int k = 0, i = 0, ind = -1;
-    float ar = 0.0f, ag = 0.0f, ab = 0.0f, dy = 0.0f;
-    float3 dir = p.cam, ru = p.cam;
-    float t = 0.0f, cr = 0.0f, cg = 0.0f, cb = 0.0f;
+    const float fAA = (float)p.AA;
     unsigned n_nonterm = 0, n_term = 0;
-    const float4 *ent = o.tq.entries;
 
-    // fold in the finished samples before the next survivor; load that survivor, or close the entry
-    auto advance = [&]() {
-        while (k < nch && !((pending >> k) & 1u)) {
-            const float4 r = ent[1 + 2 * k];
-            ar += r.x; ag += r.y; ab += r.z;
-            if (r.w >= 0.0f) dy = r.w;
-            k++;
-        }
-        if (k >= nch) {
-            o.tq.results[e] = make_float4(ar, ag, ab, dy);
-            need_entry = true;
-            return;
-        }
-        const float4 a = ent[1 + 2 * k], b = ent[2 + 2 * k];
-        dir = mk3(a.x, a.y, a.z);
-        t = a.w;
-        const int ids = __float_as_int(b.x);
-        ru = mk3(b.y, b.z, b.w);
-        ind = ids >> 8;
-        const DevShape &s0 = s_shapes[ids & 0xff], &s1 = s_shapes[ind];
-        cr = s0.col.x * s1.col.x; cg = s0.col.y * s1.col.y; cb = s0.col.z * s1.col.z;
-        i = RD - 2;
-    };
-
-    for (;;) {
-        // ---- refill: lanes without an entry take the next ones, one atomic per warp
-        const unsigned want = __ballot_sync(FULL, alive && need_entry);
-        if (want) {
-            unsigned base = 0;
-            const int leader = __ffs(want) - 1;
-            if (lane == leader) base = atomicAdd(&ctr[1], (unsigned)__popc(want));
-            base = __shfl_sync(FULL, base, leader);
-            if (alive && need_entry) {
-                const unsigned mine = base + __popc(want & lt_mask);
-                if (mine < count) {
-                    e = mine;
-                    ent = o.tq.entries + (size_t)e * TQ_ENTRY_VEC4;
-                    pending = __float_as_uint(ent[0].y);
-                    k = 0;
-                    ar = ag = ab = 0.0f;
-                    dy = 0.0f;
-                    need_entry = false;
-                    advance();      // an entry has at least one survivor
-                } else {
-                    alive = false;
+    for (unsigned base = blockIdx.x * QT_THREADS; base < count; base += gridDim.x * QT_THREADS) {
+        const unsigned e = base + tid;
+        if (e < count) {
+            const float4 *ent = o.tq.entries + (size_t)e * TQ_ENTRY_VEC4;
+            const float4 meta = ent[0];
+            const unsigned pending = __float_as_uint(meta.y);
+            float ar = 0.0f, ag = 0.0f, ab = 0.0f, dy = 0.0f;
+            int k = 0, i = 0, ind = -1;
+            float3 dir = p.cam, ru = p.cam;
+            float t = 0.0f, cr = 0.0f, cg = 0.0f, cb = 0.0f;
+            bool need_load = true;
+            for (;;) {
+                if (need_load) {
+                    while (k < nch && !((pending >> k) & 1u)) {
+                        const float4 r = ent[1 + 2 * k];
+                        ar += r.x; ag += r.y; ab += r.z;
+                        if (r.w >= 0.0f) dy = r.w;
+                        k++;
+                    }
+                    if (k >= nch) break;
+                    const float4 a = ent[1 + 2 * k], b = ent[2 + 2 * k];
+                    dir = mk3(a.x, a.y, a.z);
+                    t = a.w;
+                    const int ids = __float_as_int(b.x);
+                    ru = mk3(b.y, b.z, b.w);
+                    ind = ids >> 8;
+                    const DevShape &s0 = s_shapes[ids & 0xff], &s1 = s_shapes[ind];
+                    cr = s0.col.x * s1.col.x; cg = s0.col.y * s1.col.y; cb = s0.col.z * s1.col.z;
+                    i = RD - 2;
+                    need_load = false;
+                }
+                float3 pos, normal;
+                ao_bounce(p, s_shapes[ind], t, ru, dir, pos, normal);
+                ind = closest_hit(p, pos, dir, 0.0001f, t);
+                bool stop = true;
+                float a0r = p.bg.x, a0g = p.bg.y, a0b = p.bg.z;
+                if (ind >= 0) {
+                    const DevShape &s = s_shapes[ind];
+                    a0r = s.col.x; a0g = s.col.y; a0b = s.col.z;
+                    stop = s.emissive > 0.9f;
+                }
+                cr *= a0r; cg *= a0g; cb *= a0b;
+                if (stop) n_term++; else n_nonterm++;
+                const float term = (float)(RD - i);
+                i--;
+                if (stop || i == 0) {
+                    ar += cr; ag += cg; ab += cb;
+                    if (stop) dy = term;
+                    k++;
+                    need_load = true;
                 }
             }
-        }
-        if (!__any_sync(FULL, alive)) break;
-
-        if (alive) {
-            // ---- one path segment: bounce off (ind, t), closest hit, classify (ao_compute.glsl:161-261)
-            float3 pos, normal;
-            ao_bounce(p, s_shapes[ind], t, ru, dir, pos, normal);
-            ind = closest_hit(p, pos, dir, 0.0001f, t);
-            bool stop = true;
-            float a0r = p.bg.x, a0g = p.bg.y, a0b = p.bg.z;
-            if (ind >= 0) {
-                const DevShape &s = s_shapes[ind];
-                a0r = s.col.x; a0g = s.col.y; a0b = s.col.z;
-                stop = s.emissive > 0.9f;
-            }
-            cr *= a0r; cg *= a0g; cb *= a0b;
-            if (stop) n_term++; else n_nonterm++;
-            const float term = (float)(RD - i);
-            i--;
-            if (stop || i == 0) {
-                ar += cr; ag += cg; ab += cb;
-                if (stop) dy = term;
-                k++;
-                advance();
-            }
+            const unsigned pix = __float_as_uint(meta.x);
+            const float4 c = ao_pixel_colour(s_sky, ar, ag, ab, fAA);
+            o.color[pix] = c;
+            if (o.gather) o.gather[pix] = c;
+            o.depth_xy[pix] = make_float2(__fdiv_rn(meta.z, fAA), __fdiv_rn(dy, fAA));
         }
     }
 
-    const unsigned v_non = __reduce_add_sync(FULL, n_nonterm);
-    const unsigned v_term = __reduce_add_sync(FULL, n_term);
-    if (lane == 0 && (v_non | v_term)) {
+    const unsigned v_non = __reduce_add_sync(0xffffffffu, n_nonterm);
+    const unsigned v_term = __reduce_add_sync(0xffffffffu, n_term);
+    if ((tid & 31) == 0 && (v_non | v_term)) {
         const unsigned gw = blockIdx.x * (QT_THREADS >> 5) + (tid >> 5);
         unsigned long long *st = o.stats + (gw % STAT_STRIPES) * ST_COUNT;
         atomicAdd(&st[ST_SEG_NONTERMINAL], (unsigned long long)v_non);
@@ -297,60 +285,25 @@ __global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_kernel(const __grid_
     }
 }
 
-// gamma and the colour / depth.xy stores of the queued pixels (ao_compute.glsl:330-339), converged
-__global__ void __launch_bounds__(256) rt_ao_tail_epilogue_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+// clears the counter set the next frame will append to
+__global__ void rt_ao_queue_flip_kernel(TraceOut o)
 {
-    __shared__ float s_sky[6];
-    if (threadIdx.x < 6) s_sky[threadIdx.x] = o.sky[threadIdx.x];
-    __syncthreads();
-    unsigned *ctr = o.tq.counters + o.tq.parity * 4;
-    const unsigned count = ctr[0];
-    const float fAA = (float)p.AA;
-    for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < count; e += gridDim.x * blockDim.x) {
-        const float4 meta = o.tq.entries[(size_t)e * TQ_ENTRY_VEC4];
-        const float4 r = o.tq.results[e];
-        const unsigned pix = __float_as_uint(meta.x);
-        const float4 c = ao_pixel_colour(s_sky, r.x, r.y, r.z, fAA);
-        o.color[pix] = c;
-        if (o.gather) o.gather[pix] = c;
-        o.depth_xy[pix] = make_float2(__fdiv_rn(meta.z, fAA), __fdiv_rn(r.w, fAA));
-    }
-    // the next frame appends to the other counter set: clear it here, nobody is using it
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        unsigned *other = o.tq.counters + (o.tq.parity ^ 1) * 4;
-        other[0] = 0u;
-        other[1] = 0u;
-    }
+    unsigned *other = o.tq.counters + (o.tq.parity ^ 1) * 4;
+    other[0] = 0u;
+    other[1] = 0u;
 }
-
-static int g_tail_blocks[64] = { 0 };
 
 cudaError_t launch_ao_queued(const FrameParams &p, const TraceOut &o, cudaStream_t s)
 {
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    if (g_tail_blocks[dev] == 0) {
-        int per_sm = 0, sms = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_ao_tail_kernel, QT_THREADS, 0);
-        if (e != cudaSuccess) return e;
-        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess) return e;
-        g_tail_blocks[dev] = per_sm * sms; // persistent: one resident wave
-    }
     dim3 grid((p.W + QH_TILE_W - 1) / QH_TILE_W, (p.rows + QH_TILE_H - 1) / QH_TILE_H);
     rt_ao_head_kernel<<<grid, QH_THREADS, 0, s>>>(p, o);
+    // enough blocks for every entry of the worst case in a few grid-stride rounds
     const size_t npix = (size_t)p.W * p.rows;
-    int tail_blocks = g_tail_blocks[dev];
     const size_t cap_blocks = (npix + QT_THREADS - 1) / QT_THREADS;
-    if ((size_t)tail_blocks > cap_blocks) tail_blocks = (int)cap_blocks;
-    rt_ao_tail_kernel<<<tail_blocks, QT_THREADS, 0, s>>>(p, o);
-    int epi_blocks = (int)((npix + 255) / 256);
-    if (epi_blocks > 148 * 8) epi_blocks = 148 * 8;
-    rt_ao_tail_epilogue_kernel<<<epi_blocks, 256, 0, s>>>(p, o);
+    const int tail_blocks = (int)(cap_blocks < (size_t)(148 * 64) ? cap_blocks : (size_t)(148 * 64));
+    rt_ao_tail_flat_kernel<<<tail_blocks, QT_THREADS, 0, s>>>(p, o);
+    rt_ao_queue_flip_kernel<<<1, 1, 0, s>>>(o);
     return cudaGetLastError();
 }
-
 
 } // namespace rt

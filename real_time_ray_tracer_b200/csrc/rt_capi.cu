@@ -102,7 +102,7 @@ static void free_all(rt_ctx *c)
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
     cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->work); cudaFree(c->sky);
-    cudaFree(c->tq.entries); cudaFree(c->tq.results); cudaFree(c->tq.counters);
+    cudaFree(c->tq.entries); cudaFree(c->tq.counters);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
@@ -183,7 +183,6 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     if (c->ao_kernel == AO_KERNEL_QUEUED && cfg->aa <= 4) {
         // worst case every pixel of the band is queued
         alloc0((void **)&c->tq.entries, c->npix * TQ_ENTRY_VEC4 * sizeof(float4));
-        alloc0((void **)&c->tq.results, c->npix * sizeof(float4));
         alloc0((void **)&c->tq.counters, 8 * sizeof(unsigned));
     }
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));

@@ -71,13 +71,12 @@ enum StatIdx {
 
 enum { AO_KERNEL_PHASED = 0, AO_KERNEL_TILE = 1, AO_KERNEL_STREAM = 2, AO_KERNEL_QUEUED = 3 };
 
-// device queue of the three-kernel AO schedule (rt_ao_queued.cu): one entry per pixel that still has path
+// device queue of the two-kernel AO schedule (rt_ao_queued.cu): one entry per pixel that still has path
 // segments to trace after the head: [0] = (pixel index, pending mask, depth.x, -), then two float4 per sample
 constexpr int TQ_ENTRY_VEC4 = 9;
 struct TailQueue {
     float4 *entries;    // [capacity][TQ_ENTRY_VEC4]
-    float4 *results;    // [capacity]: colour sum rgb, depth.y
-    unsigned *counters; // [2][4]: {entries appended, entries taken, -, -} per frame parity
+    unsigned *counters; // [2][4]: {entries appended, -, -, -} per frame parity
     int parity;
 };
 
