@@ -224,8 +224,12 @@ def run_b200(args) -> None:
     # N > 1: the frame is assembled on rank 0.  Default = direct gather: every rank's kernels store their band
     # straight into rank 0's image over NVLink (rt_set_frame_target) and a one-element all-reduce fences the
     # frame; --nccl-gather = the bands travel as NCCL point-to-point messages after the kernels.
-    direct = bands.DirectGather(W, H, rank, world, local, tracer=rt, fence=args.fence) \
+    # The images exist on every rank (owners="rows") so that the e2e leg can spread the assembled frame over
+    # the GPUs; the device-timed loop keeps SURVEY 8(e)'s gather to rank 0 (split off).
+    direct = bands.DirectGather(W, H, rank, world, local, tracer=rt, fence=args.fence, owners="rows") \
         if (world > 1 and not args.nccl_gather) else None
+    if direct is not None:
+        direct.split = False
     br = bands.BandedRenderer(eng, W, H, plan, rank, world, direct=direct)
     # rank 0 assembles frames in two alternating buffers so the gather of frame k overlaps the trace of k+1
     fulls = [torch.empty(W * H * 4, dtype=torch.float32, device=f"cuda:{local}") for _ in range(2)] \
@@ -312,7 +316,8 @@ def run_b200(args) -> None:
     e2e = None
     if args.e2e:
         if world > 1 and direct is not None and not args.e2e_via_rank0:
-            e2e = run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, min(K, 64), barrier)
+            e2e = run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, min(K, 64), barrier,
+                                 None if args.e2e_own_bands else direct)
         else:
             e2e = run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, min(K, 64), barrier, direct)
 
@@ -346,7 +351,8 @@ def run_b200(args) -> None:
                        "recursion_depth": host.RECURSION_DEPTH, "ring_frames": host.NUM_FRAMES,
                        "parallelism": f"row-bands x{world}", "bands": plan,
                        "gather": ("none" if world == 1 else "nccl p2p" if direct is None else
-                                  f"direct NVLink stores into rank 0's image, halo rows stored into the neighbours, fence = {args.fence}"),
+                                  f"direct NVLink stores into rank 0's image (e2e leg: into the images of the ranks that own the rows, "
+                                  f"equal shares), halo rows stored into the neighbours, fence = {args.fence}"),
                        "l2": "no input reuse: ~1.4 KB of kernel parameters in, each frame writes a different "
                              "ring slot (8 x %.0f MB > 126 MB L2)" % (W * H * 44 / 1e6)},
             "rays_per_frame": rays / K,
@@ -467,12 +473,18 @@ def run_e2e(torch, dist, rtb, L, fr, rt, br, full, rank, world, local, steps, ba
                     "colour image read back to pinned host memory; read-back of frame k overlaps frame k+1"}
 
 
-def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, barrier):
+def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, barrier, split=None):
     """e2e for row bands: the same per-frame host work as run_e2e on every rank, but the frame reaches the host
-    through ALL ranks' PCIe links: each rank reads its own band back (rt_download_color_overlapped, copy stream,
-    overlapping its next frame) into one host image the ranks share (bands.SharedHostFrames: /dev/shm,
-    page-locked in every rank).  Rank 0 plays the consumer: it waits until every rank's band of frame k-1 has
-    landed, then releases the image for frame k+1.  No NVLink gather is needed on this path."""
+    through ALL ranks' PCIe links, into one host image the ranks share (bands.SharedHostFrames: /dev/shm,
+    page-locked in every rank).  Rank 0 plays the consumer: it waits until every rank's part of frame k-1 has
+    landed, then releases the image for frame k+1.
+
+    ``split`` (a DirectGather with owners="rows"): the kernels store every pixel into the image of the rank that
+    OWNS its row (rt_set_frame_targets, an equal share of rows per rank, over NVLink), rt_fence closes the frame,
+    and each rank reads its share back (rt_frame_download_overlapped) -- the bytes per PCIe link are equal although
+    the bands are cut for equal compute time (the sky band of config 2 is a third of the rows at N = 8).
+    ``split=None``: each rank reads its own band back from its ring slot (rt_download_color_overlapped); no
+    NVLink traffic, unequal bytes per link."""
     from real_time_ray_tracer_b200 import bands as _bands
 
     W, H = fr.W, fr.H
@@ -480,6 +492,9 @@ def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, bar
     dist.broadcast_object_list(box, src=0)
     shf = _bands.SharedHostFrames(W, H, rank, world, f"{box[0]}", barrier=dist.barrier)
     y0, rows = plan[rank]
+    if split is not None:
+        split.split = True
+        oy0, orows = split.own_rows
     rt.reset_stats()
     barrier()
     t0 = time.perf_counter()
@@ -487,11 +502,18 @@ def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, bar
         shapes = host.load_shape_buffer(fr.scene)
         rt.upload_scene(shapes, fr.n)
         slot, u, rb = fr.next()
+        kf = br.frame_k
         br.render(fr.mode, u, rb)
+        if split is not None:
+            br.gather_start(slot)           # rt_fence: every rank's stores into this rank's share have landed
         while shf.released() < k - 1:       # image k % 2 held frame k-2: wait until the consumer released it
             pass
-        rt.download_color_overlapped(slot, shf.band_ptr(k, y0), rows * W * 16)
-        rt.readback_wait(1)                 # this rank's band of frame k-1 is in host memory
+        if split is not None:
+            rt.frame_download_overlapped(split.frames[kf % len(split.frames)].ptr, oy0, orows,
+                                         shf.band_ptr(k, oy0), orows * W * 16)
+        else:
+            rt.download_color_overlapped(slot, shf.band_ptr(k, y0), rows * W * 16)
+        rt.readback_wait(1)                 # this rank's part of frame k-1 is in host memory
         shf.set_landed(k)
         if rank == 0 and k >= 1:
             while not shf.all_landed(k):    # frame k-1 is complete: shf.image(k-1) is what the application reads
@@ -513,12 +535,18 @@ def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, bar
     dist.all_reduce(t1, op=dist.ReduceOp.MAX)
     rays, dt = float(c0.item()), float(t1.item())
     shf.close(barrier=dist.barrier)
+    if split is not None:
+        split.split = False
     return {"value": round(rays / dt / 1e6, 2), "unit": "Mrays/s", "frames_per_s": round(steps / dt, 2),
             "ms_per_step": round(dt / steps * 1e3, 4), "steps": steps,
             "h2d_bytes_per_step": int(world * (fr.n * 80 + 112 + (8 * fr.AA * 4 if fr.mode in (1, 2) else 0))),
             "d2h_bytes_per_step": int(W * H * 16),
-            "what": "upload_scene + uniforms + rand_buffer from host on every rank, render (+halo, post-process), each "
-                    "rank reads its band of the float4 image back over its own PCIe link into one page-locked host "
+            "d2h_bytes_per_link": ([int((split.row_end[j] - (split.row_end[j - 1] if j else 0)) * W * 16) for j in range(world)]
+                                   if split is not None else [int(r * W * 16) for _, r in plan]),
+            "what": "upload_scene + uniforms + rand_buffer from host on every rank, render (+halo, post-process), "
+                    + ("every pixel stored into the image of the rank that owns its row (equal shares, over NVLink), "
+                       "rt_fence, each rank reads its share" if split is not None else "each rank reads its band")
+                    + " of the float4 image back over its own PCIe link into one page-locked host "
                     "image shared by the ranks; rank 0 consumes frame k-1 while frame k renders"}
 
 
@@ -686,6 +714,9 @@ def main():
                          "communication call) or a one-element NCCL all-reduce")
     ap.add_argument("--e2e-via-rank0", action="store_true",
                     help="N > 1: e2e reads the assembled frame back through rank 0's PCIe link only")
+    ap.add_argument("--e2e-own-bands", action="store_true",
+                    help="N > 1 e2e: every rank reads back its own (compute-balanced) band instead of an equal share "
+                         "of the frame assembled with rt_set_frame_targets")
     ap.add_argument("--nccl-gather", action="store_true",
                     help="N > 1: gather bands with NCCL point-to-point instead of direct NVLink stores")
     ap.add_argument("--replan", type=int, default=3, help="band re-cut rounds from measured times (N > 1)")

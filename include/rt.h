@@ -230,6 +230,18 @@ int rt_device_ptr(rt_ctx *ctx, int buffer, int slot, void **out_ptr, size_t *out
 int rt_frame_create(int device, int width, int height, void **out_frame);
 int rt_frame_destroy(int device, void *frame);
 int rt_set_frame_target(rt_ctx *ctx, void *frame); /* NULL = off; takes effect with the next rt_render_frame */
+/* Split targets: rows [row_end[k-1], row_end[k]) of the frame (row_end[-1] = 0, row_end[count-1] = height) go
+ * into frames[k], each a whole-frame image of which only those rows are written.  With one image per rank
+ * and an even split, every GPU ends up owning an equal share of the assembled frame whatever the (compute-
+ * balanced) bands are, and reads it back over its own PCIe link: rt_frame_download_overlapped.  count = 0: off. */
+int rt_set_frame_targets(rt_ctx *ctx, int count, void *const *frames, const int *row_end);
+/* rows [y0, y0 + rows) of a frame image on this context's device -> page-locked host memory, on the copy
+ * stream, ordered after the work enqueued on the context's stream so far (normally the rt_fence that closes
+ * the frame); rt_readback_wait covers it.  `pinned_host` is where row y0 lands. */
+int rt_frame_download_overlapped(rt_ctx *ctx, const void *frame, int y0, int rows, void *pinned_host, size_t bytes);
+/* the context's stream waits, on the device, for the read-backs issued so far: enqueue it before the
+ * rt_fence after which other ranks may overwrite a frame image that is still being read back */
+int rt_stream_wait_readback(rt_ctx *ctx);
 
 #define RT_PEER_HANDLE_BYTES 64
 #define RT_MAX_RANKS 16

@@ -98,6 +98,26 @@ class RayTracer:
         image at ``frame_ptr`` (a ``Frame``'s pointer, local or imported from another rank); None = off."""
         self._check(self.lib.rt_set_frame_target(self.h, C.c_void_p(frame_ptr or 0)))
 
+    def set_frame_targets(self, frame_ptrs, row_end):
+        """rt_set_frame_targets: rows [row_end[k-1], row_end[k]) of the frame go into the whole-frame image
+        ``frame_ptrs[k]`` (own or imported); ``row_end[-1]`` must be the frame height.  Empty lists = off."""
+        n = len(frame_ptrs)
+        if n != len(row_end):
+            raise ValueError("set_frame_targets: one row_end per frame")
+        arr = (C.c_void_p * max(n, 1))(*[C.c_void_p(int(f)) for f in frame_ptrs])
+        ends = (C.c_int32 * max(n, 1))(*[int(e) for e in row_end])
+        self._check(self.lib.rt_set_frame_targets(self.h, n, arr, ends))
+
+    def frame_download_overlapped(self, frame_ptr: int, y0: int, rows: int, pinned_ptr: int, nbytes: int):
+        """rt_frame_download_overlapped: rows [y0, y0+rows) of a frame image on this device -> pinned host
+        memory, on the library's copy stream, after the work enqueued on the context's stream so far"""
+        self._check(self.lib.rt_frame_download_overlapped(self.h, C.c_void_p(frame_ptr), y0, rows,
+                                                          C.c_void_p(pinned_ptr), nbytes))
+
+    def stream_wait_readback(self):
+        """rt_stream_wait_readback: the context's stream waits (on the device) for the read-backs issued so far"""
+        self._check(self.lib.rt_stream_wait_readback(self.h))
+
     def link_peers(self, rank: int, world: int, mailboxes, next_recv_lo: Optional[int] = None,
                    prev_recv_hi: Optional[int] = None):
         """rt_link_peers: ``mailboxes`` = world device pointers (own + imported)."""

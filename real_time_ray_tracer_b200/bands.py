@@ -93,6 +93,9 @@ class GpuBandEngine:
     def set_frame_target(self, ptr):
         self.rt.set_frame_target(ptr)
 
+    def set_frame_targets(self, ptrs, row_end):
+        self.rt.set_frame_targets(ptrs, row_end)
+
     def fence(self):
         self.rt.fence()
 
@@ -117,11 +120,18 @@ class DirectGather:
     each rank), so all bands are in the image."""
 
     def __init__(self, width: int, height: int, rank: int, world: int, device: int, nbuf: int = 2, group=None,
-                 tracer=None, fence: str = "allreduce"):
+                 tracer=None, fence: str = "allreduce", owners: str = "rank0"):
         """``fence="flags"`` (needs ``tracer``, one GPU per rank): the ranks exchange mailbox and halo-row
         handles once, ``rt_link_peers`` wires them into the context, and from then on a frame needs no
         host-side communication call: ``rt_fence`` is a kernel that signals and polls peer memory, and
-        ``rt_halo_pack`` stores the edge rows straight into the neighbours' halo rows."""
+        ``rt_halo_pack`` stores the edge rows straight into the neighbours' halo rows.
+
+        ``owners="rows"`` (rt_set_frame_targets): every rank holds ``nbuf`` images and OWNS an equal share of
+        the frame's rows, ``own_rows``; all ranks' kernels store each pixel into its owner's image, whatever the
+        (compute-balanced) bands are.  The assembled frame is then spread evenly over the GPUs, and each rank
+        reads its share back over its own PCIe link (``RayTracer.frame_download_overlapped``).  ``fence()``
+        then first makes the stream wait for the rank's own pending read-back, so that no rank can start
+        overwriting an image another rank is still copying out."""
         import torch
         import torch.distributed as dist
 
@@ -129,17 +139,40 @@ class DirectGather:
 
         self.rank, self.world, self.device, self.group = rank, world, device, group
         self.fence_kind, self.tracer, self.mailbox, self.maps = fence, tracer, None, []
-        handles = None
-        if rank == 0:
+        self.owners, self.height = owners, height
+        self.split = owners == "rows"   # owners="rows" only: False = gather to rank 0's image after all
+        if owners == "rows":
+            if tracer is None:
+                raise ValueError("owners='rows' needs the band's RayTracer")
+            self.row_end = [height * (j + 1) // world for j in range(world)]
             self.frames = [api.Frame.create(width, height, device) for _ in range(nbuf)]
-            handles = [f.export() for f in self.frames]
-        box = [handles]
-        if world > 1:
-            dist.broadcast_object_list(box, src=0, group=group)
-        if rank != 0:
-            self.frames = [api.Frame.open(h, width, height, device) for h in box[0]]
+            mine = [f.export() for f in self.frames]
+            allf = [None] * world
+            if world > 1:
+                dist.all_gather_object(allf, mine, group=group)
+            else:
+                allf[0] = mine
+            self.peer_frames = []       # [rank][buffer] -> Frame (own or imported)
+            for j in range(world):
+                self.peer_frames.append(self.frames if j == rank else
+                                        [api.Frame.open(h, width, height, device) for h in allf[j]])
+        elif owners == "rank0":
+            self.row_end = [height]
+            handles = None
+            if rank == 0:
+                self.frames = [api.Frame.create(width, height, device) for _ in range(nbuf)]
+                handles = [f.export() for f in self.frames]
+            box = [handles]
+            if world > 1:
+                dist.broadcast_object_list(box, src=0, group=group)
+            if rank != 0:
+                self.frames = [api.Frame.open(h, width, height, device) for h in box[0]]
+            self.peer_frames = [self.frames]
+        else:
+            raise ValueError("owners must be 'rank0' or 'rows'")
         self.token = torch.zeros(1, dtype=torch.float32, device=f"cuda:{device}")
-        self.tensors = [device_tensor(f.ptr, f.nbytes, device) for f in self.frames] if rank == 0 else None
+        self.tensors = ([device_tensor(f.ptr, f.nbytes, device) for f in self.frames]
+                        if (rank == 0 or owners == "rows") else None)
         if fence == "flags":
             if tracer is None:
                 raise ValueError("fence='flags' needs the band's RayTracer")
@@ -174,7 +207,21 @@ class DirectGather:
             raise ValueError("fence must be 'allreduce' or 'flags'")
 
     def target(self, k: int) -> int:
-        return self.frames[k % len(self.frames)].ptr
+        """rank 0's image for frame k"""
+        return self.peer_frames[0][k % len(self.frames)].ptr
+
+    def targets(self, k: int):
+        """(image pointers, row_end) of frame k for rt_set_frame_targets"""
+        b = k % len(self.frames)
+        return [fr[b].ptr for fr in self.peer_frames], self.row_end
+
+    @property
+    def own_rows(self) -> Tuple[int, int]:
+        """(y0, rows) of the frame this rank's images hold once a frame is fenced"""
+        if self.owners == "rank0":
+            return (0, self.height) if self.rank == 0 else (0, 0)
+        y0 = self.row_end[self.rank - 1] if self.rank else 0
+        return y0, self.row_end[self.rank] - y0
 
     @property
     def halo_direct(self) -> bool:
@@ -183,19 +230,28 @@ class DirectGather:
     def fence(self):
         import torch.distributed as dist
 
+        if self.owners == "rows":
+            self.tracer.stream_wait_readback()
         if self.fence_kind == "flags":
             self.tracer.fence()
         elif self.world > 1:
             dist.all_reduce(self.token, group=self.group)
 
     def frame(self, k: int):
-        """rank 0: float32 tensor [H*W*4] of the image frame k was gathered into"""
-        return self.tensors[k % len(self.tensors)] if self.rank == 0 else None
+        """float32 tensor [H*W*4] of the image frame k was gathered into: the whole frame on rank 0
+        (owners="rank0"), or this rank's image, of which rows ``own_rows`` are valid (owners="rows")"""
+        return self.tensors[k % len(self.tensors)] if self.tensors is not None else None
 
     def close(self):
         for m in self.maps:
             m.close()
         self.maps = []
+        if self.owners == "rows":
+            for j, fr in enumerate(self.peer_frames):
+                if j != self.rank:
+                    for f in fr:
+                        f.close()
+            self.peer_frames = []
         for f in self.frames:
             f.close()
         if self.mailbox:
@@ -233,7 +289,10 @@ class BandedRenderer:
 
     def render(self, mode: int, uniforms, rand_buffer):
         if self.direct is not None:
-            self.e.set_frame_target(self.direct.target(self.frame_k))
+            if self.direct.owners == "rows" and self.direct.split:
+                self.e.set_frame_targets(*self.direct.targets(self.frame_k))
+            else:
+                self.e.set_frame_target(self.direct.target(self.frame_k))
         self.e.render_frame(mode, uniforms, rand_buffer)
         if mode == 1:
             if self.world > 1:

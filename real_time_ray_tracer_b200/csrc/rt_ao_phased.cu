@@ -36,7 +36,7 @@ constexpr int PH_MIN_BLOCKS = 1024 / PH_THREADS;
 constexpr int AO_CHUNK = 4;     // samples whose state is parked in shared memory at a time
 constexpr int ST_FIELDS = 8;    // survivor: dir.xyz, t, ids, ru.xyz   finished: colour.rgb, terminal depth
 
-__global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     __shared__ float4 s_rand[2 * RT_MAX_AA];
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel
         if (!(ar == s_sky[0] && ag == s_sky[1] && ab == s_sky[2]))
             c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
         o.color[pix] = c;
-        if (o.gather) o.gather[pix] = c;   // rt_set_frame_target: the assembled frame, maybe over NVLink
+        gather_store(o.gather, yl, pix, c);   // rt_set_frame_targets: the assembled frame, maybe over NVLink
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
         o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
         o.depth_w[pix] = __fdiv_rn(dw, fAA);

@@ -44,7 +44,7 @@ __device__ __forceinline__ float4 ao_pixel_colour(const float *sky, float ar, fl
     return gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
 }
 
-__global__ void __launch_bounds__(QH_THREADS, 8) rt_ao_head_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(QH_THREADS, 8) rt_ao_head_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     __shared__ float4 s_rand[2 * Q_SAMPLES];
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(QH_THREADS, 8) rt_ao_head_kernel(const __grid_
             }
             const float4 c = ao_pixel_colour(s_sky, ar, ag, ab, fAA);
             o.color[pix] = c;
-            if (o.gather) o.gather[pix] = c;
+            gather_store(o.gather, yl, pix, c);
             o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
         }
     }
@@ -199,7 +199,7 @@ constexpr int QT_THREADS = 128;
 // Entries are appended in block order of the head kernel, so the 32 entries of a warp are pixels of one
 // neighbourhood with similar survivors.  A warp runs max-over-lanes rounds (simulated 127 k warp rounds per 1080p
 // frame against 174 k inside the phased kernel) but pays no refill logic, no scattered pulling and no drain.
-__global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_flat_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_flat_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     __shared__ float s_sky[6];
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_flat_kernel(const __
             const unsigned pix = __float_as_uint(meta.x);
             const float4 c = ao_pixel_colour(s_sky, ar, ag, ab, fAA);
             o.color[pix] = c;
-            if (o.gather) o.gather[pix] = c;
+            gather_store(o.gather, o.gather.count > 1 ? (int)(pix / (unsigned)p.W) : 0, pix, c);
             o.depth_xy[pix] = make_float2(__fdiv_rn(meta.z, fAA), __fdiv_rn(dy, fAA));
         }
     }

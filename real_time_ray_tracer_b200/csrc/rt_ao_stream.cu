@@ -266,8 +266,8 @@ __global__ void __launch_bounds__(STREAM_THREADS) rt_ao_stream_kernel(const __gr
 }
 
 // divide by AA and gamma (ao_compute.glsl:330-335), in place, fully converged and coalesced
-__global__ void __launch_bounds__(256) rt_ao_epilogue_kernel(float4 *color, float2 *depth_xy, float *depth_w, size_t n, int AA,
-                                                             float4 *gather)
+__global__ void __launch_bounds__(256) rt_ao_epilogue_kernel(float4 *color, float2 *depth_xy, float *depth_w, size_t n, int AA, int W,
+                                                             const __grid_constant__ GatherTargets gather)
 {
     const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(256) rt_ao_epilogue_kernel(float4 *color, floa
     const float w = depth_w[k];
     const float4 g = gamma_correct(__fdiv_rn(c.x, fAA), __fdiv_rn(c.y, fAA), __fdiv_rn(c.z, fAA));
     color[k] = g;
-    if (gather) gather[k] = g;
+    gather_store(gather, gather.count > 1 ? (int)(k / (size_t)W) : 0, k, g);
     depth_xy[k] = make_float2(__fdiv_rn(d.x, fAA), __fdiv_rn(d.y, fAA));
     depth_w[k] = __fdiv_rn(w, fAA);
 }
@@ -307,7 +307,7 @@ cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const size_t n = (size_t)p.rows * p.W;
-    rt_ao_epilogue_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(o.color, o.depth_xy, o.depth_w, n, p.AA, o.gather);
+    rt_ao_epilogue_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(o.color, o.depth_xy, o.depth_w, n, p.AA, p.W, o.gather);
     return cudaGetLastError();
 }
 

@@ -51,8 +51,11 @@ struct rt_ctx {
     unsigned long long fence_epoch = 0;
     void *peer_next_recv_lo = nullptr, *peer_prev_recv_hi = nullptr;
     bool halo_direct = false;
-    float4 *frame_target = nullptr; // rt_set_frame_target: whole-frame image, maybe peer memory
-    float4 *frame_target_post = nullptr; // the target the pending mode-1 frame was rendered for
+    // rt_set_frame_targets: whole-frame images (maybe peer memory) and the frame row each one's share ends at
+    float4 *frame_targets[RT_MAX_RANKS] = {};
+    int frame_target_end[RT_MAX_RANKS] = {};
+    int frame_target_count = 0;
+    GatherTargets gather_post = {};  // the targets the pending mode-1 frame was rendered for
     int rgba8_flip = 0;
     cudaStream_t copy_stream = nullptr;   // read-backs of rt_download_rgba8_async overlap the next frame
     cudaEvent_t ev_quant[2] = { nullptr, nullptr }, ev_copy[2] = { nullptr, nullptr };
@@ -281,6 +284,24 @@ static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n
     }
 }
 
+// the share of every frame target inside this band, as band-local row ranges (see GatherTargets)
+static GatherTargets band_gather_targets(const rt_ctx *c)
+{
+    GatherTargets g = {};
+    const int y0 = c->cfg.band_y0, y1 = y0 + c->rows;
+    int begin = 0;
+    for (int k = 0; k < c->frame_target_count; k++) {
+        const int end = c->frame_target_end[k];
+        if (end > begin && end > y0 && begin < y1) {    // rows [begin, end) of the frame meet the band
+            g.img[g.count] = c->frame_targets[k] + (size_t)y0 * c->cfg.width;
+            g.row_end[g.count] = (end < y1 ? end : y1) - y0;
+            g.count++;
+        }
+        begin = end > begin ? end : begin;
+    }
+    return g;
+}
+
 int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand_buffer)
 {
     if (!c) return RT_EINVAL;
@@ -335,9 +356,9 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
         c->sky_valid = true;
     }
     // mode 1: the trace output is raw; the post-processing pass writes the frame
-    float4 *band_in_frame = c->frame_target ? c->frame_target + (size_t)c->cfg.band_y0 * c->cfg.width : nullptr;
-    o.gather = (mode == RT_MODE_AO_PP) ? nullptr : band_in_frame;
-    c->frame_target_post = (mode == RT_MODE_AO_PP) ? band_in_frame : nullptr;
+    GatherTargets g = band_gather_targets(c), none = {};
+    o.gather = (mode == RT_MODE_AO_PP) ? none : g;
+    c->gather_post = (mode == RT_MODE_AO_PP) ? g : none;
     if (c->timing) CU(c, cudaEventRecord(c->ev[0], c->stream));
     CU(c, launch_trace(p, o, c->stream));
     if (c->timing) { CU(c, cudaEventRecord(c->ev[1], c->stream)); c->ev_trace_valid = true; }
@@ -359,7 +380,7 @@ static void fill_post(rt_ctx *c, PostParams &q)
     q.send_lo = c->halo[0]; q.send_hi = c->halo[1];
     q.halo_lo = c->halo[2]; q.halo_hi = c->halo[3];
     q.rand_last = c->rand_last;
-    q.gather = c->frame_target_post;
+    q.gather = c->gather_post;
     q.stats = c->stats;
 }
 
@@ -415,11 +436,30 @@ int rt_postprocess(rt_ctx *c)
 }
 
 // ---- direct gather ---------------------------------------------------------------------------
+int rt_set_frame_targets(rt_ctx *c, int count, void *const *frames, const int *row_end)
+{
+    if (!c) return RT_EINVAL;
+    if (count < 0 || count > RT_MAX_RANKS || (count > 0 && (!frames || !row_end)))
+        return fail(c, RT_EINVAL, "rt_set_frame_targets: %d targets (at most %d)", count, RT_MAX_RANKS);
+    int prev = 0;
+    for (int k = 0; k < count; k++) {
+        if (!frames[k] || row_end[k] < prev || row_end[k] > c->cfg.height)
+            return fail(c, RT_EINVAL, "rt_set_frame_targets: target %d: image %p, rows end at %d (after %d, frame height %d)",
+                        k, frames[k], row_end[k], prev, c->cfg.height);
+        prev = row_end[k];
+    }
+    if (count > 0 && prev != c->cfg.height)
+        return fail(c, RT_EINVAL, "rt_set_frame_targets: the targets cover %d of %d rows", prev, c->cfg.height);
+    for (int k = 0; k < count; k++) { c->frame_targets[k] = (float4 *)frames[k]; c->frame_target_end[k] = row_end[k]; }
+    c->frame_target_count = count;
+    return RT_OK;
+}
+
 int rt_set_frame_target(rt_ctx *c, void *frame)
 {
     if (!c) return RT_EINVAL;
-    c->frame_target = (float4 *)frame;
-    return RT_OK;
+    const int h = c->cfg.height;
+    return rt_set_frame_targets(c, frame ? 1 : 0, &frame, &h);
 }
 
 int rt_link_peers(rt_ctx *c, int rank, int world, void *const *mailboxes, void *next_recv_lo, void *prev_recv_hi)
@@ -669,6 +709,35 @@ int rt_download_color_overlapped(rt_ctx *c, int slot, void *pinned_host, size_t 
     CU(c, cudaMemcpyAsync(pinned_host, c->ring_color + (size_t)slot * c->npix, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
     CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
     c->copy_pending[h] = true;
+    return RT_OK;
+}
+
+int rt_frame_download_overlapped(rt_ctx *c, const void *frame, int y0, int rows, void *pinned_host, size_t bytes)
+{
+    if (!c || !frame || !pinned_host) return RT_EINVAL;
+    if (y0 < 0 || rows < 0 || y0 + rows > c->cfg.height)
+        return fail(c, RT_EINVAL, "rt_frame_download_overlapped: rows [%d, %d) outside the frame (height %d)", y0, y0 + rows, c->cfg.height);
+    const size_t row_bytes = (size_t)c->cfg.width * 16;
+    if (bytes != (size_t)rows * row_bytes)
+        return fail(c, RT_EINVAL, "rt_frame_download_overlapped: expected %zu bytes, got %zu", (size_t)rows * row_bytes, bytes);
+    CU(c, cudaSetDevice(c->cfg.device));
+    const int h = c->rgba8_flip;
+    c->rgba8_flip ^= 1;
+    CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    if (rows > 0)
+        CU(c, cudaMemcpyAsync(pinned_host, (const char *)frame + (size_t)y0 * row_bytes, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
+    c->copy_pending[h] = true;
+    return RT_OK;
+}
+
+int rt_stream_wait_readback(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    CU(c, cudaSetDevice(c->cfg.device));
+    const int newest = c->rgba8_flip ^ 1;   // the copy stream runs in order: the newest event covers the older one
+    if (c->copy_pending[newest]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[newest], 0));
     return RT_OK;
 }
 

@@ -46,7 +46,7 @@ __device__ __forceinline__ void flush_stats(unsigned long long *stats, const int
 // One thread per pixel.  The AA samples and their <= RD path segments are flattened into ONE loop
 // whose body is one segment, so a warp stays converged on the intersection code and its run time is
 // max over lanes of the pixel's total segment count (not the sum over samples of the per-sample max).
-__global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     __shared__ float4 s_rand[2 * RT_MAX_AA];
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid
         const float fAA = (float)p.AA;
         float4 c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
         o.color[pix] = c;
-        if (o.gather) o.gather[pix] = c;
+        gather_store(o.gather, yl, pix, c);
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
         o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
         o.depth_w[pix] = __fdiv_rn(dw, fAA);
@@ -214,7 +214,7 @@ __device__ __forceinline__ float4 phong_shade(const FrameParams &p, float4 att, 
     return scale4(0.06f, att);
 }
 
-__global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_co
         // result_color = vec4(0) + phong(dir)
         const float4 c = gamma_correct(0.0f + col.x, 0.0f + col.y, 0.0f + col.z);
         o.color[pix] = c;
-        if (o.gather) o.gather[pix] = c;
+        gather_store(o.gather, yl, pix, c);
         o.hit[pix] = ind;
     }
     const int idx[5] = { ST_RAYS_CLOSEST, ST_RAYS_SHADOW, ST_SHADED, ST_PIXELS, ST_PRIMARY };
@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_co
     flush_stats<5>(o.stats, idx, val);
 }
 
-__global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_constant__ FrameParams p, TraceOut o)
+__global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_c
         }
         const float4 c = gamma_correct(0.0f + result.x, 0.0f + result.y, 0.0f + result.z);
         o.color[pix] = c;
-        if (o.gather) o.gather[pix] = c;
+        gather_store(o.gather, yl, pix, c);
         o.hit[pix] = first_ind;
         if (p.pad0 & RT_FLAG_PHONG_GBUFFER) {
             o.normal[pix] = g_normal;
@@ -557,7 +557,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             color = div4(add4(scale4(0.9f, color), color_sum), denominator);
         }
         q.ring_color[(size_t)q.slot * plane + pix] = color; // pixels[new_frame] and img_output
-        if (q.gather) q.gather[pix] = color;                // rt_set_frame_target: the assembled frame, maybe over NVLink
+        gather_store(q.gather, yl, pix, color);             // rt_set_frame_targets: the assembled frame, maybe over NVLink
     }
     // per-warp flush, no block barrier: a warp of background pixels must not wait for its block-mates
     const int idx[3] = { ST_PP_NONBACKGROUND, ST_PP_HIST_EVALUATED, ST_PP_HIST_ACCEPTED };

@@ -80,6 +80,26 @@ struct TailQueue {
     int parity;
 };
 
+// rt_set_frame_targets: where the final colour of this band goes besides the ring slot.  Segment k covers the
+// band-local rows [row_end[k-1], row_end[k]) (row_end[-1] = 0, row_end[count-1] = rows of the band); img[k] is
+// the whole-frame image that owns those rows (maybe peer memory), already offset to the band's first row so that
+// the band-local pixel index addresses it.  count == 0: no target.
+struct GatherTargets {
+    float4 *img[RT_MAX_RANKS];
+    int row_end[RT_MAX_RANKS];
+    int count;
+};
+// the struct must live in the constant bank (a __grid_constant__ kernel parameter): row_end/img are indexed
+__device__ __forceinline__ void gather_store(const GatherTargets &g, int yl, size_t pix, const float4 &c)
+{
+    if (g.count) {
+        int k = 0;
+#pragma unroll 1
+        while (k < g.count - 1 && yl >= g.row_end[k]) k++;
+        g.img[k][pix] = c;
+    }
+}
+
 // output planes of one trace dispatch; all row-major [rows][W] of this band
 struct TraceOut {
     float4 *color;    // ring colour plane of the slot, or the raw plane in mode 1
@@ -92,7 +112,7 @@ struct TraceOut {
     int ao_kernel;    // AO_KERNEL_*
     TailQueue tq;     // AO_KERNEL_QUEUED
     const float *sky; // [6] all-background colour sum and its gamma (rt_sky_gamma_kernel), phased AO kernel
-    float4 *gather;   // rt_set_frame_target: this band's rows inside a whole-frame image (maybe peer memory), or null
+    GatherTargets gather; // rt_set_frame_target(s): the assembled frame(s) this band's final colour also goes into
 };
 
 // a halo record row: three consecutive arrays of W elements
@@ -123,7 +143,7 @@ struct PostParams {
     const float *ring_depth_w;
     void *halo_lo, *halo_hi;   // received records: row y0-1 (or the wrapped row) / row y0+rows
     void *send_lo, *send_hi;   // packed by the pack kernel
-    float4 *gather;            // like TraceOut::gather, for the post-processed colour of mode 1
+    GatherTargets gather;      // like TraceOut::gather, for the post-processed colour of mode 1
     float4 rand_last;          // rand_buffer[2*AA-1]: what pixels[0][0][-1] aliases (FLAT32)
     unsigned long long *stats;
 };

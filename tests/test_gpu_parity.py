@@ -338,7 +338,92 @@ def test_frame_target_assembles_the_bands(kernel, monkeypatch):
     o.close()
 
 
-def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q):
+@pytest.mark.parametrize("kernel", ["phased", "queued", "tile", "stream"])
+def test_split_frame_targets_spread_the_rows_over_their_owners(kernel, monkeypatch):
+    """rt_set_frame_targets: three images own rows [0,20), [20,20) (none) + [20,41) and [41,57) of the frame;
+    three bands whose cuts do NOT coincide with the owners' store every pixel into its owner.  Each image must
+    hold the oracle's rows inside its share and stay untouched outside it; rt_frame_download_overlapped then
+    reads the shares back into one host image (the path each rank takes over its own PCIe link)."""
+    import torch
+
+    from real_time_ray_tracer_b200 import bands
+
+    monkeypatch.setenv("RT_AO_KERNEL", kernel)
+    W, H, AA = 101, 57, 4
+    cuts = [0, 9, 30, 57]
+    ends = [20, 20, 41, 57]
+    n = len(cuts) - 1
+    frames = [api.Frame.create(W, H, 0) for _ in ends]
+    imgs = [bands.device_tensor(f.ptr, f.nbytes, 0) for f in frames]
+    rts = [rtb.RayTracer(W, H, AA, band_y0=cuts[i], band_rows=cuts[i + 1] - cuts[i], band_index=i, band_count=n)
+           for i in range(n)]
+    engs = [bands.GpuBandEngine(rt) for rt in rts]
+    sc = Scenario("scene6", keys=("a",))
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(sc.shapes, sc.n)
+    for rt in rts:
+        rt.upload_scene(sc.shapes, sc.n)
+        rt.set_frame_targets([f.ptr for f in frames], ends)
+    host_img = torch.empty(H * W * 4, dtype=torch.float32, pin_memory=True)
+    for k, mode in enumerate((2, 3, 4, 1, 2)):
+        for im in imgs:
+            im.fill_(-7.0)
+        torch.cuda.synchronize()
+        slot, u, rb = sc.next(mode, AA)
+        for e in engs:
+            e.render_frame(mode, u, rb)
+            if mode == 1:
+                e.halo_pack()
+        if mode == 1:
+            for rt in rts:
+                rt.synchronize()
+            for i, e in enumerate(engs):
+                engs[(i + 1) % n].recv_lo.copy_(e.send_hi)
+                if i > 0:
+                    engs[i - 1].recv_hi.copy_(e.send_lo)
+            torch.cuda.synchronize()
+            for e in engs:
+                e.postprocess()
+        for rt in rts:
+            rt.synchronize()
+        o.render(mode, u, rb)
+        if mode == 1:
+            o.postprocess()
+        want = o.get(orc.IMAGE)
+        y0 = 0
+        for j, y1 in enumerate(ends):
+            got = imgs[j].cpu().numpy().reshape(H, W, 4)
+            assert same_bits(got[y0:y1], want[y0:y1]), f"frame {k} mode {mode} owner {j}: {diff_report(got[y0:y1], want[y0:y1])}"
+            outside = np.concatenate([got[:y0].ravel(), got[y1:].ravel()])
+            assert (outside == -7.0).all(), f"frame {k} mode {mode}: owner {j} was written outside rows [{y0}, {y1})"
+            y0 = y1
+        # the read-back of the shares, each through the context that "owns" it
+        host_img.fill_(0.0)
+        y0 = 0
+        for j, y1 in enumerate(ends):
+            rt = rts[j % n]
+            rt.frame_download_overlapped(frames[j].ptr, y0, y1 - y0, host_img.data_ptr() + y0 * W * 16, (y1 - y0) * W * 16)
+            rt.stream_wait_readback()
+            y0 = y1
+        for rt in rts:
+            rt.readback_wait(0)
+        assert same_bits(host_img.numpy().reshape(H, W, 4), want)
+    # argument checks
+    with pytest.raises(rtb.RtError):
+        rts[0].set_frame_targets([frames[0].ptr, frames[1].ptr], [30, 50])     # does not cover the frame
+    with pytest.raises(rtb.RtError):
+        rts[0].set_frame_targets([frames[0].ptr, frames[1].ptr], [40, 30])     # not ascending
+    with pytest.raises(rtb.RtError):
+        rts[0].frame_download_overlapped(frames[0].ptr, 50, 10, host_img.data_ptr(), 10 * W * 16)
+    rts[0].set_frame_targets([], [])
+    for rt in rts:
+        rt.close()
+    for f in frames:
+        f.close()
+    o.close()
+
+
+def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, owners="rank0"):
     import os
 
     import torch
@@ -354,7 +439,8 @@ def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q):
         y0, rows = cuts[rank], cuts[rank + 1] - cuts[rank]
         sc = Scenario("scene1", keys=("d",))
         with rtb.RayTracer(W, H, AA, device=dev, band_y0=y0, band_rows=rows, band_index=rank, band_count=world) as rt:
-            dg = bands.DirectGather(W, H, rank, world, dev, tracer=rt, fence=fence)
+            dg = bands.DirectGather(W, H, rank, world, dev, tracer=rt, fence=fence, owners=owners)
+            shf = bands.SharedHostFrames(W, H, rank, world, f"own{port}", barrier=dist.barrier) if owners == "rows" else None
             rt.upload_scene(sc.shapes, sc.n)
             br = bands.BandedRenderer(bands.GpuBandEngine(rt), W, H, [(cuts[i], cuts[i + 1] - cuts[i]) for i in range(world)],
                                       rank, world, direct=dg)
@@ -364,29 +450,39 @@ def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q):
                 br.render(mode, u, rb)
                 kf = br.frame_k
                 br.gather_start(slot)          # the fence
+                if owners == "rows":
+                    # every rank reads the rows it owns back into the host image the ranks share
+                    oy0, orows = dg.own_rows
+                    rt.frame_download_overlapped(dg.frames[kf % len(dg.frames)].ptr, oy0, orows,
+                                                 shf.band_ptr(k, oy0), orows * W * 16)
+                    rt.readback_wait(0)
                 rt.synchronize()
                 dist.barrier()
                 if rank == 0:
                     torch.cuda.synchronize()
-                    out.append(dg.frame(kf).cpu().numpy().reshape(H, W, 4).copy())
+                    out.append(shf.image(k).copy() if owners == "rows" else
+                               dg.frame(kf).cpu().numpy().reshape(H, W, 4).copy())
+                dist.barrier()
             if fence == "flags":
                 assert not rt.fence_timed_out()
             dist.barrier()
             if rank == 0:
                 q.put(out)
             dist.barrier()
+            if shf is not None:
+                shf.close(barrier=dist.barrier)
             dg.close()
     finally:
         dist.destroy_process_group()
 
 
-def _run_ranks(world, W, H, AA, cuts, modes, fence, one_gpu):
+def _run_ranks(world, W, H, AA, cuts, modes, fence, one_gpu, owners="rank0"):
     import torch.multiprocessing as mp
 
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29650 + int(np.random.default_rng().integers(0, 200))
-    procs = [ctx.Process(target=_ipc_worker, args=(r, world, port, W, H, AA, cuts, modes, fence, one_gpu, q))
+    procs = [ctx.Process(target=_ipc_worker, args=(r, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, owners))
              for r in range(world)]
     for p in procs:
         p.start()
@@ -483,6 +579,26 @@ def test_direct_gather_across_processes_over_cuda_ipc():
     that must equal the oracle's.  Across GPUs the only difference is that the mapping goes over NVLink.
     The fence here is a gloo all-reduce: two ranks sharing one GPU must not spin on each other (rt_fence)."""
     _run_ranks(2, 88, 50, 4, [0, 21, 50], (2, 4, 3), "allreduce", True)
+
+
+def test_row_owners_across_processes_over_cuda_ipc():
+    """owners="rows" (rt_set_frame_targets): both ranks hold images, each owns half the rows (25 of 50, while the
+    bands are 21 + 29 rows), the kernels store every pixel into its owner's image through the IPC mapping, and each
+    rank reads its half back into the shared host image -- which must equal the oracle's frame.  (Mode 1 across
+    processes needs the halo exchange over peer memory or NCCL, i.e. one GPU per rank: the next test.)"""
+    _run_ranks(2, 88, 50, 4, [0, 21, 50], (2, 4, 3, 2), "allreduce", True, owners="rows")
+
+
+def test_row_owners_with_linked_bands_on_separate_gpus():
+    """as above with one GPU per rank, rt_fence and direct halo rows: the path bench.py's e2e leg takes"""
+    import torch
+
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs one GPU per rank (run under gpurun --gpus 2)")
+    world = min(n, 4)
+    cuts = {2: [0, 21, 50], 3: [0, 9, 30, 50], 4: [0, 9, 10, 33, 50]}[world]
+    _run_ranks(world, 88, 50, 4, cuts, (1, 1, 2, 1, 1, 4, 1, 3, 1), "flags", False, owners="rows")
 
 
 def test_linked_bands_fence_and_direct_halo_on_separate_gpus():
