@@ -230,6 +230,8 @@ def run_b200(args) -> None:
         if (world > 1 and not args.nccl_gather) else None
     if direct is not None:
         direct.split = False
+        if direct.halo_direct and not args.mode1_store_gather:
+            direct.mode1_gather = "copy"
     br = bands.BandedRenderer(eng, W, H, plan, rank, world, direct=direct)
     # rank 0 assembles frames in two alternating buffers so the gather of frame k overlaps the trace of k+1
     fulls = [torch.empty(W * H * 4, dtype=torch.float32, device=f"cuda:{local}") for _ in range(2)] \
@@ -262,6 +264,7 @@ def run_b200(args) -> None:
     def drain():
         br.gather_finish(pending["works"])
         pending["works"] = []
+        br.gather_flush()
 
     sampler = ClockSampler(local)
     if rank == 0:
@@ -351,16 +354,19 @@ def run_b200(args) -> None:
                        "recursion_depth": host.RECURSION_DEPTH, "ring_frames": host.NUM_FRAMES,
                        "parallelism": f"row-bands x{world}", "bands": plan,
                        "gather": ("none" if world == 1 else "nccl p2p" if direct is None else
-                                  f"direct NVLink stores into rank 0's image (e2e leg: into the images of the ranks that own the rows, "
-                                  f"equal shares), halo rows stored into the neighbours, fence = {args.fence}"),
+                                  (f"band copies into rank 0's image under the next frame's trace kernel" if (mode == 1 and direct.mode1_gather == "copy")
+                                   else f"direct NVLink stores into rank 0's image")
+                                  + f" (e2e leg: kernel stores into the images of the ranks that own the rows, equal shares), "
+                                    f"halo rows stored into the neighbours, fence = {args.fence}"),
                        "l2": "no input reuse: ~1.4 KB of kernel parameters in, each frame writes a different "
                              "ring slot (8 x %.0f MB > 126 MB L2)" % (W * H * 44 / 1e6)},
             "rays_per_frame": rays / K,
             "roofline": roof, "clocks": clocks,
             # this library's kernels per frame and rank: trace (+ halo pack + post-process in mode 1), plus the
-            # rt_fence kernels of linked bands (one per frame, two in mode 1)
+            # rt_fence kernels of linked bands (one per frame; two in mode 1 unless the bands travel as copies)
             "gpu_launches": K * world * ((1 if mode != 1 else 3)
-                                         + ((1 if mode != 1 else 2) if (direct is not None and direct.halo_direct) else 0)),
+                                         + ((1 if (mode != 1 or direct.mode1_gather == "copy") else 2)
+                                            if (direct is not None and direct.halo_direct) else 0)),
         }
         if mode == 1 and pp_ms:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
@@ -714,6 +720,9 @@ def main():
                          "communication call) or a one-element NCCL all-reduce")
     ap.add_argument("--e2e-via-rank0", action="store_true",
                     help="N > 1: e2e reads the assembled frame back through rank 0's PCIe link only")
+    ap.add_argument("--mode1-store-gather", action="store_true",
+                    help="N > 1, mode 1: the post-processing kernel stores into rank 0's image (NVLink-ingress-bound at "
+                         "8 GPUs) instead of the copy that overlaps the next frame's trace kernel")
     ap.add_argument("--e2e-own-bands", action="store_true",
                     help="N > 1 e2e: every rank reads back its own (compute-balanced) band instead of an equal share "
                          "of the frame assembled with rt_set_frame_targets")

@@ -239,6 +239,13 @@ int rt_set_frame_targets(rt_ctx *ctx, int count, void *const *frames, const int 
  * stream, ordered after the work enqueued on the context's stream so far (normally the rt_fence that closes
  * the frame); rt_readback_wait covers it.  `pinned_host` is where row y0 lands. */
 int rt_frame_download_overlapped(rt_ctx *ctx, const void *frame, int y0, int rows, void *pinned_host, size_t bytes);
+/* Copy gather: this band's colour plane of pixels[slot] -> rows [band_y0, band_y0 + band_rows) of a frame image
+ * (maybe another GPU's), on the copy stream, ordered after the work enqueued on the context's stream so far.
+ * The alternative to storing from the kernel (rt_set_frame_target) when the producing kernel is short and
+ * the target GPU's NVLink ingress would bound it -- mode 1 at 8 GPUs: the post-processing kernels of 7 ranks
+ * would push 7/8 of the frame into rank 0 within 0.2 ms -- because the copy overlaps the NEXT frame's trace
+ * kernel.  rt_stream_wait_readback before the next rt_fence then closes the frame on all ranks. */
+int rt_band_to_frame_overlapped(rt_ctx *ctx, int slot, void *frame);
 /* the context's stream waits, on the device, for the read-backs issued so far: enqueue it before the
  * rt_fence after which other ranks may overwrite a frame image that is still being read back */
 int rt_stream_wait_readback(rt_ctx *ctx);

@@ -114,6 +114,11 @@ class RayTracer:
         self._check(self.lib.rt_frame_download_overlapped(self.h, C.c_void_p(frame_ptr), y0, rows,
                                                           C.c_void_p(pinned_ptr), nbytes))
 
+    def band_to_frame_overlapped(self, slot: int, frame_ptr: int):
+        """rt_band_to_frame_overlapped: this band's colour plane of pixels[slot] -> its rows of the frame image
+        (own or imported), on the library's copy stream"""
+        self._check(self.lib.rt_band_to_frame_overlapped(self.h, slot, C.c_void_p(frame_ptr)))
+
     def stream_wait_readback(self):
         """rt_stream_wait_readback: the context's stream waits (on the device) for the read-backs issued so far"""
         self._check(self.lib.rt_stream_wait_readback(self.h))

@@ -96,6 +96,9 @@ class GpuBandEngine:
     def set_frame_targets(self, ptrs, row_end):
         self.rt.set_frame_targets(ptrs, row_end)
 
+    def band_to_frame(self, slot, ptr):
+        self.rt.band_to_frame_overlapped(slot, ptr)
+
     def fence(self):
         self.rt.fence()
 
@@ -141,6 +144,10 @@ class DirectGather:
         self.fence_kind, self.tracer, self.mailbox, self.maps = fence, tracer, None, []
         self.owners, self.height = owners, height
         self.split = owners == "rows"   # owners="rows" only: False = gather to rank 0's image after all
+        # how a mode-1 frame reaches rank 0's image: "store" = from the post-processing kernel, like the other
+        # modes; "copy" = rt_band_to_frame_overlapped after it, overlapping the next frame's trace kernel (the
+        # frame is then complete after the NEXT frame's halo fence, or BandedRenderer.gather_flush)
+        self.mode1_gather = "store"
         if owners == "rows":
             if tracer is None:
                 raise ValueError("owners='rows' needs the band's RayTracer")
@@ -230,8 +237,8 @@ class DirectGather:
     def fence(self):
         import torch.distributed as dist
 
-        if self.owners == "rows":
-            self.tracer.stream_wait_readback()
+        if self.tracer is not None:
+            self.tracer.stream_wait_readback()   # copies this rank still has in flight belong to the fenced frame
         if self.fence_kind == "flags":
             self.tracer.fence()
         elif self.world > 1:
@@ -269,6 +276,12 @@ class BandedRenderer:
         self.e, self.W, self.H = engine, width, height
         self.bands, self.rank, self.world, self.group = bands, rank, world, group
         self.direct, self.frame_k = direct, 0
+        self._copy, self._copy_pending = False, False
+
+    def _copy_gather(self, mode: int) -> bool:
+        d = self.direct
+        return (mode == 1 and self.world > 1 and d is not None and d.mode1_gather == "copy"
+                and not (d.owners == "rows" and d.split))
 
     def exchange_halo(self):
         """send_hi -> recv_lo of band (r+1) % n (the last band's send_hi is the wrapped row image row 0
@@ -288,8 +301,11 @@ class BandedRenderer:
             w.wait()
 
     def render(self, mode: int, uniforms, rand_buffer):
+        self._copy = self._copy_gather(mode)
         if self.direct is not None:
-            if self.direct.owners == "rows" and self.direct.split:
+            if self._copy:
+                self.e.set_frame_target(None)
+            elif self.direct.owners == "rows" and self.direct.split:
                 self.e.set_frame_targets(*self.direct.targets(self.frame_k))
             else:
                 self.e.set_frame_target(self.direct.target(self.frame_k))
@@ -311,8 +327,15 @@ class BandedRenderer:
         import torch.distributed as dist
 
         if self.direct is not None:
-            # the bands are already in (or on their way into) rank 0's image direct.frame(frame_k): fence only
-            self.direct.fence()
+            if self._copy:
+                # copy engine, behind the post-processing kernel and under the next frame's trace kernel; the
+                # next fence on this stream (the next frame's halo fence) waits for it and closes the frame
+                self.e.band_to_frame(slot, self.direct.target(self.frame_k))
+                self._copy_pending = True
+            else:
+                # the bands are already in (or on their way into) the image(s) of frame_k: fence only
+                self.direct.fence()
+                self._copy_pending = False
             self.frame_k += 1
             return []
         mine = self.e.band_color(slot)
@@ -330,6 +353,12 @@ class BandedRenderer:
                     ops.append(dist.P2POp(dist.irecv, dst, r, self.group))
             return dist.batch_isend_irecv(ops)
         return dist.batch_isend_irecv([dist.P2POp(dist.isend, mine, 0, self.group)])
+
+    def gather_flush(self):
+        """closes a frame whose bands are still travelling as copies (mode1_gather="copy")"""
+        if self.direct is not None and self._copy_pending:
+            self.direct.fence()
+            self._copy_pending = False
 
     @staticmethod
     def gather_finish(works):

@@ -732,6 +732,23 @@ int rt_frame_download_overlapped(rt_ctx *c, const void *frame, int y0, int rows,
     return RT_OK;
 }
 
+int rt_band_to_frame_overlapped(rt_ctx *c, int slot, void *frame)
+{
+    if (!c || !frame) return RT_EINVAL;
+    if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
+    CU(c, cudaSetDevice(c->cfg.device));
+    const int h = c->rgba8_flip;
+    c->rgba8_flip ^= 1;
+    CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    // contiguous rows on both sides; `frame` may be an imported mapping: the copy engine moves it over NVLink
+    CU(c, cudaMemcpyAsync((float4 *)frame + (size_t)c->cfg.band_y0 * c->cfg.width, c->ring_color + (size_t)slot * c->npix,
+                          c->npix * 16, cudaMemcpyDefault, c->copy_stream));
+    CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
+    c->copy_pending[h] = true;
+    return RT_OK;
+}
+
 int rt_stream_wait_readback(rt_ctx *c)
 {
     if (!c) return RT_EINVAL;

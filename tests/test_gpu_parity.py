@@ -423,7 +423,61 @@ def test_split_frame_targets_spread_the_rows_over_their_owners(kernel, monkeypat
     o.close()
 
 
-def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, owners="rank0"):
+def test_band_copies_assemble_the_frame():
+    """rt_band_to_frame_overlapped: the bands' colour planes copied (copy stream) into one whole-frame image,
+    in mode 1 after the post-processing pass; rt_stream_wait_readback orders the stream behind the copies."""
+    import torch
+
+    from real_time_ray_tracer_b200 import bands
+
+    W, H, AA = 77, 45, 4
+    cuts = [0, 13, 45]
+    n = len(cuts) - 1
+    frame = api.Frame.create(W, H, 0)
+    img = bands.device_tensor(frame.ptr, frame.nbytes, 0)
+    rts = [rtb.RayTracer(W, H, AA, band_y0=cuts[i], band_rows=cuts[i + 1] - cuts[i], band_index=i, band_count=n)
+           for i in range(n)]
+    engs = [bands.GpuBandEngine(rt) for rt in rts]
+    sc = Scenario("scene1", keys=("d",))
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(sc.shapes, sc.n)
+    for rt in rts:
+        rt.upload_scene(sc.shapes, sc.n)
+    for k, mode in enumerate((1, 1, 3, 1)):
+        slot, u, rb = sc.next(mode, AA)
+        for e in engs:
+            e.render_frame(mode, u, rb)
+            if mode == 1:
+                e.halo_pack()
+        if mode == 1:
+            for rt in rts:
+                rt.synchronize()
+            for i, e in enumerate(engs):
+                engs[(i + 1) % n].recv_lo.copy_(e.send_hi)
+                if i > 0:
+                    engs[i - 1].recv_hi.copy_(e.send_lo)
+            torch.cuda.synchronize()
+            for e in engs:
+                e.postprocess()
+        for e in engs:
+            e.band_to_frame(slot, frame.ptr)
+            e.rt.stream_wait_readback()
+        for rt in rts:
+            rt.synchronize()
+        o.render(mode, u, rb)
+        if mode == 1:
+            o.postprocess()
+        got = img.cpu().numpy().reshape(H, W, 4)
+        assert same_bits(got, o.get(orc.IMAGE)), f"frame {k} mode {mode}: {diff_report(got, o.get(orc.IMAGE))}"
+    with pytest.raises(rtb.RtError):
+        rts[0].band_to_frame_overlapped(99, frame.ptr)
+    for rt in rts:
+        rt.close()
+    frame.close()
+    o.close()
+
+
+def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, owners="rank0", mode1_gather="store"):
     import os
 
     import torch
@@ -440,22 +494,15 @@ def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, own
         sc = Scenario("scene1", keys=("d",))
         with rtb.RayTracer(W, H, AA, device=dev, band_y0=y0, band_rows=rows, band_index=rank, band_count=world) as rt:
             dg = bands.DirectGather(W, H, rank, world, dev, tracer=rt, fence=fence, owners=owners)
+            dg.mode1_gather = mode1_gather
             shf = bands.SharedHostFrames(W, H, rank, world, f"own{port}", barrier=dist.barrier) if owners == "rows" else None
             rt.upload_scene(sc.shapes, sc.n)
             br = bands.BandedRenderer(bands.GpuBandEngine(rt), W, H, [(cuts[i], cuts[i + 1] - cuts[i]) for i in range(world)],
                                       rank, world, direct=dg)
             out = []
-            for k, mode in enumerate(modes):
-                slot, u, rb = sc.next(mode, AA)
-                br.render(mode, u, rb)
-                kf = br.frame_k
-                br.gather_start(slot)          # the fence
-                if owners == "rows":
-                    # every rank reads the rows it owns back into the host image the ranks share
-                    oy0, orows = dg.own_rows
-                    rt.frame_download_overlapped(dg.frames[kf % len(dg.frames)].ptr, oy0, orows,
-                                                 shf.band_ptr(k, oy0), orows * W * 16)
-                    rt.readback_wait(0)
+            deferred = mode1_gather == "copy"   # a frame is closed by the NEXT frame's fence: read one frame late
+
+            def read_frame(k, kf):
                 rt.synchronize()
                 dist.barrier()
                 if rank == 0:
@@ -463,6 +510,30 @@ def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, own
                     out.append(shf.image(k).copy() if owners == "rows" else
                                dg.frame(kf).cpu().numpy().reshape(H, W, 4).copy())
                 dist.barrier()
+
+            for k, mode in enumerate(modes):
+                slot, u, rb = sc.next(mode, AA)
+                br.render(mode, u, rb)
+                kf = br.frame_k
+                br.gather_start(slot)          # the fence (store gather) or the band copy (copy gather)
+                if deferred:
+                    if k > 0:
+                        read_frame(k - 1, kf - 1)
+                    continue
+                if owners == "rows":
+                    # every rank reads the rows it owns back into the host image the ranks share
+                    oy0, orows = dg.own_rows
+                    if fence == "allreduce":
+                        # gloo's all-reduce does not order the tracer's private stream: close the frame by hand
+                        rt.synchronize()
+                        dist.barrier()
+                    rt.frame_download_overlapped(dg.frames[kf % len(dg.frames)].ptr, oy0, orows,
+                                                 shf.band_ptr(k, oy0), orows * W * 16)
+                    rt.readback_wait(0)
+                read_frame(k, kf)
+            if deferred:
+                br.gather_flush()
+                read_frame(len(modes) - 1, br.frame_k - 1)
             if fence == "flags":
                 assert not rt.fence_timed_out()
             dist.barrier()
@@ -476,13 +547,13 @@ def _ipc_worker(rank, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, own
         dist.destroy_process_group()
 
 
-def _run_ranks(world, W, H, AA, cuts, modes, fence, one_gpu, owners="rank0"):
+def _run_ranks(world, W, H, AA, cuts, modes, fence, one_gpu, owners="rank0", mode1_gather="store"):
     import torch.multiprocessing as mp
 
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29650 + int(np.random.default_rng().integers(0, 200))
-    procs = [ctx.Process(target=_ipc_worker, args=(r, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, owners))
+    procs = [ctx.Process(target=_ipc_worker, args=(r, world, port, W, H, AA, cuts, modes, fence, one_gpu, q, owners, mode1_gather))
              for r in range(world)]
     for p in procs:
         p.start()
@@ -612,6 +683,8 @@ def test_linked_bands_fence_and_direct_halo_on_separate_gpus():
     world = min(n, 4)
     cuts = {2: [0, 21, 50], 3: [0, 9, 30, 50], 4: [0, 9, 10, 33, 50]}[world]
     _run_ranks(world, 88, 50, 4, cuts, (1, 1, 1, 2, 1, 1, 4, 1, 1, 1, 1), "flags", False)
+    # mode-1 bands travelling as copies under the next frame (rt_band_to_frame_overlapped), closed one frame late
+    _run_ranks(world, 88, 50, 4, cuts, (1, 1, 2, 1, 1, 4, 3, 1, 1), "flags", False, mode1_gather="copy")
 
 
 @pytest.mark.parametrize("kernel", ["phased", "queued", "tile", "stream"])
