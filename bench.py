@@ -498,8 +498,26 @@ def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, bar
     dist.broadcast_object_list(box, src=0)
     shf = _bands.SharedHostFrames(W, H, rank, world, f"{box[0]}", barrier=dist.barrier)
     y0, rows = plan[rank]
+    link_rates = None
     if split is not None:
         split.split = True
+        # Shares proportional to what each link delivers when ALL ranks read back at once (set-up, untimed):
+        # behind a shared PCIe fabric the links differ (tools/probes/pcie_numa_probe.py).
+        oy0, orows = split.own_rows
+        reps = 6
+        for timed in (False, True):
+            barrier()
+            tq = time.perf_counter()
+            for _ in range(reps):
+                rt.frame_download_overlapped(split.frames[0].ptr, oy0, orows, shf.band_ptr(0, oy0), orows * W * 16)
+            rt.readback_wait(0)
+            dq = time.perf_counter() - tq
+        rate = torch.tensor([orows * W * 16 * reps / dq / 1e9], dtype=torch.float64, device=f"cuda:{local}")
+        rates = [torch.zeros_like(rate) for _ in range(world)]
+        dist.all_gather(rates, rate)
+        link_rates = [round(float(r.item()), 1) for r in rates]
+        if not os.environ.get("RT_EQUAL_SHARES"):
+            split.set_shares(link_rates)
         oy0, orows = split.own_rows
     rt.reset_stats()
     barrier()
@@ -547,6 +565,7 @@ def run_e2e_banded(torch, dist, fr, rt, br, plan, rank, world, local, steps, bar
             "ms_per_step": round(dt / steps * 1e3, 4), "steps": steps,
             "h2d_bytes_per_step": int(world * (fr.n * 80 + 112 + (8 * fr.AA * 4 if fr.mode in (1, 2) else 0))),
             "d2h_bytes_per_step": int(W * H * 16),
+            "link_gb_per_s_all_reading": link_rates,
             "d2h_bytes_per_link": ([int((split.row_end[j] - (split.row_end[j - 1] if j else 0)) * W * 16) for j in range(world)]
                                    if split is not None else [int(r * W * 16) for _, r in plan]),
             "what": "upload_scene + uniforms + rand_buffer from host on every rank, render (+halo, post-process), "

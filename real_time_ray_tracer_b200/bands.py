@@ -113,6 +113,22 @@ class GpuBandEngine:
         return self._color[slot]
 
 
+def shares_to_row_end(height: int, weights) -> List[int]:
+    """row_end[] of rt_set_frame_targets for owners whose shares of the rows are proportional to ``weights``:
+    ascending, the last one == height; a zero weight gives an empty share."""
+    tot = float(sum(weights))
+    if tot <= 0 or min(weights) < 0:
+        raise ValueError("shares_to_row_end: weights must be >= 0 and not all zero")
+    acc, ends = 0.0, []
+    for w in weights:
+        acc += float(w)
+        ends.append(min(height, int(round(height * acc / tot))))
+    ends[-1] = height
+    for j in range(1, len(ends)):
+        ends[j] = max(ends[j], ends[j - 1])
+    return ends
+
+
 class DirectGather:
     """Whole-frame images on rank 0 that every rank's kernels write their band into (rt_set_frame_target).
 
@@ -221,6 +237,14 @@ class DirectGather:
         """(image pointers, row_end) of frame k for rt_set_frame_targets"""
         b = k % len(self.frames)
         return [fr[b].ptr for fr in self.peer_frames], self.row_end
+
+    def set_shares(self, weights):
+        """owners="rows": rank j owns a share of the rows proportional to ``weights[j]`` (the same list on every
+        rank) -- e.g. each rank's measured read-back rate when all ranks read back at once: behind a shared
+        PCIe fabric the links are not equally fast (8 GPUs of one box measured 11.7 ... 20 GB/s each)."""
+        if self.owners != "rows" or len(weights) != self.world:
+            raise ValueError("set_shares: owners='rows' and one weight per rank")
+        self.row_end = shares_to_row_end(self.height, weights)
 
     @property
     def own_rows(self) -> Tuple[int, int]:

@@ -163,3 +163,18 @@ def test_plan_bands():
     assert all(r >= 1 for _, r in bands.plan_bands(5, 5, [100, 0, 0, 0, 0]))
     with pytest.raises(ValueError):
         bands.plan_bands(3, 4)
+
+
+def test_shares_to_row_end():
+    """row shares of the split frame targets (rt_set_frame_targets) from per-link weights"""
+    from real_time_ray_tracer_b200 import bands
+
+    assert bands.shares_to_row_end(1080, [1, 1, 1, 1]) == [270, 540, 810, 1080]
+    ends = bands.shares_to_row_end(1080, [11.7, 11.7, 11.8, 11.7, 18.2, 18.2, 18.2, 18.4])
+    assert ends[-1] == 1080 and ends == sorted(ends)
+    sizes = np.diff([0] + ends)
+    assert abs(sizes[0] - 1080 * 11.7 / 119.9) <= 1 and abs(sizes[7] - 1080 * 18.4 / 119.9) <= 1
+    assert bands.shares_to_row_end(7, [0, 1, 0]) == [0, 7, 7]
+    assert bands.shares_to_row_end(3, [1] * 5)[-1] == 3
+    with pytest.raises(ValueError):
+        bands.shares_to_row_end(10, [0, 0])

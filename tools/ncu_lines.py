@@ -5,7 +5,7 @@ import collections, csv, io, os, re, subprocess, sys, tempfile
 rep, pat = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 and sys.argv[3].isdigit() else 40
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-so = os.path.join(root, "real_time_ray_tracer_b200", "librt_b200.so")
+so = os.environ.get("RT_SO") or os.path.join(root, "real_time_ray_tracer_b200", "librt_b200.so")  # RT_SO: the build the report was captured with
 d = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=d, capture_output=True)
 ins = []   # (loc, text)
