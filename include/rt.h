@@ -66,7 +66,12 @@ enum {
      * and 4 also write normals_buffer[slot] = (n, 1) and depth_buffer[slot] = (t, path segments after the
      * first, 0, 1) of the camera ray's hit, zeros on a miss.  Off (0) = the shaders' behaviour: modes 3/4
      * leave both buffers as the last AO frame wrote them (p_compute.glsl:223-246). */
-    RT_FLAG_PHONG_GBUFFER = 1
+    RT_FLAG_PHONG_GBUFFER = 1,
+    /* Extension (the other half of that to-do: "... so they can use the same postprocessing"): a mode 3 or 4
+     * frame is finished by aop_postprocessing like a mode-1 frame -- rt_render_frame leaves the colour in the
+     * raw plane and rt_halo_pack / rt_postprocess blend it spatially and temporally into pixels[slot], using
+     * the normals and depths RT_FLAG_PHONG_GBUFFER (required) has written. */
+    RT_FLAG_PHONG_POSTPROCESS = 2
 };
 
 /* buffers of rt_download / rt_upload / rt_device_ptr */

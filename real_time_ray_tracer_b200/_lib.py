@@ -12,6 +12,7 @@ RT_OK, RT_EINVAL, RT_ENODEVICE, RT_ENOMEM, RT_ECUDA, RT_ESTATE = 0, -1, -2, -3, 
 MODE_AO_PP, MODE_AO, MODE_PHONG, MODE_HYBRID = 1, 2, 3, 4
 EDGE_FLAT32, EDGE_CLEAN = 0, 1
 FLAG_PHONG_GBUFFER = 1
+FLAG_PHONG_POSTPROCESS = 2
 BUF_COLOR, BUF_NORMAL, BUF_DEPTH, BUF_HIT_INDEX, BUF_IMAGE, BUF_RAW_COLOR, BUF_DEPTH_XY, BUF_DEPTH_W = range(8)
 LAYOUT_ROW_MAJOR, LAYOUT_REFERENCE = 0, 1
 MAX_SHAPES, MAX_AA, MAX_FRAMES = 10, 16, 16

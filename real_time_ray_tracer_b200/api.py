@@ -41,7 +41,12 @@ class RayTracer:
         self.y0 = band_y0
         self.rows = band_rows if band_rows else height - band_y0
         self.band_index, self.band_count = band_index, band_count
-        self.device = device
+        self.device, self.flags = device, flags
+
+    def needs_postprocess(self, mode: int) -> bool:
+        """True if a frame of this lighting mode is finished by halo_pack / postprocess: mode 1, and modes 3/4
+        under FLAG_PHONG_POSTPROCESS"""
+        return mode == L.MODE_AO_PP or (mode in (L.MODE_PHONG, L.MODE_HYBRID) and bool(self.flags & L.FLAG_PHONG_POSTPROCESS))
 
     # -- lifetime --------------------------------------------------------------------------
     def close(self):
@@ -383,12 +388,14 @@ class Application:
         elif m == 2:
             self.fill_rand_buffer()
             self.frame_num = self.compute_one_shader(self.frame_num, L.MODE_AO)
-        elif m == 3:
+        elif m in (3, 4):
             self.moving_light()
-            self.frame_num = self.compute_one_shader(self.frame_num, L.MODE_PHONG)
-        elif m == 4:
-            self.moving_light()
-            self.frame_num = self.compute_one_shader(self.frame_num, L.MODE_HYBRID)
+            program = L.MODE_PHONG if m == 3 else L.MODE_HYBRID
+            if self.rt.needs_postprocess(program):
+                # FLAG_PHONG_POSTPROCESS (the README's to-do): the Phong shaders go through the same second pass
+                self.frame_num = self.compute_two_shaders(self.frame_num, program)
+            else:
+                self.frame_num = self.compute_one_shader(self.frame_num, program)
         else:
             raise NotImplementedError("not yet implemented")  # the reference prints this (main.cpp:576)
         self.frames_rendered += 1

@@ -90,6 +90,9 @@ class GpuBandEngine:
     def render_frame(self, mode, uniforms, rand_buffer):
         self.rt.render_frame(mode, uniforms, rand_buffer)
 
+    def needs_postprocess(self, mode):
+        return self.rt.needs_postprocess(mode)
+
     def set_frame_target(self, ptr):
         self.rt.set_frame_target(ptr)
 
@@ -302,9 +305,14 @@ class BandedRenderer:
         self.direct, self.frame_k = direct, 0
         self._copy, self._copy_pending = False, False
 
+    def _post(self, mode: int) -> bool:
+        """the frame is finished by the post-processing pass (mode 1; modes 3/4 under FLAG_PHONG_POSTPROCESS)"""
+        f = getattr(self.e, "needs_postprocess", None)
+        return f(mode) if f is not None else mode == 1
+
     def _copy_gather(self, mode: int) -> bool:
         d = self.direct
-        return (mode == 1 and self.world > 1 and d is not None and d.mode1_gather == "copy"
+        return (self._post(mode) and self.world > 1 and d is not None and d.mode1_gather == "copy"
                 and not (d.owners == "rows" and d.split))
 
     def exchange_halo(self):
@@ -334,7 +342,7 @@ class BandedRenderer:
             else:
                 self.e.set_frame_target(self.direct.target(self.frame_k))
         self.e.render_frame(mode, uniforms, rand_buffer)
-        if mode == 1:
+        if self._post(mode):
             if self.world > 1:
                 self.e.halo_pack()
                 if self.direct is not None and self.direct.halo_direct:

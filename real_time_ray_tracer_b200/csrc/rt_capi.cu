@@ -128,7 +128,9 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     if (cfg->num_frames < 1 || cfg->num_frames > RT_MAX_FRAMES) return fail(nullptr, RT_EINVAL, "rt_create: num_frames must be 1..%d", RT_MAX_FRAMES);
     if (cfg->edge_mode != RT_EDGE_FLAT32 && cfg->edge_mode != RT_EDGE_CLEAN) return fail(nullptr, RT_EINVAL, "rt_create: bad edge_mode");
     for (int r : cfg->reserved) if (r != 0) return fail(nullptr, RT_EINVAL, "rt_create: reserved fields must be 0");
-    if (cfg->flags & ~RT_FLAG_PHONG_GBUFFER) return fail(nullptr, RT_EINVAL, "rt_create: unknown flags 0x%x", cfg->flags);
+    if (cfg->flags & ~(RT_FLAG_PHONG_GBUFFER | RT_FLAG_PHONG_POSTPROCESS)) return fail(nullptr, RT_EINVAL, "rt_create: unknown flags 0x%x", cfg->flags);
+    if ((cfg->flags & RT_FLAG_PHONG_POSTPROCESS) && !(cfg->flags & RT_FLAG_PHONG_GBUFFER))
+        return fail(nullptr, RT_EINVAL, "rt_create: RT_FLAG_PHONG_POSTPROCESS needs RT_FLAG_PHONG_GBUFFER (the pass reads normals and depths)");
     int rows = cfg->band_rows ? cfg->band_rows : cfg->height - cfg->band_y0;
     if (cfg->band_y0 < 0 || rows <= 0 || cfg->band_y0 + rows > cfg->height) return fail(nullptr, RT_EINVAL, "rt_create: band outside the image");
     int bcount = cfg->band_count ? cfg->band_count : 1;
@@ -312,6 +314,8 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "rt_render_frame: ring slot %d outside 0..%d", slot, c->cfg.num_frames - 1);
     if (nobj < 0 || nobj > c->nshapes) return fail(c, RT_EINVAL, "rt_render_frame: mode.z = %d but %d shapes uploaded", nobj, c->nshapes);
     const bool ao = (mode == RT_MODE_AO_PP || mode == RT_MODE_AO);
+    // the frame is finished by rt_postprocess: mode 1, and modes 3/4 under RT_FLAG_PHONG_POSTPROCESS
+    const bool post = (mode == RT_MODE_AO_PP) || (!ao && (c->cfg.flags & RT_FLAG_PHONG_POSTPROCESS));
     if (ao && !rand_buffer) return fail(c, RT_EINVAL, "rt_render_frame: AO modes need a rand_buffer");
     CU(c, cudaSetDevice(c->cfg.device));
 
@@ -338,7 +342,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
 
     TraceOut o{};
     const size_t off = (size_t)slot * c->npix;
-    o.color = (mode == RT_MODE_AO_PP) ? c->raw : c->ring_color + off;
+    o.color = post ? c->raw : c->ring_color + off;
     o.normal = c->ring_normal + off;
     o.depth_xy = c->ring_depth_xy + off;
     o.depth_w = c->ring_depth_w + off;
@@ -357,14 +361,14 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     }
     // mode 1: the trace output is raw; the post-processing pass writes the frame
     GatherTargets g = band_gather_targets(c), none = {};
-    o.gather = (mode == RT_MODE_AO_PP) ? none : g;
-    c->gather_post = (mode == RT_MODE_AO_PP) ? g : none;
+    o.gather = post ? none : g;
+    c->gather_post = post ? g : none;
     if (c->timing) CU(c, cudaEventRecord(c->ev[0], c->stream));
     CU(c, launch_trace(p, o, c->stream));
     if (c->timing) { CU(c, cudaEventRecord(c->ev[1], c->stream)); c->ev_trace_valid = true; }
     c->last_mode = mode;
     c->last_slot = slot;
-    c->frame_pending_post = (mode == RT_MODE_AO_PP);
+    c->frame_pending_post = post;
     c->halo_packed = false;
     return RT_OK;
 }

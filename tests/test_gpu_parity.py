@@ -786,6 +786,66 @@ def test_phong_modes_gbuffer_extension(scene):
         rtb.RayTracer(W, H, AA, flags=0x40)
 
 
+@pytest.mark.parametrize("edge_mode", [rtb.EDGE_FLAT32, rtb.EDGE_CLEAN])
+def test_phong_modes_postprocess_extension(edge_mode):
+    """RT_FLAG_PHONG_POSTPROCESS (the README's "... so they can use the same postprocessing"): a mode 3 / 4 frame
+    leaves its colour in the raw plane and aop_postprocessing blends it, with the normals and depths the G-buffer
+    flag wrote -- as a whole frame and as three row bands with halo rows, mixed with mode 1 and mode 2 frames."""
+    import torch
+
+    from real_time_ray_tracer_b200 import bands
+
+    W, H, AA = 97, 61, 4
+    flags = rtb.FLAG_PHONG_GBUFFER | rtb.FLAG_PHONG_POSTPROCESS
+    modes = (3, 3, 4, 1, 4, 2, 3, 4, 4, 3)
+    sc = Scenario("scene1", keys=("d",), light_movement=True)
+    o = orc.Oracle(W, H, AA, edge_mode=edge_mode, phong_gbuffer=True)
+    o.set_scene(sc.shapes, sc.n)
+    cuts = [0, 7, 33, 61]
+    n = len(cuts) - 1
+    whole = rtb.RayTracer(W, H, AA, edge_mode=edge_mode, flags=flags)
+    rts = [rtb.RayTracer(W, H, AA, edge_mode=edge_mode, flags=flags, band_y0=cuts[i], band_rows=cuts[i + 1] - cuts[i],
+                         band_index=i, band_count=n) for i in range(n)]
+    engs = [bands.GpuBandEngine(rt) for rt in rts]
+    for rt in [whole] + rts:
+        rt.upload_scene(sc.shapes, sc.n)
+    assert whole.needs_postprocess(3) and whole.needs_postprocess(4) and whole.needs_postprocess(1) and not whole.needs_postprocess(2)
+    for k, mode in enumerate(modes):
+        slot, u, rb = sc.next(mode, AA)
+        post = mode != 2
+        o.render(mode, u, rb)
+        whole.render_frame(mode, u, rb)
+        if post:
+            raw = whole.download(rtb.BUF_RAW_COLOR)
+            assert same_bits(raw, o.get(orc.PIXELS, slot)), f"frame {k} mode {mode}: raw colour"
+            o.postprocess()
+            whole.postprocess()
+        check_frame(whole, o, slot, mode, f"frame {k} whole")
+        for e in engs:
+            e.render_frame(mode, u, rb)
+            if post:
+                e.halo_pack()
+        if post:
+            for rt in rts:
+                rt.synchronize()
+            for i, e in enumerate(engs):
+                engs[(i + 1) % n].recv_lo.copy_(e.send_hi)
+                if i > 0:
+                    engs[i - 1].recv_hi.copy_(e.send_lo)
+            torch.cuda.synchronize()
+            for e in engs:
+                e.postprocess()
+        got = np.concatenate([rt.download(rtb.BUF_COLOR, slot) for rt in rts], axis=0)
+        assert same_bits(got, o.get(orc.PIXELS, slot)), f"frame {k} mode {mode} bands: {diff_report(got, o.get(orc.PIXELS, slot))}"
+    with pytest.raises(rtb.RtError):
+        rts[0].postprocess()                    # nothing pending
+    for rt in [whole] + rts:
+        rt.close()
+    o.close()
+    with pytest.raises(rtb.RtError):
+        rtb.RayTracer(W, H, AA, flags=rtb.FLAG_PHONG_POSTPROCESS)      # needs the G-buffer flag
+
+
 def test_rgba8_read_back_is_the_quantised_colour_plane():
     """rt_download_rgba8_async: byte = (uint8)(min(max(c, 0), 1) * 255 + 0.5), alpha 255; scene6 has emissive
     colours far above 1 (clamped) and the odd pixel count exercises the kernel's 4-pixel tail."""
