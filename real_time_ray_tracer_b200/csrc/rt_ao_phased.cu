@@ -207,15 +207,14 @@ __global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel
             }
         }
 
-        const float fAA = (float)p.AA;
         float4 c = make_float4(s_sky[3], s_sky[4], s_sky[5], 0.0f);
         if (!(ar == s_sky[0] && ag == s_sky[1] && ab == s_sky[2]))
-            c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+            c = gamma_correct(div_aa(p, ar), div_aa(p, ag), div_aa(p, ab));
         o.color[pix] = c;
         gather_store(o.gather, yl, pix, c);   // rt_set_frame_targets: the assembled frame, maybe over NVLink
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
-        o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
-        o.depth_w[pix] = __fdiv_rn(dw, fAA);
+        o.depth_xy[pix] = make_float2(div_aa(p, dx), div_aa(p, dy));
+        o.depth_w[pix] = div_aa(p, dw);
         o.hit[pix] = hit0;
     }
 

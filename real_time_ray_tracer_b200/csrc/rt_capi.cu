@@ -327,6 +327,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
         volatile float iw = 1.0f / fw, ih = 1.0f / fh;
         p.fW = fw; p.fH = fh; p.invW = iw; p.invH = ih;
     }
+    p.invAA = ((p.AA & (p.AA - 1)) == 0) ? 1.0f / (float)p.AA : 0.0f;   // exact for a power of two
     p.slot = slot; p.nshapes = nobj; p.edge_mode = c->cfg.edge_mode; p.mode = mode;
     p.band_index = c->cfg.band_index; p.band_count = c->cfg.band_count;
     p.pad0 = c->cfg.flags;   // FrameParams::pad0 carries rt_config.flags

@@ -41,7 +41,9 @@ struct FrameParams {
     // in separate lists (each keeps its position in the scene as *_idx, which decides ties exactly like the
     // shader's in-order `res_t < t`), plus what the intersection tests compute from `pos` alone when pos is
     // the camera (formed on the host with the shader's operation order).
-    int nsph, npl, pad1, pad2;
+    int nsph, npl;
+    float invAA;   // 1 / AA when AA is a power of two (then x * invAA == x / AA bit for bit), else 0: divide
+    int pad2;
     float4 sph[RT_MAX_SHAPES];     // centre.xyz, radius * radius
     float4 sph_cam[RT_MAX_SHAPES]; // cam - centre, dot(cam - centre, cam - centre)
     float4 pl_n[RT_MAX_SHAPES];    // normal.xyz, dot(normal, p0 - cam)

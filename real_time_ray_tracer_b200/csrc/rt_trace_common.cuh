@@ -88,12 +88,24 @@ __device__ __forceinline__ void sphere_candidate(float b, float del, int idx, fl
 __device__ __forceinline__ void plane_candidate(float num, float denom, int idx, float tmin, Closest &c)
 {
     if (denom < 0.001f && denom > -0.001f) return;
+    // A ray that starts ON the plane -- every AO bounce off the floor -- has num == +-0: t = +-0 never passes
+    // `> tmin` for tmin >= 0 (all callers), and 0 / denom takes the IEEE divide's slow path (ncu: called by 27 %
+    // of the general closest hits, 30 instructions each).
+    if (num == 0.0f && tmin >= 0.0f) return;
     const float res_t = __fdiv_rn(num, denom);
     const unsigned bits = __float_as_uint(res_t);
     if (res_t > tmin && (bits < c.tb || (bits == c.tb && idx < c.ind))) {
         c.tb = bits;
         c.ind = idx;
     }
+}
+
+// x / AA (ao_compute.glsl:330-331).  For a power-of-two AA, x * (1/AA) is the same real number, hence the same
+// correctly rounded result, and it has no range check: the zero depths of a sky pixel send whole warps down the
+// divide's slow path otherwise.
+__device__ __forceinline__ float div_aa(const FrameParams &p, float x)
+{
+    return (p.invAA != 0.0f) ? x * p.invAA : __fdiv_rn(x, (float)p.AA);
 }
 
 __device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, float3 dir, float tmin, float &t_out)
