@@ -37,11 +37,11 @@ constexpr int QH_THREADS = 128, QH_TILE_W = 16, QH_TILE_H = 8;
 constexpr int Q_SAMPLES = 4;                    // AA <= 4: one chunk
 constexpr int Q_FIELDS = 8;
 
-__device__ __forceinline__ float4 ao_pixel_colour(const float *sky, float ar, float ag, float ab, float fAA)
+__device__ __forceinline__ float4 ao_pixel_colour(const FrameParams &p, const float *sky, float ar, float ag, float ab)
 {
     // all-background pixels reuse the cached gamma (see rt_ao_phased.cu)
     if (ar == sky[0] && ag == sky[1] && ab == sky[2]) return make_float4(sky[3], sky[4], sky[5], 0.0f);
-    return gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+    return gamma_correct(div_aa(p, ar), div_aa(p, ag), div_aa(p, ab));
 }
 
 __global__ void __launch_bounds__(QH_THREADS, 8) rt_ao_head_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
@@ -137,9 +137,8 @@ __global__ void __launch_bounds__(QH_THREADS, 8) rt_ao_head_kernel(const __grid_
             }
         }
         // what the first segment of sample 0 decides is final now, queued or not
-        const float fAA = (float)p.AA;
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
-        o.depth_w[pix] = __fdiv_rn(dw, fAA);
+        o.depth_w[pix] = div_aa(p, dw);
         o.hit[pix] = hit0;
         if (pending == 0) {
             float ar = 0.0f, ag = 0.0f, ab = 0.0f, dy = 0.0f;
@@ -148,10 +147,10 @@ __global__ void __launch_bounds__(QH_THREADS, 8) rt_ao_head_kernel(const __grid_
                 const float ft = s_state[k][3][tid];
                 if (ft >= 0.0f) dy = ft;
             }
-            const float4 c = ao_pixel_colour(s_sky, ar, ag, ab, fAA);
+            const float4 c = ao_pixel_colour(p, s_sky, ar, ag, ab);
             o.color[pix] = c;
             gather_store(o.gather, yl, pix, c);
-            o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
+            o.depth_xy[pix] = make_float2(div_aa(p, dx), div_aa(p, dy));
         }
     }
 
@@ -211,7 +210,6 @@ __global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_flat_kernel(const __
     unsigned *ctr = o.tq.counters + o.tq.parity * 4;
     const unsigned count = ctr[0];
     const int nch = p.AA, RD = p.RD;
-    const float fAA = (float)p.AA;
     unsigned n_nonterm = 0, n_term = 0;
 
     for (unsigned base = blockIdx.x * QT_THREADS; base < count; base += gridDim.x * QT_THREADS) {
@@ -267,10 +265,10 @@ __global__ void __launch_bounds__(QT_THREADS, 8) rt_ao_tail_flat_kernel(const __
                 }
             }
             const unsigned pix = __float_as_uint(meta.x);
-            const float4 c = ao_pixel_colour(s_sky, ar, ag, ab, fAA);
+            const float4 c = ao_pixel_colour(p, s_sky, ar, ag, ab);
             o.color[pix] = c;
             gather_store(o.gather, o.gather.count > 1 ? (int)(pix / (unsigned)p.W) : 0, pix, c);
-            o.depth_xy[pix] = make_float2(__fdiv_rn(meta.z, fAA), __fdiv_rn(dy, fAA));
+            o.depth_xy[pix] = make_float2(div_aa(p, meta.z), div_aa(p, dy));
         }
     }
 

@@ -162,13 +162,12 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid
             }
         }
 
-        const float fAA = (float)p.AA;
-        float4 c = gamma_correct(__fdiv_rn(ar, fAA), __fdiv_rn(ag, fAA), __fdiv_rn(ab, fAA));
+        float4 c = gamma_correct(div_aa(p, ar), div_aa(p, ag), div_aa(p, ab));
         o.color[pix] = c;
         gather_store(o.gather, yl, pix, c);
         if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
-        o.depth_xy[pix] = make_float2(__fdiv_rn(dx, fAA), __fdiv_rn(dy, fAA));
-        o.depth_w[pix] = __fdiv_rn(dw, fAA);
+        o.depth_xy[pix] = make_float2(div_aa(p, dx), div_aa(p, dy));
+        o.depth_w[pix] = div_aa(p, dw);
         o.hit[pix] = hit0;
     }
 
