@@ -178,8 +178,9 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
         if (!strcmp(k, "tile")) c->ao_kernel = AO_KERNEL_TILE;
         else if (!strcmp(k, "stream")) c->ao_kernel = AO_KERNEL_STREAM;
         else if (!strcmp(k, "queued")) c->ao_kernel = AO_KERNEL_QUEUED;
+        else if (!strcmp(k, "pulled")) c->ao_kernel = AO_KERNEL_PULLED;
         else if (strcmp(k, "phased")) {
-            fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected phased, queued, tile or stream)", k);
+            fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected phased, pulled, queued, tile or stream)", k);
             free_all(c);
             return RT_EINVAL;
         }

@@ -338,6 +338,7 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
     if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO) {
         const bool queued = (o.ao_kernel == AO_KERNEL_QUEUED);
         if (queued && o.tq.entries && p.AA <= 4) return launch_ao_queued(p, o, s);
+        if (o.ao_kernel == AO_KERNEL_PULLED) return launch_ao_pulled(p, o, s);
         if (o.ao_kernel == AO_KERNEL_PHASED || queued) return launch_ao_phased(p, o, s);
         if (o.ao_kernel == AO_KERNEL_STREAM) return launch_ao_stream(p, o, s);  // persistent ray queue (rt_ao_stream.cu)
         rt_ao_trace_kernel<<<grid, block, 0, s>>>(p, o); // first-generation tile kernel, kept for A/B profiling

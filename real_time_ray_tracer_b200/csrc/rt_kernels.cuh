@@ -71,7 +71,7 @@ enum StatIdx {
     ST_COUNT
 };
 
-enum { AO_KERNEL_PHASED = 0, AO_KERNEL_TILE = 1, AO_KERNEL_STREAM = 2, AO_KERNEL_QUEUED = 3 };
+enum { AO_KERNEL_PHASED = 0, AO_KERNEL_TILE = 1, AO_KERNEL_STREAM = 2, AO_KERNEL_QUEUED = 3, AO_KERNEL_PULLED = 4 };
 
 // device queue of the two-kernel AO schedule (rt_ao_queued.cu): one entry per pixel that still has path
 // segments to trace after the head: [0] = (pixel index, pending mask, depth.x, -), then two float4 per sample
@@ -160,6 +160,7 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
 cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_phased(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_queued(const FrameParams &p, const TraceOut &o, cudaStream_t s);
+cudaError_t launch_ao_pulled(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_sky_gamma(float4 bg, int AA, float *sky, cudaStream_t s);
 cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s);
 cudaError_t launch_postprocess(const PostParams &q, cudaStream_t s);
