@@ -334,8 +334,8 @@ def run_b200(args) -> None:
         fl = float(np.mean([f for _, f, _ in tr_ms]))
         kr = float(np.mean([r for _, _, r in tr_ms]))
         ach = fl / (t_ms * 1e-3) / 1e12
-        ao_name = {"tile": "rt_ao_trace_kernel", "stream": "rt_ao_stream_kernel"}.get(
-            os.environ.get("RT_AO_KERNEL", "phased"), "rt_ao_phased_kernel")
+        ao_name = {"tile": "rt_ao_trace_kernel", "stream": "rt_ao_stream_kernel", "phased": "rt_ao_phased_kernel",
+                   "queued": "rt_ao_head_kernel"}.get(os.environ.get("RT_AO_KERNEL", "pulled"), "rt_ao_pulled_kernel")
         kname = {1: ao_name, 2: ao_name, 3: "rt_phong_kernel", 4: "rt_hybrid_kernel"}[mode]
         roof = {"bound": "fp32", "kernel": kname,
                 "achieved": round(ach, 4), "peak": round(peak_tf, 3), "unit": "TFLOP/s",

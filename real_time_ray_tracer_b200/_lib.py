@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librt_b200.so")
+# RT_B200_LIB: a differently tuned build of the same sources for A/B runs (tools/gpu_variants.sh); never a fallback
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(HERE, "librt_b200.so")
 
 RT_OK, RT_EINVAL, RT_ENODEVICE, RT_ENOMEM, RT_ECUDA, RT_ESTATE = 0, -1, -2, -3, -4, -5
 MODE_AO_PP, MODE_AO, MODE_PHONG, MODE_HYBRID = 1, 2, 3, 4

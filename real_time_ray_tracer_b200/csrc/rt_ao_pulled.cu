@@ -18,12 +18,16 @@
 
 namespace rt {
 
-constexpr int PU_THREADS = 128;                 // 2x2 warps of 8x4 pixels
-constexpr int PU_TILE_W = 16, PU_TILE_H = 8;
+#ifndef PU_THREADS_N
+#define PU_THREADS_N 128
+#endif
+constexpr int PU_THREADS = PU_THREADS_N;        // 2 x (PU_THREADS / 64) warps of 8x4 pixels
+constexpr int PU_TILE_W = 16, PU_TILE_H = 4 * (PU_THREADS / 64);
+constexpr int PU_MIN_BLOCKS = 1024 / PU_THREADS;
 constexpr int PU_CHUNK = 4;                     // samples whose state is parked in shared memory at a time
 constexpr int PU_FIELDS = 8;                    // survivor: dir.xyz, t, ids, ru.xyz   finished: colour.rgb, terminal depth
 
-__global__ void __launch_bounds__(PU_THREADS, 8) rt_ao_pulled_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
+__global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
     __shared__ float4 s_rand[2 * RT_MAX_AA];

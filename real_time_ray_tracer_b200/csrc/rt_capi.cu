@@ -38,7 +38,7 @@ struct rt_ctx {
     float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
     float4 sky_bg{};
     bool sky_valid = false;
-    int ao_kernel = AO_KERNEL_PHASED; // RT_AO_KERNEL=tile|stream selects the earlier kernels (A/B profiling)
+    int ao_kernel = AO_KERNEL_PULLED; // RT_AO_KERNEL=phased|queued|tile|stream selects the earlier kernels (A/B profiling)
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
     int nshapes = 0;
@@ -178,8 +178,8 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
         if (!strcmp(k, "tile")) c->ao_kernel = AO_KERNEL_TILE;
         else if (!strcmp(k, "stream")) c->ao_kernel = AO_KERNEL_STREAM;
         else if (!strcmp(k, "queued")) c->ao_kernel = AO_KERNEL_QUEUED;
-        else if (!strcmp(k, "pulled")) c->ao_kernel = AO_KERNEL_PULLED;
-        else if (strcmp(k, "phased")) {
+        else if (!strcmp(k, "phased")) c->ao_kernel = AO_KERNEL_PHASED;
+        else if (strcmp(k, "pulled")) {
             fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected phased, pulled, queued, tile or stream)", k);
             free_all(c);
             return RT_EINVAL;
