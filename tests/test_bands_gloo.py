@@ -178,3 +178,78 @@ def test_shares_to_row_end():
     assert bands.shares_to_row_end(3, [1] * 5)[-1] == 3
     with pytest.raises(ValueError):
         bands.shares_to_row_end(10, [0, 0])
+
+
+class _Recorder:
+    """stands in for GpuBandEngine / DirectGather: records the calls BandedRenderer makes, in order"""
+
+    def __init__(self, log, post_modes=(1,)):
+        self.log, self.post_modes = log, post_modes
+
+    def needs_postprocess(self, mode):
+        return mode in self.post_modes
+
+    def __getattr__(self, name):
+        def call(*a):
+            self.log.append((name,) + tuple(x for x in a if isinstance(x, (int, str, type(None)))))
+        return call
+
+
+class _FakeDirect:
+    def __init__(self, log, owners="rank0", halo_direct=True):
+        self.log, self.owners, self.split, self.mode1_gather, self._hd = log, owners, owners == "rows", "store", halo_direct
+
+    halo_direct = property(lambda self: self._hd)
+
+    def target(self, k):
+        return 1000 + k % 2
+
+    def targets(self, k):
+        return [2000 + k % 2, 3000 + k % 2], [5, 10]
+
+    def fence(self):
+        self.log.append(("fence",))
+
+
+def test_banded_renderer_call_sequences():
+    """the per-frame call sequence of the N > 1 path (no GPU): kernel-store gather, split row owners, and the
+    copy gather of post-processed frames that the NEXT fence closes"""
+    log = []
+    eng = _Recorder(log, post_modes=(1, 3))
+    d = _FakeDirect(log)
+    br = bands.BandedRenderer(eng, 8, 10, [(0, 5), (5, 5)], rank=1, world=2, direct=d)
+    # mode 2, kernel stores: target, render, fence
+    br.render(2, None, None); br.gather_start(0)
+    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "fence"] and log[0] == ("set_frame_target", 1000)
+    # mode 1, kernel stores: render, pack, halo fence, post-process, frame fence
+    del log[:]
+    br.render(1, None, None); br.gather_start(1)
+    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "halo_pack", "fence", "postprocess", "fence"]
+    assert log[0] == ("set_frame_target", 1001) and br.frame_k == 2
+    # copy gather: no target, one fence per frame, the band copy after the pass, flush closes the last frame
+    del log[:]
+    d.mode1_gather = "copy"
+    br.render(1, None, None); br.gather_start(2)
+    br.render(3, None, None); br.gather_start(3)     # mode 3 under FLAG_PHONG_POSTPROCESS behaves like mode 1
+    br.gather_flush(); br.gather_flush()
+    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "halo_pack", "fence", "postprocess", "band_to_frame",
+                                   "set_frame_target", "render_frame", "halo_pack", "fence", "postprocess", "band_to_frame",
+                                   "fence"]
+    assert log[0] == ("set_frame_target", None) and log[5] == ("band_to_frame", 2, 1000) and log[11] == ("band_to_frame", 3, 1001)
+    # a single-pass frame after a copied one: its fence closes both, nothing left to flush
+    del log[:]
+    br.render(1, None, None); br.gather_start(4)
+    br.render(2, None, None); br.gather_start(5)
+    br.gather_flush()
+    assert [c[0] for c in log][-3:] == ["set_frame_target", "render_frame", "fence"] and [c[0] for c in log].count("fence") == 2
+    # split row owners: every pixel goes to its owner's image, post-processed frames included (no copy gather)
+    del log[:]
+    d2 = _FakeDirect(log, owners="rows")
+    d2.mode1_gather = "copy"
+    br2 = bands.BandedRenderer(eng, 8, 10, [(0, 5), (5, 5)], rank=0, world=2, direct=d2)
+    br2.render(1, None, None); br2.gather_start(0)
+    assert [c[0] for c in log] == ["set_frame_targets", "render_frame", "halo_pack", "fence", "postprocess", "fence"]
+    d2.split = False      # the same images, gathered to rank 0 after all
+    del log[:]
+    br2.render(2, None, None); br2.gather_start(1)
+    assert log[0] == ("set_frame_target", 1001)
