@@ -31,6 +31,14 @@ namespace rt {
 constexpr int PU_THREADS = PU_THREADS_N;        // 2 x (PU_THREADS / 64) warps of 8x4 pixels
 constexpr int PU_TILE_W = 16, PU_TILE_H = 4 * (PU_THREADS / 64);
 constexpr int PU_MIN_BLOCKS = 1024 / PU_THREADS;
+// PU_WARP_WAIT=1: after its tail a warp waits only until the survivors of ITS OWN pixels are finished (a counter
+// per warp that the finishing lanes decrement) instead of the block barrier, so it can go on -- and after the last
+// chunk exit and free its registers -- while other warps still trace long paths.  Bit-exact as well, but slower
+// (config 2: 0.2524 against 0.2464 ms in the same run; config 5: 15.40 against 15.14 ms): the fence + atomic per
+// finished survivor and the polling cost more than the early exits return.  Off.
+#ifndef PU_WARP_WAIT
+#define PU_WARP_WAIT 0
+#endif
 constexpr int PU_CHUNK = 4;                     // samples whose state is parked in shared memory at a time
 constexpr int PU_FIELDS = 8;                    // survivor: dir.xyz, t, ids, ru.xyz   finished: colour.rgb, terminal depth
 
@@ -40,15 +48,17 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
     __shared__ float4 s_rand[2 * RT_MAX_AA];
     __shared__ float s_state[PU_CHUNK][PU_FIELDS][PU_THREADS];   // [sample][field][owner thread]
     __shared__ float s_sky[6];                                    // sum.rgb, gamma.rgb of an all-background pixel
-    __shared__ unsigned short s_task[PU_CHUNK * PU_THREADS];      // owner thread | sample << 8
-    __shared__ unsigned s_count[2][2];                            // per chunk parity: {appended, handed out}
+    __shared__ unsigned short s_task[2][PU_CHUNK * PU_THREADS];   // per chunk parity: owner thread | sample << 8
+    __shared__ unsigned s_count[3][2];                            // per chunk mod 3: {appended, handed out}
+    __shared__ unsigned s_out[PU_THREADS / 32];                   // per warp: its pixels' survivors not finished yet
     const int tid = threadIdx.x;
 #pragma unroll 1
     for (int i = tid; i < p.nshapes; i += PU_THREADS) s_shapes[i] = p.shapes[i];
 #pragma unroll 1
     for (int i = tid; i < 2 * p.AA; i += PU_THREADS) s_rand[i] = p.rand[i];
     if (tid < 6) s_sky[tid] = o.sky[tid];
-    if (tid < 4) s_count[tid >> 1][tid & 1] = 0u;
+    if (tid < 6) s_count[tid >> 1][tid & 1] = 0u;
+    if (tid < PU_THREADS / 32) s_out[tid] = 0u;
     __syncthreads();
 
     const int lane = tid & 31, warp = tid >> 5;
@@ -69,7 +79,10 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
 
     for (int c0 = 0; c0 < p.AA; c0 += PU_CHUNK) {
         const int nch = min(PU_CHUNK, p.AA - c0);
-        const int par = (c0 / PU_CHUNK) & 1;
+        // Counter sets rotate by three: set (c+2) % 3 is cleared after chunk c's barrier, when every warp has left
+        // chunk c-1 (its last user) and none can reach chunk c+2's appends before the NEXT barrier.  The task
+        // lists alternate: chunk c+2 appends only after chunk c+1's barrier, when chunk c's pulls are over.
+        const int par = (c0 / PU_CHUNK) % 3, tp = (c0 / PU_CHUNK) & 1;
         unsigned pending = 0;       // samples of this chunk that this thread parked as survivors
         bool have = false;          // tail: this lane is tracing a pulled survivor
         int slot = 0;               // tail: owner thread | sample << 8 of that survivor
@@ -88,13 +101,15 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                 // every head is done: put this thread's survivors on the block's list
                 if (pending) {
                     unsigned pos = atomicAdd(&s_count[par][0], (unsigned)__popc(pending));
+#if PU_WARP_WAIT
+                    atomicAdd(&s_out[warp], (unsigned)__popc(pending));
+#endif
 #pragma unroll
                     for (int k = 0; k < PU_CHUNK; k++)
-                        if ((pending >> k) & 1u) s_task[pos++] = (unsigned short)(tid | (k << 8));
+                        if ((pending >> k) & 1u) s_task[tp][pos++] = (unsigned short)(tid | (k << 8));
                 }
                 __syncthreads();
-                // the other parity's counters are idle now (their chunk ended before this one's heads began)
-                if (tid < 2) s_count[par ^ 1][tid] = 0u;
+                if (tid < 2) s_count[(par + 2) % 3][tid] = 0u;
             }
             if (head) {
                 if (active) {
@@ -133,7 +148,7 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                     if (*(volatile unsigned *)&s_count[par][1] >= total) break;   // list exhausted: it cannot grow
                     const unsigned my = atomicAdd(&s_count[par][1], 1u);
                     if (my >= total) break;
-                    slot = s_task[my];
+                    slot = s_task[tp][my];
                     const int ow = slot & 0xff, k = slot >> 8;
                     dir = mk3(s_state[k][0][ow], s_state[k][1][ow], s_state[k][2][ow]);
                     t = s_state[k][3][ow];
@@ -193,9 +208,19 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                 s_state[k][0][ow] = cr; s_state[k][1][ow] = cg; s_state[k][2][ow] = cb;
                 s_state[k][3][ow] = stop ? term : -1.0f;
                 have = false;
+#if PU_WARP_WAIT
+                __threadfence_block();
+                atomicSub(&s_out[ow >> 5], 1u);
+#endif
             }
         }
+#if PU_WARP_WAIT
+        __syncwarp();
+        while (*(volatile unsigned *)&s_out[warp] != 0u) __nanosleep(32);   // the pullers never wait: no cycle
+        __threadfence_block();
+#else
         __syncthreads();    // every survivor of the chunk has been traced: all records are in place
+#endif
         if (active) {
 #pragma unroll 1
             for (int k = 0; k < nch; k++) {

@@ -129,7 +129,7 @@ def test_mode_switching_shares_the_ring():
         o.close()
 
 
-@pytest.mark.parametrize("aa", [1, 2, 16])
+@pytest.mark.parametrize("aa", [1, 2, 3, 6, 13, 16])
 def test_aa_counts(aa):
     W, H = 64, 48
     sc = Scenario("scene1")
