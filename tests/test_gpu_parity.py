@@ -687,6 +687,34 @@ def test_linked_bands_fence_and_direct_halo_on_separate_gpus():
     _run_ranks(world, 88, 50, 4, cuts, (1, 1, 2, 1, 1, 4, 3, 1, 1), "flags", False, mode1_gather="copy")
 
 
+def test_pulled_kernel_does_not_depend_on_who_traced_what():
+    """The default AO kernel hands a block's surviving paths to whichever lane is free, so the assignment differs
+    from run to run; the frame must not.  The same frame rendered repeatedly (AA 4: one chunk; AA 9: three chunks,
+    the last one partial, rotating list and counter sets) gives identical bits in every plane, and equals the oracle."""
+    for (W, H, AA) in ((642, 363, 4), (322, 181, 9)):
+        sc = Scenario("scene1", keys=("d",))
+        slot, u, rb = sc.next(2, AA)
+        o = orc.Oracle(W, H, AA)
+        o.set_scene(sc.shapes, sc.n)
+        o.render(2, u, rb)
+        with rtb.RayTracer(W, H, AA) as rt:
+            rt.upload_scene(sc.shapes, sc.n)
+            first = None
+            for rep in range(6):
+                rt.reset_stats()
+                rt.render_frame(2, u, rb)
+                planes = [rt.download(b, slot) for b in (rtb.BUF_COLOR, rtb.BUF_NORMAL, rtb.BUF_DEPTH)]
+                st = {k: v for k, v in rt.stats().items() if not k.startswith("ms_")}
+                if first is None:
+                    first = (planes, st)
+                    check_frame(rt, o, slot, 2, f"{W}x{H} aa {AA}")
+                else:
+                    for a, b in zip(planes, first[0]):
+                        assert same_bits(a, b), f"{W}x{H} aa {AA}: run {rep} differs from run 0"
+                    assert st == first[1]
+        o.close()
+
+
 @pytest.mark.parametrize("kernel", ["phased", "pulled", "queued", "tile", "stream"])
 def test_all_ao_kernels(kernel, monkeypatch):
     """the phased (default), tile and persistent streaming kernels are three schedules of the same arithmetic;
