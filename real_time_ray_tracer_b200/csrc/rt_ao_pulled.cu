@@ -54,7 +54,9 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
     __shared__ float s_sky[6];                                    // sum.rgb, gamma.rgb of an all-background pixel
     __shared__ unsigned short s_task[2][PU_CHUNK * PU_THREADS];   // per chunk parity: owner thread | sample << 8
     __shared__ unsigned s_count[3][2];                            // per chunk mod 3: {appended, handed out}
+#if PU_WARP_WAIT
     __shared__ unsigned s_out[PU_THREADS / 32];                   // per warp: its pixels' survivors not finished yet
+#endif
     const int tid = threadIdx.x;
 #pragma unroll 1
     for (int i = tid; i < p.nshapes; i += PU_THREADS) s_shapes[i] = p.shapes[i];
@@ -62,7 +64,9 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
     for (int i = tid; i < 2 * p.AA; i += PU_THREADS) s_rand[i] = p.rand[i];
     if (tid < 6) s_sky[tid] = o.sky[tid];
     if (tid < 6) s_count[tid >> 1][tid & 1] = 0u;
+#if PU_WARP_WAIT
     if (tid < PU_THREADS / 32) s_out[tid] = 0u;
+#endif
     __syncthreads();
 
     const int lane = tid & 31, warp = tid >> 5;
@@ -73,6 +77,12 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
     const size_t pix = (size_t)yl * p.W + x;
     const float fx = (float)x, fy = (float)y;
     const int RD = p.RD;
+    // a tile that provably sees only background (tile_misses_everything): its heads skip the camera ray and the
+    // closest hit -- the sample ends there with the background colour whatever the ray is -- but the warp still
+    // takes part in the barriers and pulls other warps' survivors
+    const bool sky_tile = (p.cull_a > 0.0f) &&
+        tile_misses_everything(p, ((float)(blockIdx.x * PU_TILE_W + ((warp & 1) << 3)) + 3.5f) * p.invW,
+                               ((float)(p.y0 + blockIdx.y * PU_TILE_H + ((warp >> 1) << 2)) + 1.5f) * p.invH);
     unsigned n_nonterm = 0, n_term = 0;
     float ar = 0.0f, ag = 0.0f, ab = 0.0f;  // result_color summed over samples, in sample order
     float3 nrm = mk3(0.0f, 0.0f, 0.0f);
@@ -120,8 +130,11 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                     // ------------------------------------------------ camera ray of sample aa, converged
                     const int aa = c0 + it;
                     const float4 rf = s_rand[2 * aa], rs = s_rand[2 * aa + 1];
-                    dir = ao_camera_ray(p, aa, rf, rs, fx, fy);
-                    ind = closest_hit_primary(p, dir, 0.0001f, t);
+                    ind = -1;
+                    if (!sky_tile) {
+                        dir = ao_camera_ray(p, aa, rf, rs, fx, fy);
+                        ind = closest_hit_primary(p, dir, 0.0001f, t);
+                    }
                     first = (aa == 0);
                     if (first) hit0 = ind;
                     cr = p.bg.x; cg = p.bg.y; cb = p.bg.z;      // 1 * a0 == a0

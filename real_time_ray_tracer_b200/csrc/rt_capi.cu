@@ -38,6 +38,7 @@ struct rt_ctx {
     float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
     float4 sky_bg{};
     bool sky_valid = false;
+    bool ao_cull = true;      // RT_AO_CULL=0 switches tile_misses_everything off (A/B)
     int ao_kernel = AO_KERNEL_PULLED; // RT_AO_KERNEL=phased|queued|tile|stream selects the earlier kernels (A/B profiling)
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
@@ -174,6 +175,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     alloc0((void **)&c->work, 2 * sizeof(unsigned));
     alloc0((void **)&c->sky, 6 * sizeof(float));
+    if (const char *k = getenv("RT_AO_CULL")) c->ao_cull = strcmp(k, "0") != 0;
     if (const char *k = getenv("RT_AO_KERNEL")) {
         if (!strcmp(k, "tile")) c->ao_kernel = AO_KERNEL_TILE;
         else if (!strcmp(k, "stream")) c->ao_kernel = AO_KERNEL_STREAM;
@@ -263,10 +265,16 @@ static inline float3 f3(const rt_vec4 &v) { return make_float3(v.x, v.y, v.z); }
 // sphere_eval_ray / plane_eval_ray (ao_compute.glsl:75-117) compute from `pos` alone, for pos = the camera:
 // one binary32 operation per shader operation, dot = multiply then fused multiply-adds (rt_math.cuh).
 // volatile keeps the host compiler from contracting or reassociating anything.
-static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n)
+static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n, bool cull)
 {
     p.nsph = p.npl = 0;
     const float3 cam = p.cam;
+    // tile_misses_everything: the farthest a camera ray of an 8x4 tile gets from the tile's centre ray before
+    // normalisation: 3.5 (1.5) pixels + the jitter's 0.084, rounded up to 3.7 (1.7), +10 %
+    const float lh = sqrtf(p.horiz.x * p.horiz.x + p.horiz.y * p.horiz.y + p.horiz.z * p.horiz.z);
+    const float lv = sqrtf(p.vert.x * p.vert.x + p.vert.y * p.vert.y + p.vert.z * p.vert.z);
+    p.cull_a = cull ? 1.1f * ((3.7f / (float)p.W) * lh + (1.7f / (float)p.H) * lv) : 0.0f;
+    if (!(p.cull_a > 0.0f)) p.cull_a = 0.0f;    // NaN / degenerate camera: no culling
     for (int i = 0; i < n; i++) {
         const DevShape &s = shapes[i];
         if (s.id == SPHERE_ID) {
@@ -275,6 +283,9 @@ static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n
             volatile float dd = fmaf(pz, pz, fmaf(py, py, xx));
             p.sph[p.nsph] = make_float4(s.s0.x, s.s0.y, s.s0.z, s.r2);
             p.sph_cam[p.nsph] = make_float4(px, py, pz, dd);
+            const float gap = dd - s.r2;
+            p.sph_len[p.nsph] = sqrtf(dd) * 1.001f;
+            p.sph_gap[p.nsph] = (gap > 0.0f) ? gap * 0.999f : -1.0f;
             p.sph_idx[p.nsph++] = i;
         } else if (s.id == PLANE_ID) {
             volatile float qx = s.s3.x - cam.x, qy = s.s3.y - cam.y, qz = s.s3.z - cam.z;
@@ -282,6 +293,7 @@ static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n
             volatile float num = fmaf(s.s0.z, qz, fmaf(s.s0.y, qy, xx));
             p.pl_n[p.npl] = make_float4(s.s0.x, s.s0.y, s.s0.z, num);
             p.pl_p0[p.npl] = make_float4(s.s3.x, s.s3.y, s.s3.z, 0.0f);
+            p.pl_len[p.npl] = sqrtf(s.s0.x * s.s0.x + s.s0.y * s.s0.y + s.s0.z * s.s0.z) * 1.001f;
             p.pl_idx[p.npl++] = i;
         } // any other id (rectangle = 3) is never intersected: ao_compute.glsl:130-135
     }
@@ -336,7 +348,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     p.cam = f3(u->camera_location); p.light = f3(u->light_pos);
     p.bg = make_float4(u->background.x, u->background.y, u->background.z, u->background.w);
     memcpy(p.shapes, c->shapes, sizeof p.shapes);
-    build_traversal_tables(p, c->shapes, nobj);
+    build_traversal_tables(p, c->shapes, nobj, c->ao_cull);
     if (rand_buffer) {
         memcpy(p.rand, rand_buffer, (size_t)c->cfg.aa * 2 * sizeof(float4));
         c->rand_last = p.rand[2 * c->cfg.aa - 1];
