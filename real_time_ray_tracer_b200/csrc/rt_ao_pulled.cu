@@ -77,12 +77,13 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
     const size_t pix = (size_t)yl * p.W + x;
     const float fx = (float)x, fy = (float)y;
     const int RD = p.RD;
-    // a tile that provably sees only background (tile_misses_everything): its heads skip the camera ray and the
-    // closest hit -- the sample ends there with the background colour whatever the ray is -- but the warp still
-    // takes part in the barriers and pulls other warps' survivors
-    const bool sky_tile = (p.cull_a > 0.0f) &&
-        tile_misses_everything(p, ((float)(blockIdx.x * PU_TILE_W + ((warp & 1) << 3)) + 3.5f) * p.invW,
-                               ((float)(p.y0 + blockIdx.y * PU_TILE_H + ((warp >> 1) << 2)) + 1.5f) * p.invH);
+    // The objects a camera ray of this warp's tile can hit at all (tile_candidates).  None: the tile provably sees
+    // only background, and its heads skip the camera ray and the closest hit -- the sample ends there with the
+    // background colour whatever the ray is -- but the warp still takes part in the barriers and pulls other
+    // warps' survivors.  Otherwise the camera rays test the candidates only.
+    const unsigned cand = tile_candidates(p, ((float)(blockIdx.x * PU_TILE_W + ((warp & 1) << 3)) + 3.5f) * p.invW,
+                                          ((float)(p.y0 + blockIdx.y * PU_TILE_H + ((warp >> 1) << 2)) + 1.5f) * p.invH);
+    const bool sky_tile = cand == 0u;
     unsigned n_nonterm = 0, n_term = 0;
     float ar = 0.0f, ag = 0.0f, ab = 0.0f;  // result_color summed over samples, in sample order
     float3 nrm = mk3(0.0f, 0.0f, 0.0f);
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                     ind = -1;
                     if (!sky_tile) {
                         dir = ao_camera_ray(p, aa, rf, rs, fx, fy);
-                        ind = closest_hit_primary(p, dir, 0.0001f, t);
+                        ind = closest_hit_primary_masked(p, dir, 0.0001f, t, cand);
                     }
                     first = (aa == 0);
                     if (first) hit0 = ind;

@@ -38,7 +38,7 @@ struct rt_ctx {
     float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
     float4 sky_bg{};
     bool sky_valid = false;
-    bool ao_cull = true;      // RT_AO_CULL=0 switches tile_misses_everything off (A/B)
+    bool ao_cull = true;      // RT_AO_CULL=0 switches the tile test (tile_candidates) off (A/B)
     int ao_kernel = AO_KERNEL_PULLED; // RT_AO_KERNEL=phased|queued|tile|stream selects the earlier kernels (A/B profiling)
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
@@ -269,7 +269,7 @@ static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n
 {
     p.nsph = p.npl = 0;
     const float3 cam = p.cam;
-    // tile_misses_everything: the farthest a camera ray of an 8x4 tile gets from the tile's centre ray before
+    // tile_candidates: the farthest a camera ray of an 8x4 tile gets from the tile's centre ray before
     // normalisation: 3.5 (1.5) pixels + the jitter's 0.084, rounded up to 3.7 (1.7), +10 %
     const float lh = sqrtf(p.horiz.x * p.horiz.x + p.horiz.y * p.horiz.y + p.horiz.z * p.horiz.z);
     const float lv = sqrtf(p.vert.x * p.vert.x + p.vert.y * p.vert.y + p.vert.z * p.vert.z);

@@ -50,7 +50,7 @@ struct FrameParams {
     float4 pl_p0[RT_MAX_SHAPES];   // p0.xyz, 0
     int sph_idx[RT_MAX_SHAPES];
     int pl_idx[RT_MAX_SHAPES];
-    // Bounds for tile_misses_everything (rt_trace_common.cuh), all rounded to the safe side on the host:
+    // Bounds for tile_candidates (rt_trace_common.cuh), all rounded to the safe side on the host:
     // |cam - centre|, (|cam - centre|^2 - r^2) or -1 when the camera is not outside the sphere, |n| of a plane,
     // and cull_a >= |v - v0| for any camera ray v = llc + hp horiz + vp vert of an 8x4 tile with centre ray v0
     // (jitter included).  cull_a == 0 switches the test off (RT_AO_CULL=0).

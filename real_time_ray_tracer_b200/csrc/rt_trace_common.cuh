@@ -149,27 +149,32 @@ __device__ __forceinline__ int closest_hit_primary(const FrameParams &p, float3 
     return c.ind;
 }
 
-// Can NO camera ray of an 8x4 pixel tile (any sample, jitter included) hit anything?  A conservative test on
-// the tile's centre ray d0: every ray d of the tile is within an angle whose sine is below s of d0, hence
+// Which objects can a camera ray of an 8x4 pixel tile (any sample, jitter included) hit at all?  A conservative
+// test on the tile's centre ray d0: every ray d of the tile is within an angle whose sine is below s of d0, hence
 //   |d . oc| <= |d0 . oc| + |oc| s        so the sphere test's  b^2 - |oc|^2 + r^2 >= 0  needs at least
 //   (|d0 . oc| + |oc| s)^2 >= |oc|^2 - r^2;
 //   n . d  >= (1 - s) n . d0 - |n| s      so a plane whose numerator is negative (camera on the normal's side)
 //   cannot give t > 0 while that lower bound is positive (mirrored for a positive numerator).
 // The margins (host: +10 % on s, 0.1 % on the lengths; here 1e-3 |n|) are orders of magnitude above the
-// rounding of the exact tests, and every comparison is written so that a NaN keeps the tile.  A tile that
-// passes is what 40 % of config 2's warps are: sky.  Their samples all end on the camera ray with the
-// background colour, whatever the ray is, so the head skips the camera ray and the closest hit for them.
-__device__ __forceinline__ bool tile_misses_everything(const FrameParams &p, float hp0, float vp0)
+// rounding of the exact tests, and every comparison is written so that a NaN keeps the object.  An object that
+// is ruled out would never have produced a candidate, so leaving it out of the camera rays' closest hit changes
+// nothing.  A tile with NO candidate is what 40 % of config 2's warps are: sky.  Its samples all end on the camera
+// ray with the background colour, whatever the ray is, so the head skips the camera ray itself as well.
+// Returns sphere bits | plane bits << 16 (positions in FrameParams::sph / pl_n).
+__device__ __forceinline__ unsigned tile_candidates(const FrameParams &p, float hp0, float vp0)
 {
+    unsigned sph_mask, pl_mask;
     const float3 v0 = add3(add3(p.llc, scale3(hp0, p.horiz)), scale3(vp0, p.vert));
     const float inv = rsqrtf(dot3(v0, v0));
     const float3 d0 = scale3(inv, v0);
     const float s = p.cull_a * inv;
-    bool miss = s < 0.05f;
+    sph_mask = (1u << p.nsph) - 1u;
+    pl_mask = (1u << p.npl) - 1u;
+    if (!(p.cull_a > 0.0f && s < 0.05f)) return sph_mask | (pl_mask << 16);   // off, degenerate camera, or tiles too wide for the margins
 #pragma unroll 1
     for (int i = 0; i < p.nsph; i++) {
         const float m = fabsf(dot3(d0, xyz(p.sph_cam[i]))) + p.sph_len[i] * s;
-        miss = miss && (m * m < p.sph_gap[i]);
+        if (m * m < p.sph_gap[i]) sph_mask &= ~(1u << i);
     }
 #pragma unroll 1
     for (int j = 0; j < p.npl; j++) {
@@ -177,9 +182,31 @@ __device__ __forceinline__ bool tile_misses_everything(const FrameParams &p, flo
         const float dn = dot3(xyz(n), d0);
         const float q = (n.w < 0.0f) ? dn : -dn;
         const float len = p.pl_len[j];
-        miss = miss && (n.w == 0.0f || q * (1.0f - s) - len * s > 1e-3f * len);
+        if (n.w == 0.0f || q * (1.0f - s) - len * s > 1e-3f * len) pl_mask &= ~(1u << j);
     }
-    return miss;
+    return sph_mask | (pl_mask << 16);
+}
+
+// closest_hit_primary over the tile's candidates only, in scene order (the tie rule needs ascending order)
+__device__ __forceinline__ int closest_hit_primary_masked(const FrameParams &p, float3 dir, float tmin, float &t_out,
+                                                          unsigned cand)
+{
+    Closest c = { 0xffffffffu, -1 };
+#pragma unroll 1
+    for (unsigned m = cand & 0xffffu; m; m &= m - 1u) {
+        const int i = __ffs((int)m) - 1;
+        const float4 k = p.sph_cam[i];
+        const float b = dot3(dir, xyz(k));
+        sphere_candidate(b, b * b - k.w + p.sph[i].w, p.sph_idx[i], tmin, c);
+    }
+#pragma unroll 1
+    for (unsigned m = cand >> 16; m; m &= m - 1u) {
+        const int j = __ffs((int)m) - 1;
+        const float4 n = p.pl_n[j];
+        plane_candidate(n.w, dot3(xyz(n), dir), p.pl_idx[j], tmin, c);
+    }
+    t_out = (c.ind < 0) ? -1.0f : __uint_as_float(c.tb);
+    return c.ind;
 }
 
 __device__ __forceinline__ float3 shape_normal(const DevShape &s, float3 pt)

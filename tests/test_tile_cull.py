@@ -1,9 +1,11 @@
-"""The AO head's tile test (csrc/rt_trace_common.cuh: tile_misses_everything, bounds from rt_capi.cu:
-build_traversal_tables) must be CONSERVATIVE: a tile it declares empty may not contain a single camera ray --
-any sample, jitter included -- that hits anything.  This is a numpy restatement of the test checked against the
-oracle's frames on CPU: in every 8x4 tile it would cull, every pixel must have hit index -1 and exactly the
-all-background colour (one sample that hit something would change the sum).  It also reports how many of the truly
-empty tiles the test finds, so that a change that makes it useless is noticed as well."""
+"""The AO head's tile test (csrc/rt_trace_common.cuh: tile_candidates, bounds from rt_capi.cu:
+build_traversal_tables) must be CONSERVATIVE: an object it rules out for a tile may not be hit by a single camera
+ray of that tile -- any sample, jitter included.  This is a numpy restatement of the test, checked on CPU
+(a) against the oracle's frames: in every 8x4 tile left without candidates, every pixel must have hit index -1 and
+exactly the all-background colour (one sample that hit something would change the sum), and no pixel's hit index
+may be an object the tile ruled out; (b) against the geometry itself in binary64: rays through a dense set of
+points of the tile (its corners and the jitter range included) must all miss every object that was ruled out.
+It also checks how many of the truly empty tiles the test finds, so that a change that makes it useless is noticed."""
 import numpy as np
 import pytest
 
@@ -26,31 +28,39 @@ def cull_bounds(u, shapes, n, W, H):
             oc = cam - rec[0, :3]
             dd = f32((oc * oc).sum(dtype=f32))
             gap = dd - f32(rec[0, 3]) * f32(rec[0, 3])
-            sph.append((oc, f32(np.sqrt(dd)) * f32(1.001), gap * f32(0.999) if gap > 0 else f32(-1.0)))
+            sph.append((oc, f32(np.sqrt(dd)) * f32(1.001), gap * f32(0.999) if gap > 0 else f32(-1.0), i))
         elif kind == host.PLANE_ID:
             nrm = rec[0, :3].astype(f32)
             num = f32((nrm * (rec[3, :3] - cam)).sum(dtype=f32))
-            pl.append((nrm, num, f32(np.sqrt((nrm * nrm).sum(dtype=f32))) * f32(1.001)))
+            pl.append((nrm, num, f32(np.sqrt((nrm * nrm).sum(dtype=f32))) * f32(1.001), i))
     return cull_a, sph, pl
 
 
-def tile_misses_everything(u, bounds, hp0, vp0):
-    """device side"""
+def tile_candidates(u, bounds, hp0, vp0):
+    """device side: scene indices of the spheres / planes a camera ray of the tile may hit"""
     cull_a, sph, pl = bounds
     hz, vt, llc = u[1, :3].astype(f32), u[2, :3].astype(f32), u[3, :3].astype(f32)
     v0 = llc + f32(hp0) * hz + f32(vp0) * vt
     inv = f32(1.0) / np.sqrt(f32((v0 * v0).sum(dtype=f32)))
     d0 = v0 * inv
     s = cull_a * inv
-    miss = bool(s < f32(0.05))
-    for oc, ln, gap in sph:
+    if not (cull_a > 0 and s < f32(0.05)):
+        return {e[3] for e in sph} | {e[3] for e in pl}
+    keep = set()
+    for oc, ln, gap, idx in sph:
         m = abs(f32((d0 * oc).sum(dtype=f32))) + ln * s
-        miss = miss and bool(m * m < gap)
-    for nrm, num, ln in pl:
+        if not bool(m * m < gap):
+            keep.add(idx)
+    for nrm, num, ln, idx in pl:
         dn = f32((nrm * d0).sum(dtype=f32))
         q = dn if num < 0 else -dn
-        miss = miss and bool(num == 0 or q * (f32(1.0) - s) - ln * s > f32(1e-3) * ln)
-    return miss
+        if not bool(num == 0 or q * (f32(1.0) - s) - ln * s > f32(1e-3) * ln):
+            keep.add(idx)
+    return keep
+
+
+def tile_misses_everything(u, bounds, hp0, vp0):
+    return not tile_candidates(u, bounds, hp0, vp0)
 
 
 def sky_colour(bg, aa):
@@ -83,7 +93,10 @@ def test_culled_tiles_are_pure_background(scene, keys, W, H, AA):
             for tx in range(0, W, 8):
                 tile_sky = bool(is_sky[ty:ty + 4, tx:tx + 8].all())
                 empty += tile_sky
-                if tile_misses_everything(u, bounds, (f32(tx) + f32(3.5)) / f32(W), (f32(ty) + f32(1.5)) / f32(H)):
+                keep = tile_candidates(u, bounds, (f32(tx) + f32(3.5)) / f32(W), (f32(ty) + f32(1.5)) / f32(H))
+                seen = set(np.unique(hit[ty:ty + 4, tx:tx + 8]).tolist()) - {-1}
+                assert seen <= keep, f"{scene} frame {frame}: tile ({tx}, {ty}) rules out {seen - keep} but a camera ray hits it"
+                if not keep:
                     culled += 1
                     assert tile_sky, f"{scene} frame {frame}: tile ({tx}, {ty}) would be culled but is not pure background"
     o.close()
@@ -91,3 +104,40 @@ def test_culled_tiles_are_pure_background(scene, keys, W, H, AA):
     # (1920x1080, scene1: 23 038 of 25 289; a tile of a tiny frame subtends too large an angle for the margins)
     if W >= 640:
         assert culled >= 0.7 * empty, (culled, empty)
+
+
+@pytest.mark.parametrize("scene,keys,W,H", [("scene1", ("d", "w"), 320, 180), ("scene6", ("a",), 256, 144), ("scene5", (), 200, 120),
+                                            ("scene1", ("s",), 1920, 1080)])
+def test_ruled_out_objects_are_missed_by_every_ray_of_the_tile(scene, keys, W, H):
+    """binary64 geometry, independent of the oracle: rays through the tile's pixels shifted by the whole jitter range
+    (+-0.0834 pixel, corners included) against the exact sphere / plane conditions of the shaders"""
+    rng = np.random.default_rng(5)
+    sc = Scenario(scene, keys=keys, frametime=0.3)
+    for frame in range(4):
+        slot, u, rb = sc.next(2, 4)
+        bounds = cull_bounds(u, sc.shapes, sc.n, W, H)
+        hz, vt, llc, cam = (u[k, :3].astype(np.float64) for k in (1, 2, 3, 4))
+        tiles = [(int(rng.integers(0, W // 8)) * 8, int(rng.integers(0, (H + 3) // 4)) * 4) for _ in range(300)]
+        for tx, ty in tiles:
+            keep = tile_candidates(u, bounds, (f32(tx) + f32(3.5)) / f32(W), (f32(ty) + f32(1.5)) / f32(H))
+            out = [i for i in range(sc.n) if i not in keep and int(sc.shapes[i][4, 3]) in (host.SPHERE_ID, host.PLANE_ID)]
+            if not out:
+                continue
+            xs = np.concatenate([np.arange(8) + d for d in (-0.0834, 0.0, 0.0834)]) + tx
+            ys = np.concatenate([np.arange(4) + d for d in (-0.0834, 0.0, 0.0834)]) + ty
+            gx, gy = np.meshgrid(xs, ys)
+            v = llc[None, :] + (gx.ravel() / W)[:, None] * hz[None, :] + (gy.ravel() / H)[:, None] * vt[None, :]
+            d = v / np.linalg.norm(v, axis=1, keepdims=True)
+            for i in out:
+                rec = sc.shapes[i].astype(np.float64)
+                if int(rec[4, 3]) == host.SPHERE_ID:
+                    oc = cam - rec[0, :3]
+                    b = d @ oc
+                    delta = b * b - oc @ oc + rec[0, 3] ** 2
+                    assert (delta < 0).all(), f"{scene} frame {frame} tile ({tx}, {ty}): sphere {i} ruled out but delta max {delta.max()}"
+                else:
+                    num = rec[0, :3] @ (rec[3, :3] - cam)
+                    den = d @ rec[0, :3]
+                    with np.errstate(divide="ignore", invalid="ignore"):
+                        t = np.where(np.abs(den) < 0.001, -1.0, num / den)
+                    assert (t <= 0.0001).all(), f"{scene} frame {frame} tile ({tx}, {ty}): plane {i} ruled out but t max {t.max()}"
