@@ -141,3 +141,70 @@ def test_ruled_out_objects_are_missed_by_every_ray_of_the_tile(scene, keys, W, H
                     with np.errstate(divide="ignore", invalid="ignore"):
                         t = np.where(np.abs(den) < 0.001, -1.0, num / den)
                     assert (t <= 0.0001).all(), f"{scene} frame {frame} tile ({tx}, {ty}): plane {i} ruled out but t max {t.max()}"
+
+
+def _exact_hits(rec, cam, d):
+    """binary64 statement of sphere_eval_ray / plane_eval_ray's "can give t > tmin" for unit directions d[n][3]"""
+    if int(rec[4, 3]) == host.SPHERE_ID:
+        oc = cam - rec[0, :3]
+        b = d @ oc
+        return (b * b - oc @ oc + rec[0, 3] ** 2) >= 0
+    num = rec[0, :3] @ (rec[3, :3] - cam)
+    den = d @ rec[0, :3]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t = np.where(np.abs(den) < 0.001, -1.0, num / den)
+    return t > 0.0001
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_tile_test_holds_for_arbitrary_cameras(seed):
+    """random camera positions (far away, between the shapes, inside a sphere, on the floor plane, below it),
+    random view directions (straight up and down included) and frame sizes: no ruled-out object is hit by a ray
+    through the tile (binary64 geometry).  Also counts that the test is not vacuous."""
+    rng = np.random.default_rng(seed)
+    ruled_out = 0
+    for trial in range(60):
+        scene = ("scene1", "scene5", "scene6")[trial % 3]
+        sc = Scenario(scene)
+        W, H = [(64, 48), (440, 330), (1920, 1080), (203, 117), (7680, 4320)][trial % 5]
+        kind = trial % 6
+        if kind == 0:       # inside / at the surface of the first sphere
+            c = sc.shapes[0][0, :3] + rng.normal(size=3).astype(f32) * f32(0.3) * sc.shapes[0][0, 3]
+        elif kind == 1:     # exactly on the height of the first plane's point, if the scene has a plane
+            c = rng.uniform(-8, 8, 3).astype(f32)
+            for i in range(sc.n):
+                if int(sc.shapes[i][4, 3]) == host.PLANE_ID:
+                    c[1] = sc.shapes[i][3, 1]
+        elif kind == 2:     # far away
+            c = (rng.normal(size=3) * 300).astype(f32)
+        else:
+            c = rng.uniform(-12, 16, 3).astype(f32)
+        sc.cam.location = c.astype(f32)
+        look = rng.normal(size=3)
+        if trial % 7 == 0:
+            look = np.array([0.0, 1.0, 1e-3])      # nearly straight up: up x look is tiny
+        if trial % 11 == 0:
+            look = np.array([1e-3, -1.0, 0.0])
+        sc.cam.look_towards = (look / np.linalg.norm(look)).astype(f32)
+        hz, vt, llc = host.camera_basis(sc.cam, sc.aspect)
+        u = host.pack_uniforms(0, sc.n, hz, vt, llc, sc.cam.location, sc.light, sc.bg)
+        if not np.isfinite(u).all():
+            continue
+        bounds = cull_bounds(u, sc.shapes, sc.n, W, H)
+        hz64, vt64, llc64, cam64 = (u[k, :3].astype(np.float64) for k in (1, 2, 3, 4))
+        for _ in range(40):
+            tx, ty = int(rng.integers(0, (W + 7) // 8)) * 8, int(rng.integers(0, (H + 3) // 4)) * 4
+            keep = tile_candidates(u, bounds, (f32(tx) + f32(3.5)) / f32(W), (f32(ty) + f32(1.5)) / f32(H))
+            out = [i for i in range(sc.n) if i not in keep and int(sc.shapes[i][4, 3]) in (host.SPHERE_ID, host.PLANE_ID)]
+            ruled_out += len(out)
+            if not out:
+                continue
+            xs = np.concatenate([np.arange(8) + d for d in (-0.0834, 0.0, 0.0834)]) + tx
+            ys = np.concatenate([np.arange(4) + d for d in (-0.0834, 0.0, 0.0834)]) + ty
+            gx, gy = np.meshgrid(xs, ys)
+            v = llc64[None, :] + (gx.ravel() / W)[:, None] * hz64[None, :] + (gy.ravel() / H)[:, None] * vt64[None, :]
+            d = v / np.linalg.norm(v, axis=1, keepdims=True)
+            for i in out:
+                assert not _exact_hits(sc.shapes[i].astype(np.float64), cam64, d).any(), \
+                    f"trial {trial} ({scene}, {W}x{H}, camera {c}, look {look}): object {i} ruled out for tile ({tx}, {ty}) but hit"
+    assert ruled_out > 500, ruled_out
