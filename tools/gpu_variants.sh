@@ -10,7 +10,7 @@ for tag in $1; do
 import json
 try:
     d=json.loads(open("gpurun_out/var.json").read().strip().splitlines()[-1])
-    print("$tag ${RT_AO_KERNEL:-phased} $wl", "frame", d["ms_per_step"], "trace_ms", d["roofline"]["kernel_ms"], "Mrays/s", d["value"])
+    print("$tag ${RT_AO_KERNEL:-pulled} $wl", "frame", d["ms_per_step"], "trace_ms", d["roofline"]["kernel_ms"], "Mrays/s", d["value"])
 except Exception as e: print("$tag $wl failed", e)
 PY
   done
