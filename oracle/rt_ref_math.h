@@ -7,7 +7,7 @@
  * so the built-ins are DEFINED here, once, as sequences of IEEE-754 operations
  * that a CPU and a GPU both execute bit-for-bit:
  *
- *   + - * / sqrt in binary32/binary64, round-to-nearest-even, no flush-to-zero,
+ *   + - * / sqrt in binary32 (binary64 only where the shader says double), round-to-nearest-even, no flush-to-zero,
  *   fused multiply-add ONLY where it is written as fmaf()/fma() below.
  *
  * The CUDA kernels (real_time_ray_tracer_b200/csrc/rt_math.cuh) implement the
@@ -37,10 +37,6 @@
 #else
 #define RTR_INLINE static inline
 #endif
-
-/* ---- bit casts ---------------------------------------------------------- */
-RTR_INLINE uint64_t rtr_d2u(double d) { uint64_t u; memcpy(&u, &d, 8); return u; }
-RTR_INLINE double rtr_u2d(uint64_t u) { double d; memcpy(&d, &u, 8); return d; }
 
 /* ---- sin(float) ----------------------------------------------------------
  * binary32 throughout: k = round(x * 2/pi) by the add-magic trick, Cody-Waite reduction
@@ -81,89 +77,83 @@ RTR_INLINE float rtr_sin(float x)
 }
 
 /* ---- pow(float x, float y) for x >= 0 ------------------------------------
- * exp(y*log(x)) in binary64; log from fdlibm e_log.c's reduction and Lg1..Lg7,
- * exp as 2^k * Taylor(r) with |r| <= ln2/2, degree 11.  x == 0 -> 0 (all call
- * sites have y > 0), x < 0 or NaN -> NaN.  Relative error ~1e-15 before the
- * final rounding to binary32.
+ * binary32 throughout, exp2(y * log2(x)) with log2(x) and the product carried as
+ * hi + lo pairs (the pow a GPU driver emits is ex2(y * lg2(x)); this is the same
+ * decomposition with the error terms kept).  Every operation below is one IEEE-754
+ * binary32 operation, fused only where fmaf is written:
+ *   x = m * 2^e, m in [sqrt(1/2), sqrt(2)) (integer arithmetic on the bit pattern;
+ *     subnormal x is first scaled by 2^24);  f = m - 1 (exact)
+ *   log(m) = f + c,  c = s*(f*f/2 + R(s*s)) - f*f/2,  s = f * RN(1/(2+f)),
+ *     R = the four-term series of fdlibm's e_logf.c (Lg1..Lg4, |error| < 2^-34)
+ *   (l_hi, l_lo) = Fast2Sum(f, c);  (p_hi, p_lo) = (l_hi, l_lo) * (LOG2E_HI, LOG2E_LO)
+ *   (L_hi, L_lo) = e + (p_hi, p_lo);  (t_hi, t_lo) = y * (L_hi, L_lo)
+ *   k = round(t_hi) (add-magic), r = (t_hi - k) + t_lo,
+ *   2^r = 1 + r*Q(r), Q of degree 6 (minimax on [-1/2, 1/2], |rel. error| < 1.6e-9)
+ *   result = (2^r * 2^(k>>1)) * 2^(k - (k>>1))   (one rounding, also for subnormal results)
+ * x == 0 -> 0 (every call site has y > 0), x < 0 or NaN or y NaN -> NaN, x = inf -> inf,
+ * t_hi >= 128.5 or NaN -> inf, t_hi < -150.5 -> 0.
+ * Measured against binary64 pow (tests/test_oracle_math.py): < 1 ulp for y = 1/2.2 (the gamma,
+ * ao_compute.glsl:335) over all positive binary32 x; for y = 500 (the specular exponent,
+ * p_compute.glsl:208) < 1 ulp wherever the result is above 1e-6 and < 16 ulp below that.
+ * Round 1 defined pow in binary64 (fdlibm log + degree-11 exp); ncu showed it was 24 % of
+ * the hybrid kernel's and 9 % of the AO kernel's issued instructions.
  */
-#define RTR_RND_MAGIC 6755399441055744.0 /* 1.5 * 2^52 */
-#define RTR_LN2_HI 6.93147180369123816490e-01 /* 0x3FE62E42FEE00000 */
-#define RTR_LN2_LO 1.90821492927058770002e-10 /* 0x3DEA39EF35793C76 */
-#define RTR_LOG2E 1.44269504088896338700e+00  /* 0x3FF71547652B82FE */
+#define RTR_POW_LOG2E_HI 0x1.715476p+0f   /* RN32(log2 e)                0x3FB8AA3B */
+#define RTR_POW_LOG2E_LO 0x1.4ae0cp-26f   /* RN32(log2 e - LOG2E_HI)     0x32A57060 */
+#define RTR_POW_MAGIC 12582912.0f         /* 1.5 * 2^23 */
 
-RTR_INLINE double rtr_log_pos(double x) /* x finite, > 0, normal */
-{
-    static const double Lg[7] = {
-        1.479819860511658591e-01, 1.531383769920937332e-01,
-        1.818357216161805012e-01, 2.222219843214978396e-01,
-        2.857142874366239149e-01, 3.999999999940941908e-01,
-        6.666666666666735130e-01 };
-    uint64_t u = rtr_d2u(x);
-    int e = (int)(u >> 52) - 1023;
-    uint64_t mant = u & 0x000FFFFFFFFFFFFFull;
-    /* m in [1,2); fold [sqrt2,2) down to [sqrt2/2,1) */
-    if (mant > 0x6A09E667F3BCDull) { /* m > sqrt(2) */
-        e += 1;
-        u = mant | 0x3FE0000000000000ull;
-    } else {
-        u = mant | 0x3FF0000000000000ull;
-    }
-    double m = rtr_u2d(u);
-    double f = m - 1.0;
-    double s = f / (2.0 + f);
-    double z = s * s;
-    double R = Lg[0];
-    R = fma(R, z, Lg[1]);
-    R = fma(R, z, Lg[2]);
-    R = fma(R, z, Lg[3]);
-    R = fma(R, z, Lg[4]);
-    R = fma(R, z, Lg[5]);
-    R = fma(R, z, Lg[6]);
-    R = R * z;
-    double hfsq = 0.5 * f * f;
-    /* log(1+f) = f - (hfsq - s*(hfsq+R)) */
-    double lm = f - (hfsq - s * (hfsq + R));
-    double de = (double)e;
-    return fma(de, RTR_LN2_HI, fma(de, RTR_LN2_LO, lm));
-}
-
-RTR_INLINE double rtr_exp_clamped(double a) /* a finite */
-{
-    static const double T[12] = { /* 1/11! ... 1/0! */
-        2.50521083854417187751e-08, 2.75573192239858906526e-07,
-        2.75573192239858906526e-06, 2.48015873015873015873e-05,
-        1.98412698412698412698e-04, 1.38888888888888888889e-03,
-        8.33333333333333333333e-03, 4.16666666666666666667e-02,
-        1.66666666666666666667e-01, 5.0e-01, 1.0, 1.0 };
-    if (a < -125.0) a = -125.0; /* e^-125 rounds to 0 in binary32 */
-    if (a > 89.5) a = 89.5;     /* e^89.5 rounds to +inf in binary32 */
-    double kd = (a * RTR_LOG2E + RTR_RND_MAGIC) - RTR_RND_MAGIC;
-    double r = fma(-kd, RTR_LN2_HI, a);
-    r = fma(-kd, RTR_LN2_LO, r);
-    double p = T[0];
-    p = fma(p, r, T[1]);
-    p = fma(p, r, T[2]);
-    p = fma(p, r, T[3]);
-    p = fma(p, r, T[4]);
-    p = fma(p, r, T[5]);
-    p = fma(p, r, T[6]);
-    p = fma(p, r, T[7]);
-    p = fma(p, r, T[8]);
-    p = fma(p, r, T[9]);
-    p = fma(p, r, T[10]);
-    p = fma(p, r, T[11]);
-    int64_t k = (int64_t)kd; /* |k| <= 181 */
-    double scale = rtr_u2d((uint64_t)(k + 1023) << 52);
-    return p * scale;
-}
+RTR_INLINE uint32_t rtr_f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+RTR_INLINE float rtr_u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 
 RTR_INLINE float rtr_pow(float x, float y)
 {
-    if (!(x >= 0.0f)) return NAN; /* negative or NaN */
+    if (!(x >= 0.0f) || y != y) return NAN; /* negative or NaN */
     if (x == 0.0f) return 0.0f;
     if (isinf(x)) return INFINITY;
-    double lx = rtr_log_pos((double)x);
-    return (float)rtr_exp_clamped((double)y * lx);
+    int e = 0;
+    uint32_t ix = rtr_f2u(x);
+    if (ix < 0x00800000u) { /* subnormal */
+        x = x * 16777216.0f;
+        ix = rtr_f2u(x);
+        e = -24;
+    }
+    int de = (int)(ix - 0x3f3504f3u) >> 23; /* arithmetic shift: floor */
+    e += de;
+    float m = rtr_u2f(ix - ((uint32_t)de << 23));
+    float f = m - 1.0f;
+    float s = f * (1.0f / (2.0f + f));
+    float z = s * s;
+    float R = 0.24279078841f;           /* Lg4 */
+    R = fmaf(R, z, 0.28498786688f);     /* Lg3 */
+    R = fmaf(R, z, 0.40000972152f);     /* Lg2 */
+    R = fmaf(R, z, 0.66666662693f);     /* Lg1 */
+    R = R * z;
+    float hfsq = (0.5f * f) * f;
+    float c = fmaf(s, hfsq + R, -hfsq);
+    float l_hi = f + c;
+    float l_lo = (f - l_hi) + c;
+    float p_hi = l_hi * RTR_POW_LOG2E_HI;
+    float p_lo = fmaf(l_lo, RTR_POW_LOG2E_HI, fmaf(l_hi, RTR_POW_LOG2E_LO, fmaf(l_hi, RTR_POW_LOG2E_HI, -p_hi)));
+    float fe = (float)e;
+    float L_hi = fe + p_hi;
+    float L_lo = ((fe - L_hi) + p_hi) + p_lo;
+    float t_hi = y * L_hi;
+    float t_lo = fmaf(y, L_lo, fmaf(y, L_hi, -t_hi));
+    if (!(t_hi < 128.5f)) return INFINITY;
+    if (t_hi < -150.5f) return 0.0f;
+    float kf = (t_hi + RTR_POW_MAGIC) - RTR_POW_MAGIC;
+    float r = (t_hi - kf) + t_lo;
+    float q = 0x1.fde5fep-17f;
+    q = fmaf(q, r, 0x1.445c84p-13f);
+    q = fmaf(q, r, 0x1.5d8a86p-10f);
+    q = fmaf(q, r, 0x1.3b29f4p-7f);
+    q = fmaf(q, r, 0x1.c6b08ap-5f);
+    q = fmaf(q, r, 0x1.ebfbep-3f);
+    q = fmaf(q, r, 0x1.62e43p-1f);
+    float v = fmaf(q, r, 1.0f);
+    int k = (int)kf; /* -151 .. 128 */
+    int k1 = k >> 1, k2 = k - k1;
+    return (v * rtr_u2f((uint32_t)(k1 + 127) << 23)) * rtr_u2f((uint32_t)(k2 + 127) << 23);
 }
 
 /* ---- scalar helpers ------------------------------------------------------ */

@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librt_b200.so")
-SOURCES = ["rt_kernels.cu", "rt_ao_phased.cu", "rt_ao_queued.cu", "rt_ao_pulled.cu", "rt_ao_stream.cu", "rt_capi.cu"]
+SOURCES = ["rt_kernels.cu", "rt_ao_phased.cu", "rt_ao_pulled.cu", "rt_capi.cu"]
 DEPS = SOURCES + ["rt_kernels.cuh", "rt_math.cuh", "rt_trace_common.cuh", os.path.join("..", "..", "include", "rt.h")]
 
 NVCC_FLAGS = [

@@ -32,14 +32,11 @@ struct rt_ctx {
     void *halo[4] = { nullptr, nullptr, nullptr, nullptr }; // send_lo, send_hi, recv_lo, recv_hi
     void *staging = nullptr; // npix * 16 bytes, layout conversions
     unsigned long long *stats = nullptr;
-    unsigned *work = nullptr; // streaming AO kernel's unit counters
-    TailQueue tq{};           // AO_KERNEL_QUEUED (allocated when aa <= 4)
-    unsigned frame_parity = 0;
     float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
     float4 sky_bg{};
     bool sky_valid = false;
     bool ao_cull = true;      // RT_AO_CULL=0 switches the tile test (tile_candidates) off (A/B)
-    int ao_kernel = AO_KERNEL_PULLED; // RT_AO_KERNEL=phased|queued|tile|stream selects the earlier kernels (A/B profiling)
+    int ao_kernel = AO_KERNEL_PULLED; // RT_AO_KERNEL=phased selects the A/B partner
     unsigned long long *stats_host = nullptr; // pinned
     DevShape shapes[RT_MAX_SHAPES]{};
     int nshapes = 0;
@@ -105,8 +102,7 @@ static void free_all(rt_ctx *c)
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
-    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->work); cudaFree(c->sky);
-    cudaFree(c->tq.entries); cudaFree(c->tq.counters);
+    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->sky);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
@@ -173,26 +169,17 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0((void **)&c->hit, c->npix * sizeof(int));
     alloc0(&c->staging, c->npix * sizeof(float4));
     alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
-    alloc0((void **)&c->work, 2 * sizeof(unsigned));
     alloc0((void **)&c->sky, 6 * sizeof(float));
     if (const char *k = getenv("RT_AO_CULL")) c->ao_cull = strcmp(k, "0") != 0;
     if (const char *k = getenv("RT_AO_KERNEL")) {
-        if (!strcmp(k, "tile")) c->ao_kernel = AO_KERNEL_TILE;
-        else if (!strcmp(k, "stream")) c->ao_kernel = AO_KERNEL_STREAM;
-        else if (!strcmp(k, "queued")) c->ao_kernel = AO_KERNEL_QUEUED;
-        else if (!strcmp(k, "phased")) c->ao_kernel = AO_KERNEL_PHASED;
+        if (!strcmp(k, "phased")) c->ao_kernel = AO_KERNEL_PHASED;
         else if (strcmp(k, "pulled")) {
-            fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected phased, pulled, queued, tile or stream)", k);
+            fail(nullptr, RT_EINVAL, "rt_create: RT_AO_KERNEL=%s (expected pulled or phased)", k);
             free_all(c);
             return RT_EINVAL;
         }
     }
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width));
-    if (c->ao_kernel == AO_KERNEL_QUEUED && cfg->aa <= 4) {
-        // worst case every pixel of the band is queued
-        alloc0((void **)&c->tq.entries, c->npix * TQ_ENTRY_VEC4 * sizeof(float4));
-        alloc0((void **)&c->tq.counters, 8 * sizeof(unsigned));
-    }
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -362,11 +349,8 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     o.depth_w = c->ring_depth_w + off;
     o.hit = c->hit;
     o.stats = c->stats;
-    o.work = c->work;
     o.ao_kernel = c->ao_kernel;
     o.sky = c->sky;
-    o.tq = c->tq;
-    if (ao) { o.tq.parity = (int)(c->frame_parity & 1u); c->frame_parity++; }
     if (ao && (!c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0)) {
         // first AO frame, or the background changed (scene toggle, src/main.cpp:229-255)
         CU(c, launch_sky_gamma(p.bg, p.AA, c->sky, c->stream));

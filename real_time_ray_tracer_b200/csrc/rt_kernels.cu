@@ -1,6 +1,6 @@
 // rt_kernels.cu -- sm_100a kernels of the per-pixel hot path.
 //
-//   rt_ao_trace_kernel      <- resources/ao_compute.glsl:161-340 (= aop_compute.glsl:159-337)
+//   (AO trace, modes 1/2: rt_ao_pulled.cu, A/B partner rt_ao_phased.cu)
 //   rt_phong_kernel         <- resources/p_compute.glsl:145-246
 //   rt_hybrid_kernel        <- resources/h_compute.glsl:145-322
 //   rt_halo_pack_kernel     <- the out-of-range neighbour reads of aop_postprocessing.glsl:81-90,150-159
@@ -38,143 +38,6 @@ __device__ __forceinline__ void flush_stats(unsigned long long *stats, const int
         unsigned v = __reduce_add_sync(0xffffffffu, val[k]);
         if ((threadIdx.x & 31) == 0 && v) atomicAdd(&st[idx[k]], (unsigned long long)v);
     }
-}
-
-// ---------------------------------------------------------------------------------------------
-// AO trace (modes 1 and 2)
-// ---------------------------------------------------------------------------------------------
-// One thread per pixel.  The AA samples and their <= RD path segments are flattened into ONE loop
-// whose body is one segment, so a warp stays converged on the intersection code and its run time is
-// max over lanes of the pixel's total segment count (not the sum over samples of the per-sample max).
-__global__ void __launch_bounds__(TRACE_THREADS) rt_ao_trace_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
-{
-    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
-    __shared__ float4 s_rand[2 * RT_MAX_AA];
-    for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
-    for (int i = threadIdx.x; i < 2 * p.AA; i += blockDim.x) s_rand[i] = p.rand[i];
-    __syncthreads();
-
-    int x, yl;
-    tile_pixel(x, yl);
-    const bool active = (x < p.W) && (yl < p.rows);
-    const int y = p.y0 + yl;
-    const size_t pix = (size_t)yl * p.W + x;
-    unsigned n_nonterm = 0, n_term = 0;
-
-    if (active) {
-        const float fx = (float)x, fy = (float)y;
-        float ar = 0.0f, ag = 0.0f, ab = 0.0f;   // result_color summed over samples
-        float3 nrm = mk3(0.0f, 0.0f, 0.0f);
-        float nrm_w = 0.0f;
-        float dx = 0.0f, dy = 0.0f, dw = 0.0f;  // depth_buffer[frame][x][y] (.z is always 0)
-        bool keep_normal = false;
-        int hit0 = -1;
-
-        int aa = 0;
-        bool need_new = true, have_ru = false;
-        float3 pos = p.cam, dir = p.cam, ru = p.cam;
-        float cr = 1.0f, cg = 1.0f, cb = 1.0f;
-        int i = p.RD;
-
-        while (aa < p.AA) {
-            if (need_new) {
-                float hp, vp;
-                if (aa == 0) {
-                    hp = div_const(fx, p.fW, p.invW);
-                    vp = div_const(fy, p.fH, p.invH);
-                } else {
-                    // ao_compute.glsl:310-323, seeds cross-wired exactly as written there
-                    float4 rf = s_rand[2 * aa], rs = s_rand[2 * aa + 1];
-                    float s1x = rs.x, s1y = rf.y, s2x = rf.z, s2y = rs.w;
-                    float s3x = rf.x, s3y = rs.y, s4x = rs.z, s4y = rf.w;
-                    float ax = ((s1x + fx * s2x) - fx) + s3x;
-                    float ay = ((s1y + fy * s2y) - fy) + s3y;
-                    float bx = s4x * fx - (s3x * fx) * s2x;
-                    float by = s4y * fy - (s3y * fy) * s2y;
-                    float r1 = random2(ax, ay), r2 = random2(bx, by);
-                    float inv = inv_sqrt_ieee(dot2(r1, r2, r1, r2));
-                    float jx = div_const(r1 * inv, 6.0f, RT_INV6) - 0.08333f;
-                    float jy = div_const(r2 * inv, 6.0f, RT_INV6) - 0.08333f;
-                    hp = div_const(fx + jx, p.fW, p.invW);
-                    vp = div_const(fy + jy, p.fH, p.invH);
-                }
-                dir = primary_dir(p, hp, vp);
-                pos = p.cam;
-                cr = cg = cb = 1.0f;
-                i = p.RD;
-                need_new = false;
-                have_ru = false;
-            }
-
-            // ---- one path segment: ambient_occlusion_helper, ao_compute.glsl:161-261 ----
-            float t;
-            const int ind = closest_hit(p, pos, dir, 0.0001f, t);
-            const bool first = (aa == 0) && (i == p.RD);
-            if (first) hit0 = ind;
-            bool stop;
-            float a0r, a0g, a0b;
-            if (ind < 0) {
-                if (first) { nrm = mk3(0.0f, 0.0f, 0.0f); nrm_w = 0.0f; dx = 0.0f; dw = 0.0f; }
-                a0r = p.bg.x; a0g = p.bg.y; a0b = p.bg.z;
-                stop = true;
-                dy = (float)(p.RD - i);
-            } else {
-                const DevShape &s = s_shapes[ind];
-                a0r = s.col.x; a0g = s.col.y; a0b = s.col.z;
-                if (s.emissive > 0.9f) {
-                    if (first) {
-                        // the shader returns before touching normals/depth: the slot keeps what an
-                        // earlier frame left there (ao_compute.glsl:199-208 precede :222-229)
-                        keep_normal = true;
-                        float2 od = o.depth_xy[pix];
-                        dx = od.x;
-                        dw = o.depth_w[pix];
-                    }
-                    stop = true;
-                    dy = (float)(p.RD - i);
-                } else {
-                    float3 curr_pos = add3(p.cam, scale3(t, dir)); // camera origin even on bounces (:210)
-                    float3 normal = shape_normal(s, curr_pos);
-                    if (first) { nrm = normal; nrm_w = 1.0f; dx = t; dy = 0.0f; dw = 1.0f; }
-                    pos = curr_pos;
-                    if (!have_ru) {
-                        ru = get_pt_within_unit_sphere(s_rand[2 * aa], s_rand[2 * aa + 1], fx, fy);
-                        have_ru = true;
-                    }
-                    float refl = s.s3.w;
-                    if (refl > 0.999f) {
-                        dir = normalize3(add3(ru, normal));
-                    } else {
-                        float dn = dot3(dir, normal);
-                        float3 R = normalize3(sub3(dir, scale3(2.0f, scale3(dn, normal))));
-                        dir = normalize3(add3(R, scale3(refl, ru)));
-                    }
-                    stop = false;
-                }
-            }
-            cr *= a0r; cg *= a0g; cb *= a0b;
-            if (stop) n_term++; else n_nonterm++;
-            i--;
-            if (stop || i == 0) {
-                ar += cr; ag += cg; ab += cb;
-                aa++;
-                need_new = true;
-            }
-        }
-
-        float4 c = gamma_correct(div_aa(p, ar), div_aa(p, ag), div_aa(p, ab));
-        o.color[pix] = c;
-        gather_store(o.gather, yl, pix, c);
-        if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
-        o.depth_xy[pix] = make_float2(div_aa(p, dx), div_aa(p, dy));
-        o.depth_w[pix] = div_aa(p, dw);
-        o.hit[pix] = hit0;
-    }
-
-    const int idx[6] = { ST_SEG_NONTERMINAL, ST_SEG_TERMINAL, ST_RAYS_CLOSEST, ST_PIXELS, ST_PRIMARY, ST_JITTERED };
-    unsigned val[6] = { n_nonterm, n_term, n_nonterm + n_term, active ? 1u : 0u, active ? 1u : 0u,
-                        active ? (unsigned)(p.AA - 1) : 0u };
-    flush_stats<6>(o.stats, idx, val);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -335,14 +198,8 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
 {
     dim3 grid((p.W + TILE_W - 1) / TILE_W, (p.rows + TILE_H - 1) / TILE_H);
     dim3 block(TRACE_THREADS);
-    if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO) {
-        const bool queued = (o.ao_kernel == AO_KERNEL_QUEUED);
-        if (queued && o.tq.entries && p.AA <= 4) return launch_ao_queued(p, o, s);
-        if (o.ao_kernel == AO_KERNEL_PULLED) return launch_ao_pulled(p, o, s);
-        if (o.ao_kernel == AO_KERNEL_PHASED || queued) return launch_ao_phased(p, o, s);
-        if (o.ao_kernel == AO_KERNEL_STREAM) return launch_ao_stream(p, o, s);  // persistent ray queue (rt_ao_stream.cu)
-        rt_ao_trace_kernel<<<grid, block, 0, s>>>(p, o); // first-generation tile kernel, kept for A/B profiling
-    }
+    if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO)
+        return (o.ao_kernel == AO_KERNEL_PHASED) ? launch_ao_phased(p, o, s) : launch_ao_pulled(p, o, s);
     else if (p.mode == RT_MODE_PHONG)
         rt_phong_kernel<<<grid, block, 0, s>>>(p, o);
     else

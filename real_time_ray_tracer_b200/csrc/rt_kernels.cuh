@@ -77,16 +77,7 @@ enum StatIdx {
     ST_COUNT
 };
 
-enum { AO_KERNEL_PHASED = 0, AO_KERNEL_TILE = 1, AO_KERNEL_STREAM = 2, AO_KERNEL_QUEUED = 3, AO_KERNEL_PULLED = 4 };
-
-// device queue of the two-kernel AO schedule (rt_ao_queued.cu): one entry per pixel that still has path
-// segments to trace after the head: [0] = (pixel index, pending mask, depth.x, -), then two float4 per sample
-constexpr int TQ_ENTRY_VEC4 = 9;
-struct TailQueue {
-    float4 *entries;    // [capacity][TQ_ENTRY_VEC4]
-    unsigned *counters; // [2][4]: {entries appended, -, -, -} per frame parity
-    int parity;
-};
+enum { AO_KERNEL_PHASED = 0, AO_KERNEL_PULLED = 4 };
 
 // rt_set_frame_targets: where the final colour of this band goes besides the ring slot.  Segment k covers the
 // band-local rows [row_end[k-1], row_end[k]) (row_end[-1] = 0, row_end[count-1] = rows of the band); img[k] is
@@ -116,9 +107,7 @@ struct TraceOut {
     float *depth_w;   // ring depth.w plane of the slot
     int *hit;         // hit-index plane
     unsigned long long *stats; // [STAT_STRIPES][ST_COUNT]
-    unsigned *work;   // [2] unit counter + finished-warp counter of the streaming AO kernel (self re-arming)
     int ao_kernel;    // AO_KERNEL_*
-    TailQueue tq;     // AO_KERNEL_QUEUED
     const float *sky; // [6] all-background colour sum and its gamma (rt_sky_gamma_kernel), phased AO kernel
     GatherTargets gather; // rt_set_frame_target(s): the assembled frame(s) this band's final colour also goes into
 };
@@ -163,9 +152,7 @@ cudaError_t launch_fence(const PeerBoxes &peers, int rank, int world, unsigned l
 
 // launchers (rt_kernels.cu)
 cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s);
-cudaError_t launch_ao_stream(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_phased(const FrameParams &p, const TraceOut &o, cudaStream_t s);
-cudaError_t launch_ao_queued(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_ao_pulled(const FrameParams &p, const TraceOut &o, cudaStream_t s);
 cudaError_t launch_sky_gamma(float4 bg, int AA, float *sky, cudaStream_t s);
 cudaError_t launch_halo_pack(const PostParams &q, cudaStream_t s);

@@ -276,7 +276,7 @@ def test_row_bands_on_one_gpu_equal_the_whole_frame(edge_mode, cuts):
         o.close()
 
 
-@pytest.mark.parametrize("kernel", ["phased", "pulled", "queued", "stream"])
+@pytest.mark.parametrize("kernel", ["phased", "pulled"])
 def test_frame_target_assembles_the_bands(kernel, monkeypatch):
     """rt_set_frame_target: three band contexts store their final colour straight into one whole-frame image
     (here on the same GPU; across ranks the same pointer is a peer mapping) -- it must equal the oracle's
@@ -338,7 +338,7 @@ def test_frame_target_assembles_the_bands(kernel, monkeypatch):
     o.close()
 
 
-@pytest.mark.parametrize("kernel", ["phased", "pulled", "queued", "tile", "stream"])
+@pytest.mark.parametrize("kernel", ["phased", "pulled"])
 def test_split_frame_targets_spread_the_rows_over_their_owners(kernel, monkeypatch):
     """rt_set_frame_targets: three images own rows [0,20), [20,20) (none) + [20,41) and [41,57) of the frame;
     three bands whose cuts do NOT coincide with the owners' store every pixel into its owner.  Each image must
@@ -715,7 +715,7 @@ def test_pulled_kernel_does_not_depend_on_who_traced_what():
         o.close()
 
 
-@pytest.mark.parametrize("kernel", ["phased", "pulled", "queued", "tile", "stream"])
+@pytest.mark.parametrize("kernel", ["phased", "pulled"])
 def test_all_ao_kernels(kernel, monkeypatch):
     """the phased (default), tile and persistent streaming kernels are three schedules of the same arithmetic;
     recursion depths 1, 2 and 3 exercise the phased kernel's head-only, no-survivor and first-survivor paths"""
