@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* compile-time limits (reference: NUM_SHAPES 10 src/main.cpp:34; AA 4 :31) */
 #define RT_MAX_SHAPES 10
@@ -156,7 +156,9 @@ typedef struct rt_stats {
  * `[f][x][-1]` reads).  The caller moves send_hi -> recv_lo of band (i+1) % count and
  * send_lo -> recv_hi of band i-1 (NCCL, cudaMemcpyPeer, ...), then calls rt_postprocess. */
 typedef struct rt_halo_info {
-    void *send_lo, *send_hi, *recv_lo, *recv_hi;
+    void *send_lo, *send_hi, *recv_lo, *recv_hi; /* recv_lo / recv_hi are allocations of 2 * row_bytes: linked bands
+                                                    (rt_link_peers) alternate between the two rows by frame parity;
+                                                    a caller that moves the rows itself uses the first one only */
     size_t row_bytes;
 } rt_halo_info;
 
@@ -228,10 +230,15 @@ int rt_device_ptr(rt_ctx *ctx, int buffer, int slot, void **out_ptr, size_t *out
  * available: a barrier on the context's stream, one small kernel that signals every peer's mailbox and
  * spins on its own until every peer has signalled (each rank must own its GPU; after rt_fence returns on
  * the stream, everything the other ranks enqueued before THEIR rt_fence is complete and visible); and
- * (b) the neighbours' halo rows, so that rt_halo_pack stores this band's edge rows straight into
- * recv_lo of band (i+1) % count and recv_hi of band i-1.  A mode-1 frame then is
- *     rt_render_frame; rt_halo_pack; rt_fence; rt_postprocess; rt_fence
- * with no host-side communication call at all. */
+ * (b) the neighbours' halo rows, so that the halo exchange happens INSIDE the two kernels of the second pass:
+ * rt_halo_pack stores this band's edge rows straight into recv_lo of band (i+1) % count and recv_hi of band
+ * i-1 (the row of the frame's parity) and then publishes the frame's sequence number in those bands' mailboxes;
+ * the edge rows of rt_postprocess -- scheduled last -- wait for the sequence number in their own mailbox before
+ * they read the halo.  A mode-1 frame then is
+ *     rt_render_frame; rt_halo_pack; rt_postprocess
+ * with no barrier between the ranks and no host-side communication call: a rank only ever waits for its two
+ * neighbours, and only in the last blocks of a kernel.  Every rank must render the same sequence of frames.
+ * rt_fence remains the way to close a frame (all bands stored / copied into the frame images). */
 int rt_frame_create(int device, int width, int height, void **out_frame);
 int rt_frame_destroy(int device, void *frame);
 int rt_set_frame_target(rt_ctx *ctx, void *frame); /* NULL = off; takes effect with the next rt_render_frame */
@@ -268,8 +275,18 @@ int rt_mailbox_destroy(int device, void *mailbox);
  * this context's own send rows (prev_recv_hi is NULL for band 0). */
 int rt_link_peers(rt_ctx *ctx, int rank, int world, void *const *mailboxes, void *next_recv_lo, void *prev_recv_hi);
 int rt_fence(rt_ctx *ctx);
+/* The same barrier off the critical path: it is enqueued on an internal stream behind the work issued on the
+ * context's stream so far, and the context's stream goes on.  rt_fence_join(ctx, 0) makes the context's stream
+ * wait for the newest such barrier (device side), rt_fence_join(ctx, 1) blocks the host until it has completed:
+ * the frames issued before it are then complete in the frame images on every rank. */
+int rt_fence_async(rt_ctx *ctx);
+int rt_fence_join(rt_ctx *ctx, int block_host);
 /* synchronises; *timed_out = 1 if a fence gave up waiting for a peer (10 s): the frame data is not valid */
 int rt_fence_status(rt_ctx *ctx, int *timed_out);
+
+/* the G-buffer ring, the raw plane and the hit-index plane back to zero, i.e. the state right after rt_create
+ * (the reference's value-initialised ssbo_CPUMEM, src/main.cpp:810); asynchronous on the context's stream */
+int rt_reset_ring(rt_ctx *ctx);
 
 int rt_get_stats(rt_ctx *ctx, rt_stats *out); /* synchronises */
 int rt_reset_stats(rt_ctx *ctx);

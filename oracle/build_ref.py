@@ -116,10 +116,11 @@ template <class S> static void dispatch(ref_ctx *c, int nthreads, int y0, int y1
     S *sh = (S *)c->ssbo;
     glsl::shader_base::img_output.data = c->image;
     glsl::shader_base::img_output.width = WIDTH;
-    /* glDispatchCompute(WIDTH, HEIGHT, 1) with 1x1 work-groups (src/main.cpp:604) */
-#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
-    for (int y = y0; y < y1; y++)
-        for (int x = 0; x < WIDTH; x++) {
+    /* glDispatchCompute(WIDTH, HEIGHT, 1) with 1x1 work-groups (src/main.cpp:604).  Columns outermost: the
+       block is x-major (pixels[f][x][y]), so a thread walks contiguous memory. */
+#pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads)
+    for (int x = 0; x < WIDTH; x++)
+        for (int y = y0; y < y1; y++) {
             glsl::shader_base::gl_GlobalInvocationID = glsl::uvec3((unsigned)x, (unsigned)y, 0u);
             sh->main();
         }
@@ -172,24 +173,23 @@ int glslref_dispatch_rows(ref_ctx *c, int program, int nthreads, int y0, int y1)
         glsl::shader_base::img_output.width = WIDTH;
         int frame = (int)sh->mode.y;
         /* An invocation writes pixels[frame][x][y] at its end (restored to the raw value right after), and the
-           invocations of rows y-1 and y+1 read it (row 0 also reads row HEIGHT-1: `y - 1 > 0` on a uint).  Rows
-           are therefore run in three interleaved passes -- rows 3 apart do not read each other -- with row 0 on
-           its own, so the passes can use all threads and still see only raw values (snapshot semantics). */
-        for (int pass = 0; pass < 4; pass++) {
+           invocations of the columns x-1 and x+1 read it (row 0 of column x also reads row HEIGHT-1 of column x-1:
+           `y - 1 > 0` on a uint).  Columns are therefore run in three interleaved passes -- columns 3 apart do not
+           read each other; inside a column the rows run one after the other -- so the passes can use all threads
+           and still see only raw values (snapshot semantics). */
+        for (int pass = 0; pass < 3; pass++) {
 #pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
-            for (int y = y0; y < y1; y++) {
-                if (pass == 3 ? (y != 0) : (y == 0 || y % 3 != pass)) continue;
-                for (int x = 0; x < WIDTH; x++) {
+            for (int x = pass; x < WIDTH; x += 3)
+                for (int y = y0; y < y1; y++) {
                     glsl::vec4 raw = sh->pixels[frame][x][y];
                     glsl::shader_base::gl_GlobalInvocationID = glsl::uvec3((unsigned)x, (unsigned)y, 0u);
                     sh->main();
                     sh->pixels[frame][x][y] = raw;
                 }
-            }
         }
 #pragma omp parallel for schedule(static) num_threads(nthreads)
-        for (int y = y0; y < y1; y++)
-            for (int x = 0; x < WIDTH; x++)
+        for (int x = 0; x < WIDTH; x++)
+            for (int y = y0; y < y1; y++)
                 sh->pixels[frame][x][y] = c->image[(size_t)y * WIDTH + x];
         return 0;
     }

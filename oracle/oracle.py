@@ -82,8 +82,7 @@ class Oracle:
             raise MemoryError("rto_create failed")
         if phong_gbuffer:
             self.L.rto_set_phong_gbuffer(self.h, 1)
-        if threads:
-            self.L.rto_set_threads(self.h, threads)
+        self.L.rto_set_threads(self.h, threads if threads else len(os.sched_getaffinity(0)))
         self.W, self.H, self.AA, self.NF = width, height, aa, num_frames
 
     def close(self):
@@ -95,6 +94,11 @@ class Oracle:
 
     def threads(self):
         return self.L.rto_set_threads(self.h, 0)
+
+    def set_threads(self, n):
+        """an explicit thread count (OMP_NUM_THREADS is 1 under torch.distributed.run; pass
+        len(os.sched_getaffinity(0)) to use the host's cores all the same)"""
+        return self.L.rto_set_threads(self.h, int(n))
 
     def set_scene(self, shapes, n):
         s = np.ascontiguousarray(shapes, dtype=np.float32)
@@ -189,7 +193,8 @@ class GlslRef:
         assert (L.glslref_width(), L.glslref_height(), L.glslref_aa()) == (width, height, aa)
         self.W, self.H, self.AA, self.NF = width, height, aa, L.glslref_num_frames()
         self.h = L.glslref_create()
-        self.nthreads = L.glslref_max_threads()
+        # not omp_get_max_threads(): OMP_NUM_THREADS is 1 under torch.distributed.run
+        self.nthreads = len(os.sched_getaffinity(0))
         # header = 7 uniform vec4 + 10x5 shape vec4 + 2*AA rand vec4 (src/main.cpp:52-79)
         nhead = (7 + 50 + 2 * aa) * 4
         base = L.glslref_ssbo(self.h)

@@ -528,9 +528,11 @@ int rto_render_rows(rto_ctx *c, int mode, const float *uniforms, const float *ra
     {
         rto_stats st;
         memset(&st, 0, sizeof st);
-#pragma omp for schedule(dynamic, 1)
-        for (int y = y0; y < y1; y++) {
-            for (int x = 0; x < W; x++) {
+        /* columns outermost: the struct is x-major (pixels[f][x][y], src/main.cpp:81-84), so a thread walks
+           contiguous memory; the pixels are independent, the order does not change a bit */
+#pragma omp for schedule(dynamic, 4)
+        for (int x = 0; x < W; x++) {
+            for (int y = y0; y < y1; y++) {
                 if (mode == 1) ao_pixel(c, (unsigned)x, (unsigned)y, 0, &st);
                 else if (mode == 2) ao_pixel(c, (unsigned)x, (unsigned)y, 1, &st);
                 else if (mode == 3) phong_pixel(c, (unsigned)x, (unsigned)y, &st);
@@ -643,23 +645,34 @@ int rto_postprocess_rows(rto_ctx *c, int y0, int y1)
 {
     const int W = c->cfg.width, H = c->cfg.height;
     rtr_v4 *slotp = &c->base[c->pixels_off + (long long)c->slot * c->npix];
-    memcpy(c->raw, slotp, (size_t)c->npix * sizeof(rtr_v4));
+    if (y0 <= 0 && y1 >= H) {
+        memcpy(c->raw, slotp, (size_t)c->npix * sizeof(rtr_v4));
+    } else {
+        /* a row range only reads the raw rows y0-1 .. y1 (and row H-1 from row 0: `y - 1 > 0` on a uint):
+           snapshot those instead of the whole slot (x-major layout: one run of rows per column) */
+        const int ylo = y0 > 0 ? y0 - 1 : 0, yhi = y1 < H ? y1 + 1 : H;
+        for (int x = 0; x < W; x++) {
+            memcpy(&c->raw[(long long)x * H + ylo], &slotp[(long long)x * H + ylo], (size_t)(yhi - ylo) * sizeof(rtr_v4));
+            if (y0 <= 0) c->raw[(long long)x * H + H - 1] = slotp[(long long)x * H + H - 1];
+        }
+    }
     rto_stats total;
     memset(&total, 0, sizeof total);
 #pragma omp parallel num_threads(c->nthreads)
     {
         rto_stats st;
         memset(&st, 0, sizeof st);
-#pragma omp for schedule(dynamic, 1)
-        for (int y = y0; y < y1; y++)
-            for (int x = 0; x < W; x++) pp_pixel(c, (unsigned)x, (unsigned)y, &st);
+#pragma omp for schedule(dynamic, 4)
+        for (int x = 0; x < W; x++)
+            for (int y = y0; y < y1; y++) pp_pixel(c, (unsigned)x, (unsigned)y, &st);
 #pragma omp critical
         stats_add(&total, &st);
     }
     total.pixels = 0;
     stats_add(&c->stats, &total);
-    for (int y = y0; y < y1; y++)
-        for (int x = 0; x < W; x++) slotp[(long long)x * H + y] = c->image[(long long)y * W + x];
+#pragma omp parallel for schedule(static) num_threads(c->nthreads)
+    for (int x = 0; x < W; x++)
+        for (int y = y0; y < y1; y++) slotp[(long long)x * H + y] = c->image[(long long)y * W + x];
     return 0;
 }
 

@@ -42,9 +42,9 @@ EXPORTS = (
     "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_last_error", "rt_set_stream",
     "rt_synchronize", "rt_set_timing", "rt_upload_scene", "rt_render_frame", "rt_halo_pack", "rt_get_halo",
     "rt_postprocess", "rt_download", "rt_upload", "rt_download_async", "rt_download_rgba8_async", "rt_download_color_overlapped", "rt_readback_wait", "rt_device_ptr", "rt_get_stats",
-    "rt_reset_stats", "rt_debug_eval_math", "rt_measure_fp32_peak",
+    "rt_reset_stats", "rt_reset_ring", "rt_debug_eval_math", "rt_measure_fp32_peak",
     "rt_set_frame_target", "rt_set_frame_targets", "rt_frame_download_overlapped", "rt_stream_wait_readback", "rt_band_to_frame_overlapped", "rt_frame_create", "rt_frame_destroy", "rt_peer_export", "rt_peer_import",
-    "rt_peer_release", "rt_mailbox_create", "rt_mailbox_destroy", "rt_link_peers", "rt_fence", "rt_fence_status",
+    "rt_peer_release", "rt_mailbox_create", "rt_mailbox_destroy", "rt_link_peers", "rt_fence", "rt_fence_async", "rt_fence_join", "rt_fence_status",
 )
 
 _lib = None
@@ -83,6 +83,7 @@ def load():
     L.rt_device_ptr.argtypes = [vp, i32, i32, C.POINTER(vp), C.POINTER(sz)]
     L.rt_get_stats.argtypes = [vp, C.POINTER(rt_stats)]
     L.rt_reset_stats.argtypes = [vp]
+    L.rt_reset_ring.argtypes = [vp]
     L.rt_debug_eval_math.argtypes = [i32, i32, vp, vp, vp, sz]
     L.rt_measure_fp32_peak.argtypes = [i32, C.POINTER(C.c_double)]
     L.rt_set_frame_target.argtypes = [vp, vp]
@@ -99,6 +100,8 @@ def load():
     L.rt_mailbox_destroy.argtypes = [i32, vp]
     L.rt_link_peers.argtypes = [vp, i32, i32, C.POINTER(vp), vp, vp]
     L.rt_fence.argtypes = [vp]
+    L.rt_fence_async.argtypes = [vp]
+    L.rt_fence_join.argtypes = [vp, i32]
     L.rt_fence_status.argtypes = [vp, C.POINTER(i32)]
     _lib = L
     return L

@@ -138,6 +138,13 @@ class RayTracer:
     def fence(self):
         self._check(self.lib.rt_fence(self.h))
 
+    def fence_async(self):
+        """rt_fence_async: the barrier on an internal stream, behind the work issued so far"""
+        self._check(self.lib.rt_fence_async(self.h))
+
+    def fence_join(self, block_host: bool = False):
+        self._check(self.lib.rt_fence_join(self.h, int(block_host)))
+
     def fence_timed_out(self) -> bool:
         v = C.c_int(0)
         self._check(self.lib.rt_fence_status(self.h, C.byref(v)))
@@ -207,6 +214,10 @@ class RayTracer:
 
     def reset_stats(self):
         self._check(self.lib.rt_reset_stats(self.h))
+
+    def reset_ring(self):
+        """rt_reset_ring: ring, raw plane and hit indices back to the all-zero state of a new context"""
+        self._check(self.lib.rt_reset_ring(self.h))
 
 
 class PeerMem:

@@ -261,15 +261,26 @@ class DirectGather:
     def halo_direct(self) -> bool:
         return self.fence_kind == "flags"
 
-    def fence(self):
+    def fence(self, background: bool = False):
+        """Close the frames issued so far: after it, every rank's kernels and band copies of those frames have
+        landed in the frame images.  ``background`` (fence="flags" only): rt_fence_async -- the barrier runs on
+        the library's fence stream and the rank's own stream goes straight on to the next frame; ``join()`` waits
+        for the newest one."""
         import torch.distributed as dist
 
         if self.tracer is not None:
             self.tracer.stream_wait_readback()   # copies this rank still has in flight belong to the fenced frame
         if self.fence_kind == "flags":
-            self.tracer.fence()
+            if background:
+                self.tracer.fence_async()
+            else:
+                self.tracer.fence()
         elif self.world > 1:
             dist.all_reduce(self.token, group=self.group)
+
+    def join(self, block_host: bool = False):
+        if self.fence_kind == "flags":
+            self.tracer.fence_join(block_host)
 
     def frame(self, k: int):
         """float32 tensor [H*W*4] of the image frame k was gathered into: the whole frame on rank 0
@@ -304,6 +315,10 @@ class BandedRenderer:
         self.bands, self.rank, self.world, self.group = bands, rank, world, group
         self.direct, self.frame_k = direct, 0
         self._copy, self._copy_pending = False, False
+        # how gather_start closes a frame whose bands the kernels store into the frame images:
+        # "stream" = rt_fence on the rank's stream (the frame is complete when the stream gets there);
+        # "background" = rt_fence_async, nothing on the rank's stream waits (a consumer joins the fence);
+        self.frame_fence = "stream"
 
     def _post(self, mode: int) -> bool:
         """the frame is finished by the post-processing pass (mode 1; modes 3/4 under FLAG_PHONG_POSTPROCESS)"""
@@ -345,9 +360,9 @@ class BandedRenderer:
         if self._post(mode):
             if self.world > 1:
                 self.e.halo_pack()
-                if self.direct is not None and self.direct.halo_direct:
-                    self.direct.fence()     # the pack kernels stored into the neighbours' halo rows
-                else:
+                # linked bands: the pack kernel stores into the neighbours' halo rows and raises their flags, the
+                # edge rows of the post-processing kernel wait for this band's flags -- no call in between
+                if not (self.direct is not None and self.direct.halo_direct):
                     self.exchange_halo()
             self.e.postprocess()
 
@@ -361,12 +376,15 @@ class BandedRenderer:
         if self.direct is not None:
             if self._copy:
                 # copy engine, behind the post-processing kernel and under the next frame's trace kernel; the
-                # next fence on this stream (the next frame's halo fence) waits for it and closes the frame
+                # next fence on this stream (a single-pass frame's, or gather_flush) waits for it and closes the frame
                 self.e.band_to_frame(slot, self.direct.target(self.frame_k))
                 self._copy_pending = True
             else:
                 # the bands are already in (or on their way into) the image(s) of frame_k: fence only
-                self.direct.fence()
+                if self.frame_fence == "background" and self.direct.halo_direct:
+                    self.direct.fence(background=True)
+                else:
+                    self.direct.fence()
                 self._copy_pending = False
             self.frame_k += 1
             return []
@@ -391,6 +409,8 @@ class BandedRenderer:
         if self.direct is not None and self._copy_pending:
             self.direct.fence()
             self._copy_pending = False
+        if self.direct is not None and self.frame_fence == "background":
+            self.direct.join()
 
     @staticmethod
     def gather_finish(works):

@@ -29,8 +29,11 @@ struct rt_ctx {
     float *ring_depth_w = nullptr;
     float4 *raw = nullptr; // mode-1 trace output of the current frame
     int *hit = nullptr;
-    void *halo[4] = { nullptr, nullptr, nullptr, nullptr }; // send_lo, send_hi, recv_lo, recv_hi
-    void *staging = nullptr; // npix * 16 bytes, layout conversions
+    void *halo[4] = { nullptr, nullptr, nullptr, nullptr }; // send_lo, send_hi, recv_lo[2], recv_hi[2] (two rows each: frame parity of linked bands)
+    void *staging = nullptr; // npix * 16 bytes, layout conversions of rt_download / rt_upload (synchronous users only)
+    uchar4 *rgba8 = nullptr; // 2 x npix 8-bit pixels, rt_download_rgba8_async (allocated on first use)
+    unsigned *pack_count = nullptr; // block counter of the pack kernel (linked bands)
+    unsigned long long halo_seq = 0; // mode-1 frames packed so far by linked bands (the value the halo flags carry)
     unsigned long long *stats = nullptr;
     float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
     float4 sky_bg{};
@@ -47,6 +50,9 @@ struct rt_ctx {
     PeerBoxes peers{};           // rt_link_peers
     int link_rank = -1, link_world = 0;
     unsigned long long fence_epoch = 0;
+    cudaStream_t fence_stream = nullptr;  // rt_fence_async
+    cudaEvent_t ev_fence_in = nullptr, ev_fence_done = nullptr, ev_stream_switch = nullptr;
+    bool fence_async_pending = false;
     void *peer_next_recv_lo = nullptr, *peer_prev_recv_hi = nullptr;
     bool halo_direct = false;
     // rt_set_frame_targets: whole-frame images (maybe peer memory) and the frame row each one's share ends at
@@ -103,6 +109,11 @@ static void free_all(rt_ctx *c)
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
     cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->sky);
+    cudaFree(c->rgba8); cudaFree(c->pack_count);
+    if (c->ev_fence_in) cudaEventDestroy(c->ev_fence_in);
+    if (c->ev_fence_done) cudaEventDestroy(c->ev_fence_done);
+    if (c->ev_stream_switch) cudaEventDestroy(c->ev_stream_switch);
+    if (c->fence_stream) cudaStreamDestroy(c->fence_stream);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
@@ -155,6 +166,10 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     };
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->fence_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fence_in, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fence_done, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_stream_switch, cudaEventDisableTiming);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&c->ev_quant[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming);
@@ -179,7 +194,8 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
             return RT_EINVAL;
         }
     }
-    for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width));
+    for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width) * (i >= 2 ? 2 : 1));
+    alloc0((void **)&c->pack_count, sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
     for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -200,7 +216,12 @@ int rt_set_stream(rt_ctx *c, void *cuda_stream)
 {
     if (!c) return RT_EINVAL;
     cudaStream_t ns = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
-    if (ns != c->stream) c->sky_valid = false; // rt_sky_gamma_kernel was ordered on the old stream
+    if (ns != c->stream) {
+        // what is still pending on the old stream (kernels, the sky constants) stays ahead of the new one
+        CU(c, cudaSetDevice(c->cfg.device));
+        CU(c, cudaEventRecord(c->ev_stream_switch, c->stream));
+        CU(c, cudaStreamWaitEvent(ns, c->ev_stream_switch, 0));
+    }
     c->stream = ns;
     return RT_OK;
 }
@@ -211,6 +232,8 @@ int rt_synchronize(rt_ctx *c)
     CU(c, cudaSetDevice(c->cfg.device));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaStreamSynchronize(c->copy_stream)); // outstanding rt_download_rgba8_async read-backs
+    CU(c, cudaStreamSynchronize(c->fence_stream));
+    c->fence_async_pending = false;
     c->copy_pending[0] = c->copy_pending[1] = false;
     return RT_OK;
 }
@@ -380,10 +403,18 @@ static void fill_post(rt_ctx *c, PostParams &q)
     q.raw = c->raw; q.ring_color = c->ring_color; q.ring_normal = c->ring_normal;
     q.ring_depth_xy = c->ring_depth_xy; q.ring_depth_w = c->ring_depth_w;
     q.send_lo = c->halo[0]; q.send_hi = c->halo[1];
-    q.halo_lo = c->halo[2]; q.halo_hi = c->halo[3];
+    // linked bands alternate between two receive rows: frame k+1's rows may arrive while frame k's are still read
+    const size_t par = c->halo_direct ? (size_t)(c->halo_seq & 1ull) * halo_row_bytes(c->cfg.width) : 0;
+    q.halo_lo = (char *)c->halo[2] + par; q.halo_hi = (char *)c->halo[3] + par;
     q.rand_last = c->rand_last;
     q.gather = c->gather_post;
     q.stats = c->stats;
+    q.seq = c->halo_seq;
+    if (c->halo_direct) {
+        unsigned long long *own = c->peers.box[c->link_rank];
+        q.flag_lo = own + MB_HALO_LO; q.flag_hi = own + MB_HALO_HI; q.status = own + MB_STATUS;
+        q.wait_halo = 1;
+    }
 }
 
 int rt_halo_pack(rt_ctx *c)
@@ -392,15 +423,22 @@ int rt_halo_pack(rt_ctx *c)
     if (!c->frame_pending_post) return fail(c, RT_ESTATE, "rt_halo_pack: no mode-1 frame waiting for post-processing");
     CU(c, cudaSetDevice(c->cfg.device));
     PostParams q{};
+    if (c->halo_direct) c->halo_seq++;
     fill_post(c, q);
     if (c->cfg.band_count == 1) {
         // the wrapped row goes straight into this band's own lower halo
         q.send_lo = nullptr;
         q.send_hi = c->halo[2];
     } else if (c->halo_direct) {
-        // rt_link_peers: the edge rows go straight into the neighbours' halo rows over NVLink
-        q.send_lo = c->peer_prev_recv_hi; // null on band 0: nobody below
-        q.send_hi = c->peer_next_recv_lo;
+        // rt_link_peers: the edge rows go straight into the neighbours' halo rows (of this frame's parity) over
+        // NVLink, followed by the frame's sequence number in the neighbours' flags
+        const size_t par = (size_t)(c->halo_seq & 1ull) * halo_row_bytes(c->cfg.width);
+        const int r = c->link_rank, n = c->link_world;
+        q.send_lo = c->peer_prev_recv_hi ? (char *)c->peer_prev_recv_hi + par : nullptr; // null on band 0: nobody below
+        q.send_hi = (char *)c->peer_next_recv_lo + par;
+        q.sig_next_lo = c->peers.box[(r + 1) % n] + MB_HALO_LO;
+        q.sig_prev_hi = (r > 0) ? c->peers.box[r - 1] + MB_HALO_HI : nullptr;
+        q.pack_count = c->pack_count;
     }
     CU(c, launch_halo_pack(q, c->stream));
     c->halo_packed = true;
@@ -482,6 +520,10 @@ int rt_link_peers(rt_ctx *c, int rank, int world, void *const *mailboxes, void *
     // same rank keeps counting instead of starting below the peers' expectations)
     CU(c, cudaSetDevice(c->cfg.device));
     CU(c, cudaMemcpy(&c->fence_epoch, c->peers.box[rank] + rank, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    // the halo flags likewise: every rank has packed the same number of frames when contexts are (re)linked
+    unsigned long long fl[2] = { 0, 0 };
+    CU(c, cudaMemcpy(fl, c->peers.box[rank] + MB_HALO_LO, sizeof fl, cudaMemcpyDeviceToHost));
+    c->halo_seq = fl[0] > fl[1] ? fl[0] : fl[1];
     return RT_OK;
 }
 
@@ -494,14 +536,38 @@ int rt_fence(rt_ctx *c)
     return RT_OK;
 }
 
+int rt_fence_async(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence_async: call rt_link_peers first");
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, cudaEventRecord(c->ev_fence_in, c->stream));
+    CU(c, cudaStreamWaitEvent(c->fence_stream, c->ev_fence_in, 0));
+    CU(c, launch_fence(c->peers, c->link_rank, c->link_world, ++c->fence_epoch, c->fence_stream));
+    CU(c, cudaEventRecord(c->ev_fence_done, c->fence_stream));
+    c->fence_async_pending = true;
+    return RT_OK;
+}
+
+int rt_fence_join(rt_ctx *c, int block_host)
+{
+    if (!c) return RT_EINVAL;
+    if (!c->fence_async_pending) return RT_OK;
+    CU(c, cudaSetDevice(c->cfg.device));
+    if (block_host) { CU(c, cudaEventSynchronize(c->ev_fence_done)); c->fence_async_pending = false; }
+    else CU(c, cudaStreamWaitEvent(c->stream, c->ev_fence_done, 0));
+    return RT_OK;
+}
+
 int rt_fence_status(rt_ctx *c, int *timed_out)
 {
     if (!c || !timed_out) return RT_EINVAL;
     if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence_status: call rt_link_peers first");
     CU(c, cudaSetDevice(c->cfg.device));
     CU(c, cudaStreamSynchronize(c->stream));
+    CU(c, cudaStreamSynchronize(c->fence_stream));
     unsigned long long st = 0;
-    CU(c, cudaMemcpy(&st, c->peers.box[c->link_rank] + RT_MAX_RANKS, sizeof st, cudaMemcpyDeviceToHost));
+    CU(c, cudaMemcpy(&st, c->peers.box[c->link_rank] + MB_STATUS, sizeof st, cudaMemcpyDeviceToHost));
     *timed_out = st != 0;
     return RT_OK;
 }
@@ -682,12 +748,14 @@ int rt_download_rgba8_async(rt_ctx *c, int slot, void *pinned_host, size_t bytes
     if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
     if (bytes != c->npix * 4) return fail(c, RT_EINVAL, "rt_download_rgba8_async: expected %zu bytes, got %zu", c->npix * 4, bytes);
     CU(c, cudaSetDevice(c->cfg.device));
-    // Two alternating halves of the staging plane.  The conversion runs on the context's stream (after the
+    // Two alternating halves of a device buffer of its own (rt_download / rt_upload use `staging`).  The conversion runs on the context's stream (after the
     // frame's kernels); the PCIe copy runs on an internal copy stream behind an event, so it overlaps the next
     // frame's kernels; a half is converted into again only after the copy that last read it has finished.
+    const size_t half = (c->npix + 3) & ~(size_t)3; // 16-byte aligned halves
+    if (!c->rgba8) CU(c, cudaMalloc((void **)&c->rgba8, 2 * half * sizeof(uchar4)));
     const int h = c->rgba8_flip;
     c->rgba8_flip ^= 1;
-    uchar4 *dst = (uchar4 *)c->staging + (size_t)h * ((c->npix + 3) & ~(size_t)3); // 16-byte aligned halves
+    uchar4 *dst = c->rgba8 + (size_t)h * half;
     if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));
     CU(c, launch_quantize_rgba8(c->ring_color + (size_t)slot * c->npix, dst, c->npix, c->stream));
     CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
@@ -806,6 +874,21 @@ int rt_upload(rt_ctx *c, int buffer, int slot, int layout, const void *host, siz
     cudaFree(tmp);
     if (rc != RT_OK) return rc;
     CU(c, e);
+    return RT_OK;
+}
+
+int rt_reset_ring(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    CU(c, cudaSetDevice(c->cfg.device));
+    const size_t ring = c->npix * c->cfg.num_frames;
+    CU(c, cudaMemsetAsync(c->ring_color, 0, ring * sizeof(float4), c->stream));
+    CU(c, cudaMemsetAsync(c->ring_normal, 0, ring * sizeof(float4), c->stream));
+    CU(c, cudaMemsetAsync(c->ring_depth_xy, 0, ring * sizeof(float2), c->stream));
+    CU(c, cudaMemsetAsync(c->ring_depth_w, 0, ring * sizeof(float), c->stream));
+    CU(c, cudaMemsetAsync(c->raw, 0, c->npix * sizeof(float4), c->stream));
+    CU(c, cudaMemsetAsync(c->hit, 0, c->npix * sizeof(int), c->stream));
+    c->frame_pending_post = false;
     return RT_OK;
 }
 

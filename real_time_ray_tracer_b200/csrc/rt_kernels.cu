@@ -215,10 +215,30 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
 // shader's `[f][x][y - 1]` with y = 0 (uint wrap) actually addresses: flat index (f*W + x)*H - 1,
 // i.e. (x-1, H-1) of the same slot, and for x = 0 the last element of the previous slot / array
 // (aop_postprocessing.glsl:150-159 over the layout of src/main.cpp:79-84).
-__global__ void rt_halo_pack_kernel(PostParams q)
+__device__ __forceinline__ void halo_pack_rows(const PostParams &q, int x);
+
+// Linked bands: after the rows, the flags.  Every block fences its stores (system scope: they went to peer
+// memory) and counts itself; the last one publishes the frame's sequence number in the neighbours' flags, which
+// the edge rows of THEIR post-processing kernels are waiting for (halo_wait below).  The counter re-arms itself.
+__global__ void rt_halo_pack_kernel(const __grid_constant__ PostParams q)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    if (x >= q.W) return;
+    if (x < q.W) halo_pack_rows(q, x);
+    if (!q.pack_count) return;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(q.pack_count, 1u) == gridDim.x - 1) {
+            *q.pack_count = 0u;
+            __threadfence_system();
+            if (q.sig_next_lo) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(q.sig_next_lo), "l"(q.seq) : "memory");
+            if (q.sig_prev_hi) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(q.sig_prev_hi), "l"(q.seq) : "memory");
+        }
+    }
+}
+
+__device__ __forceinline__ void halo_pack_rows(const PostParams &q, int x)
+{
     const size_t plane = (size_t)q.rows * q.W;
     const float4 *nslot = q.ring_normal + (size_t)q.slot * plane;
     const float2 *dslot = q.ring_depth_xy + (size_t)q.slot * plane;
@@ -259,6 +279,35 @@ __global__ void rt_halo_pack_kernel(PostParams q)
 
 struct NbRec { float4 color, normal; float2 depth; };
 
+// a warp whose row reads a halo row of a linked band waits for the neighbour's flag (see rt_halo_pack_kernel);
+// the neighbour published it before its own post-processing kernel of this frame, so the wait cannot cycle
+__device__ __forceinline__ void halo_wait(const unsigned long long *flag, unsigned long long seq, unsigned long long *status)
+{
+    if ((threadIdx.x & 31) == 0) {
+        unsigned long long seen = 0, t0 = 0, now = 0;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flag) : "memory");
+        if (seen < seq) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            for (;;) {
+                __nanosleep(100);
+                asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flag) : "memory");
+                if (seen >= seq) break;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (now - t0 > 10000000000ull) { *status = 1ull; break; }
+            }
+        }
+    }
+    __syncwarp();
+}
+// halo records of a linked band were written by another GPU while this kernel may already have been running:
+// read them past L1 (the flag's acquire orders the loads, ld.cv keeps a stale line out of the way)
+__device__ __forceinline__ void halo_read(const PostParams &q, const void *row, int x, NbRec &r)
+{
+    HaloRow h = halo_row_view(const_cast<void *>(row), q.W);
+    if (q.wait_halo) { r.color = __ldcv(h.color + x); r.normal = __ldcv(h.normal + x); r.depth = __ldcv(h.depth + x); }
+    else { r.color = h.color[x]; r.normal = h.normal[x]; r.depth = h.depth[x]; }
+}
+
 __device__ __forceinline__ float nb_weight(float4 nn, float nd, float nb, const NbRec &r)
 {
     if (r.normal.w < 0.001f) return 1.0f;
@@ -290,9 +339,18 @@ constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 4;
 __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_postprocess_kernel(const __grid_constant__ PostParams q)
 {
     const int x = blockIdx.x * PP_BLOCK_X + threadIdx.x;
-    const int yl = blockIdx.y * PP_BLOCK_Y + threadIdx.y;
+    // linked bands: the row blocks that read halo rows (the first and the last) are scheduled last, so that the
+    // neighbours' rows have normally arrived by the time they look at the flags
+    int by = blockIdx.y;
+    if (q.wait_halo && gridDim.y >= 3) by = (by + 2 < (int)gridDim.y) ? by + 1 : (by + 2 == (int)gridDim.y ? 0 : by);
+    const int yl = by * PP_BLOCK_Y + threadIdx.y;
     const bool active = (x < q.W) && (yl < q.rows);
     unsigned n_nonbg = 0, n_eval = 0, n_acc = 0;
+    if (q.wait_halo && yl < q.rows) {   // warp-uniform: a warp is 32 consecutive x of one row
+        const int y = q.y0 + yl;
+        if (yl == 0 && ((q.edge_mode == RT_EDGE_FLAT32) ? (y != 1) : (y > 0))) halo_wait(q.flag_lo, q.seq, q.status);
+        if (yl == q.rows - 1 && y + 1 < q.H) halo_wait(q.flag_hi, q.seq, q.status);
+    }
     if (active) {
         const int y = q.y0 + yl;
         const size_t plane = (size_t)q.rows * q.W;
@@ -337,8 +395,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
                 if (yl + 1 < q.rows) {
                     U.color = q.raw[pix + q.W]; U.normal = nslot[pix + q.W]; U.depth = dslot[pix + q.W];
                 } else {
-                    HaloRow h = halo_row_view(q.halo_hi, q.W);
-                    U.color = h.color[x]; U.normal = h.normal[x]; U.depth = h.depth[x];
+                    halo_read(q, q.halo_hi, x, U);
                 }
                 u = nb_weight(nn, new_depth, new_bounces, U);
             }
@@ -348,8 +405,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
                 if (yl > 0) {
                     D.color = q.raw[pix - q.W]; D.normal = nslot[pix - q.W]; D.depth = dslot[pix - q.W];
                 } else {
-                    HaloRow h = halo_row_view(q.halo_lo, q.W);
-                    D.color = h.color[x]; D.normal = h.normal[x]; D.depth = h.depth[x];
+                    halo_read(q, q.halo_lo, x, D);
                 }
                 d = nb_weight(nn, new_depth, new_bounces, D);
             }
@@ -466,7 +522,7 @@ __global__ void rt_fence_kernel(const __grid_constant__ PeerBoxes peers, int ran
         if (seen >= epoch) break;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
         if (now - t0 > 10000000000ull) {
-            peers.box[rank][RT_MAX_RANKS] = 1ull;
+            peers.box[rank][MB_STATUS] = 1ull;
             break;
         }
         __nanosleep(64);

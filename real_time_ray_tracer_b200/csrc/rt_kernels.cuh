@@ -143,10 +143,23 @@ struct PostParams {
     GatherTargets gather;      // like TraceOut::gather, for the post-processed colour of mode 1
     float4 rand_last;          // rand_buffer[2*AA-1]: what pixels[0][0][-1] aliases (FLAT32)
     unsigned long long *stats;
+    // Linked bands (rt_link_peers): the halo exchange lives inside the two kernels.  The pack kernel stores the
+    // edge rows into the neighbours' receive rows of parity seq & 1 and then publishes `seq` in the neighbours'
+    // flags (sig_*: peer memory; pack_count finds the last block).  The post-processing kernel's edge-row warps
+    // wait (wait_halo) until their own flags (flag_*) show `seq` before they read halo_lo / halo_hi.
+    unsigned long long *sig_next_lo, *sig_prev_hi;
+    unsigned *pack_count;
+    const unsigned long long *flag_lo, *flag_hi;
+    unsigned long long *status;    // set to 1 when a wait gave up (10 s)
+    unsigned long long seq;
+    int wait_halo;
 };
 
-// mailboxes of rt_fence: RT_MAX_RANKS 64-bit epochs (slot j = last epoch signalled by rank j) + a status word
-constexpr int MAILBOX_WORDS = RT_MAX_RANKS + 1;
+// mailboxes of rt_fence: RT_MAX_RANKS 64-bit epochs (slot j = last epoch signalled by rank j), a status word,
+// and the two halo flags of linked bands: the sequence number of the last mode-1 frame whose lower / upper halo
+// row the neighbouring band has delivered
+constexpr int MB_STATUS = RT_MAX_RANKS, MB_HALO_LO = RT_MAX_RANKS + 1, MB_HALO_HI = RT_MAX_RANKS + 2;
+constexpr int MAILBOX_WORDS = RT_MAX_RANKS + 3;
 struct PeerBoxes { unsigned long long *box[RT_MAX_RANKS]; };
 cudaError_t launch_fence(const PeerBoxes &peers, int rank, int world, unsigned long long epoch, cudaStream_t s);
 

@@ -207,8 +207,11 @@ class _FakeDirect:
     def targets(self, k):
         return [2000 + k % 2, 3000 + k % 2], [5, 10]
 
-    def fence(self):
-        self.log.append(("fence",))
+    def fence(self, background=False):
+        self.log.append(("fence_bg" if background else "fence",))
+
+    def join(self, block_host=False):
+        self.log.append(("join",))
 
 
 def test_banded_renderer_call_sequences():
@@ -221,34 +224,42 @@ def test_banded_renderer_call_sequences():
     # mode 2, kernel stores: target, render, fence
     br.render(2, None, None); br.gather_start(0)
     assert [c[0] for c in log] == ["set_frame_target", "render_frame", "fence"] and log[0] == ("set_frame_target", 1000)
-    # mode 1, kernel stores: render, pack, halo fence, post-process, frame fence
+    # mode 1, kernel stores: render, pack (halo rows + flags travel inside the kernels), post-process, frame fence
     del log[:]
     br.render(1, None, None); br.gather_start(1)
-    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "halo_pack", "fence", "postprocess", "fence"]
+    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "halo_pack", "postprocess", "fence"]
     assert log[0] == ("set_frame_target", 1001) and br.frame_k == 2
-    # copy gather: no target, one fence per frame, the band copy after the pass, flush closes the last frame
+    # copy gather: no target, no fence per frame, the band copy after the pass, flush closes the frames
     del log[:]
     d.mode1_gather = "copy"
     br.render(1, None, None); br.gather_start(2)
     br.render(3, None, None); br.gather_start(3)     # mode 3 under FLAG_PHONG_POSTPROCESS behaves like mode 1
     br.gather_flush(); br.gather_flush()
-    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "halo_pack", "fence", "postprocess", "band_to_frame",
-                                   "set_frame_target", "render_frame", "halo_pack", "fence", "postprocess", "band_to_frame",
+    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "halo_pack", "postprocess", "band_to_frame",
+                                   "set_frame_target", "render_frame", "halo_pack", "postprocess", "band_to_frame",
                                    "fence"]
-    assert log[0] == ("set_frame_target", None) and log[5] == ("band_to_frame", 2, 1000) and log[11] == ("band_to_frame", 3, 1001)
+    assert log[0] == ("set_frame_target", None) and log[4] == ("band_to_frame", 2, 1000) and log[9] == ("band_to_frame", 3, 1001)
     # a single-pass frame after a copied one: its fence closes both, nothing left to flush
     del log[:]
     br.render(1, None, None); br.gather_start(4)
     br.render(2, None, None); br.gather_start(5)
     br.gather_flush()
-    assert [c[0] for c in log][-3:] == ["set_frame_target", "render_frame", "fence"] and [c[0] for c in log].count("fence") == 2
+    assert [c[0] for c in log][-3:] == ["set_frame_target", "render_frame", "fence"] and [c[0] for c in log].count("fence") == 1
+    # background fences: the rank's stream never waits; flush joins the newest one
+    del log[:]
+    br.frame_fence = "background"
+    br.render(2, None, None); br.gather_start(6)
+    br.render(2, None, None); br.gather_start(7)
+    br.gather_flush()
+    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "fence_bg", "set_frame_target", "render_frame", "fence_bg", "join"]
+    br.frame_fence = "stream"
     # split row owners: every pixel goes to its owner's image, post-processed frames included (no copy gather)
     del log[:]
     d2 = _FakeDirect(log, owners="rows")
     d2.mode1_gather = "copy"
     br2 = bands.BandedRenderer(eng, 8, 10, [(0, 5), (5, 5)], rank=0, world=2, direct=d2)
     br2.render(1, None, None); br2.gather_start(0)
-    assert [c[0] for c in log] == ["set_frame_targets", "render_frame", "halo_pack", "fence", "postprocess", "fence"]
+    assert [c[0] for c in log] == ["set_frame_targets", "render_frame", "halo_pack", "postprocess", "fence"]
     d2.split = False      # the same images, gathered to rank 0 after all
     del log[:]
     br2.render(2, None, None); br2.gather_start(1)

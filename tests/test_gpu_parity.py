@@ -276,6 +276,66 @@ def test_row_bands_on_one_gpu_equal_the_whole_frame(edge_mode, cuts):
         o.close()
 
 
+@pytest.mark.parametrize("edge_mode", [rtb.EDGE_FLAT32, rtb.EDGE_CLEAN])
+@pytest.mark.parametrize("cuts", [[0, 30, 64], [0, 1, 9, 40, 64], [0, 5, 64]])
+def test_linked_bands_exchange_the_halo_inside_the_kernels(edge_mode, cuts):
+    """rt_link_peers on one device: every band context has its own stream and mailbox, the pack kernel stores the
+    edge rows into the neighbours' receive rows (two per side, alternating with the frame) and raises their flags,
+    and the edge rows of the post-processing kernels wait for the flags.  No copy, no fence, no synchronisation
+    between the bands for 19 frames (ring wrap, both parities, the wrapped row of FLAT32); a stalled band in the
+    middle (its stream blocked by a sleeping kernel for a while) must not change a bit."""
+    import torch
+
+    W, H, AA = 96, 64, 4
+    n = len(cuts) - 1
+    rts = [rtb.RayTracer(W, H, AA, edge_mode=edge_mode, band_y0=cuts[i], band_rows=cuts[i + 1] - cuts[i],
+                         band_index=i, band_count=n) for i in range(n)]
+    boxes = [api.mailbox_create(0) for _ in range(n)]
+    infos = [rt.halo_info() for rt in rts]
+    for i, rt in enumerate(rts):
+        rt.link_peers(i, n, boxes, infos[(i + 1) % n].recv_lo, infos[i - 1].recv_hi if i > 0 else None)
+    sc = Scenario("scene1", keys=("d", "e"))
+    o = orc.Oracle(W, H, AA, edge_mode=edge_mode)
+    o.set_scene(sc.shapes, sc.n)
+    for rt in rts:
+        rt.upload_scene(sc.shapes, sc.n)
+    frames = []
+    side = torch.cuda.Stream()
+    rts[n // 2].set_stream(side.cuda_stream)       # the band that gets stalled
+    for k in range(19):
+        slot, u, rb = sc.next(1, AA)
+        frames.append((slot, u, rb))
+        # issue order rotates so that every band is sometimes the first and sometimes the last to be enqueued
+        order = [(i + k) % n for i in range(n)]
+        if k == 11:
+            with torch.cuda.stream(side):
+                torch.cuda._sleep(20_000_000)      # ~10 ms before its trace: the neighbours' edge rows wait for it
+        for i in order:
+            rts[i].render_frame(1, u, rb)
+            rts[i].halo_pack()
+        if k == 7:
+            with torch.cuda.stream(side):
+                torch.cuda._sleep(20_000_000)      # between pack and pass: the others run a frame ahead meanwhile
+        for i in order:
+            rts[i].postprocess()
+    for rt in rts:
+        rt.synchronize()
+        assert not rt.fence_timed_out()
+    for k, (slot, u, rb) in enumerate(frames):
+        o.render(1, u, rb)
+        o.postprocess()
+        if k >= 19 - 8:    # the ring still holds the last eight frames
+            for buf, which in ((rtb.BUF_COLOR, orc.PIXELS), (rtb.BUF_NORMAL, orc.NORMALS), (rtb.BUF_DEPTH, orc.DEPTH)):
+                got = np.concatenate([rt.download(buf, slot) for rt in rts], axis=0)
+                want = o.get(which, slot)
+                assert same_bits(got, want), f"frame {k} buffer {buf}: {diff_report(got, want)}"
+    for rt in rts:
+        rt.close()
+    for b in boxes:
+        api.mailbox_destroy(0, b)
+    o.close()
+
+
 @pytest.mark.parametrize("kernel", ["phased", "pulled"])
 def test_frame_target_assembles_the_bands(kernel, monkeypatch):
     """rt_set_frame_target: three band contexts store their final colour straight into one whole-frame image
