@@ -578,8 +578,8 @@ def parity_rows(H: int, plan) -> list:
     want = {0, H - 1}
     for (y0, rows) in plan[1:]:
         want.update((y0 - 1, y0))
-    for i in range(1, 12):
-        want.add((H * i) // 12 + 1)
+    for i in range(1, 20):
+        want.add((H * i) // 20 + 1)
     rows = sorted(y for y in want if 0 <= y < H)
     ranges = []
     for y in rows:
