@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel
 
     // per-warp statistics flush, no block barrier
     const unsigned gw = (blockIdx.x + blockIdx.y * gridDim.x) * (PH_THREADS >> 5) + warp;
-    unsigned long long *st = o.stats + (gw % STAT_STRIPES) * ST_COUNT;
+    unsigned long long *st = o.stats + (gw % STAT_STRIPES) * STAT_STRIDE;
     const unsigned v_non = __reduce_add_sync(0xffffffffu, n_nonterm);
     const unsigned v_term = __reduce_add_sync(0xffffffffu, n_term);
     const unsigned v_pix = __reduce_add_sync(0xffffffffu, active ? 1u : 0u);
@@ -246,6 +246,7 @@ __global__ void rt_sky_gamma_kernel(float4 bg, int AA, float *sky)
     for (int k = 0; k < AA; k++) sum += b;
     sky[c] = sum;
     sky[3 + c] = pow_f32(__fdiv_rn(sum, (float)AA), __fdiv_rn(1.0f, 2.2f));
+    sky[6 + c] = pow_f32(0.0f + b, __fdiv_rn(1.0f, 2.2f));   // modes 3 / 4: result_color = vec4(0) + background
 }
 
 cudaError_t launch_sky_gamma(float4 bg, int AA, float *sky, cudaStream_t s)

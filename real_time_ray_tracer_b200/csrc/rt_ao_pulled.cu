@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
 
     // per-warp statistics flush: the counts are sums, so it does not matter which lane traced which path
     const unsigned gw = (blockIdx.x + blockIdx.y * gridDim.x) * (PU_THREADS >> 5) + warp;
-    unsigned long long *st = o.stats + (gw % STAT_STRIPES) * ST_COUNT;
+    unsigned long long *st = o.stats + (gw % STAT_STRIPES) * STAT_STRIDE;
     const unsigned v_non = __reduce_add_sync(0xffffffffu, n_nonterm);
     const unsigned v_term = __reduce_add_sync(0xffffffffu, n_term);
     const unsigned v_pix = __reduce_add_sync(0xffffffffu, active ? 1u : 0u);

@@ -35,7 +35,7 @@ struct rt_ctx {
     unsigned *pack_count = nullptr; // block counter of the pack kernel (linked bands)
     unsigned long long halo_seq = 0; // mode-1 frames packed so far by linked bands (the value the halo flags carry)
     unsigned long long *stats = nullptr;
-    float *sky = nullptr;     // [6] all-background colour sum + gamma, valid for (sky_bg, cfg.aa)
+    float *sky = nullptr;     // [9] all-background colour sum + its gamma (AO), gamma(background) (modes 3/4); valid for (sky_bg, cfg.aa)
     float4 sky_bg{};
     bool sky_valid = false;
     bool ao_cull = true;      // RT_AO_CULL=0 switches the tile test (tile_candidates) off (A/B)
@@ -183,8 +183,8 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0((void **)&c->raw, c->npix * sizeof(float4));
     alloc0((void **)&c->hit, c->npix * sizeof(int));
     alloc0(&c->staging, c->npix * sizeof(float4));
-    alloc0((void **)&c->stats, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
-    alloc0((void **)&c->sky, 6 * sizeof(float));
+    alloc0((void **)&c->stats, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long));
+    alloc0((void **)&c->sky, 12 * sizeof(float));
     if (const char *k = getenv("RT_AO_CULL")) c->ao_cull = strcmp(k, "0") != 0;
     if (const char *k = getenv("RT_AO_KERNEL")) {
         if (!strcmp(k, "phased")) c->ao_kernel = AO_KERNEL_PHASED;
@@ -196,7 +196,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     }
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width) * (i >= 2 ? 2 : 1));
     alloc0((void **)&c->pack_count, sizeof(unsigned));
-    if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long));
     for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
@@ -374,8 +374,8 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     o.stats = c->stats;
     o.ao_kernel = c->ao_kernel;
     o.sky = c->sky;
-    if (ao && (!c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0)) {
-        // first AO frame, or the background changed (scene toggle, src/main.cpp:229-255)
+    if (!c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0) {
+        // first frame, or the background changed (scene toggle, src/main.cpp:229-255)
         CU(c, launch_sky_gamma(p.bg, p.AA, c->sky, c->stream));
         c->sky_bg = p.bg;
         c->sky_valid = true;
@@ -896,12 +896,12 @@ int rt_get_stats(rt_ctx *c, rt_stats *out)
 {
     if (!c || !out) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
-    const size_t bytes = STAT_STRIPES * ST_COUNT * sizeof(unsigned long long);
+    const size_t bytes = STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long);
     CU(c, cudaMemcpyAsync(c->stats_host, c->stats, bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     uint64_t t[ST_COUNT] = { 0 };
     for (int s = 0; s < STAT_STRIPES; s++)
-        for (int k = 0; k < ST_COUNT; k++) t[k] += c->stats_host[s * ST_COUNT + k];
+        for (int k = 0; k < ST_COUNT; k++) t[k] += c->stats_host[s * STAT_STRIDE + k];
     memset(out, 0, sizeof *out);
     out->rays_closest = t[ST_RAYS_CLOSEST]; out->rays_shadow = t[ST_RAYS_SHADOW];
     out->primary = t[ST_PRIMARY]; out->jittered = t[ST_JITTERED];
@@ -920,7 +920,7 @@ int rt_reset_stats(rt_ctx *c)
 {
     if (!c) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
-    CU(c, cudaMemsetAsync(c->stats, 0, STAT_STRIPES * ST_COUNT * sizeof(unsigned long long), c->stream));
+    CU(c, cudaMemsetAsync(c->stats, 0, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long), c->stream));
     return RT_OK;
 }
 

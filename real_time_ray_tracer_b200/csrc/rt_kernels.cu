@@ -32,7 +32,7 @@ template <int N>
 __device__ __forceinline__ void flush_stats(unsigned long long *stats, const int (&idx)[N], unsigned (&val)[N])
 {
     const unsigned gw = (blockIdx.x + blockIdx.y * gridDim.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    unsigned long long *st = stats + (gw % STAT_STRIPES) * ST_COUNT;
+    unsigned long long *st = stats + (gw % STAT_STRIPES) * STAT_STRIDE;
 #pragma unroll
     for (int k = 0; k < N; k++) {
         unsigned v = __reduce_add_sync(0xffffffffu, val[k]);
@@ -43,20 +43,55 @@ __device__ __forceinline__ void flush_stats(unsigned long long *stats, const int
 // ---------------------------------------------------------------------------------------------
 // Phong (mode 3) and Phong + reflections (mode 4)
 // ---------------------------------------------------------------------------------------------
-// shadow_ray, p_compute.glsl:145-166: FP64 t and FP64 length, every object tested
+// shadow_ray, p_compute.glsl:145-166.  The shader converts every object's t to a double, and for t > 0.0001
+// compares length(dvec3(t * l)) -- a binary64 sqrt of a fused sum of squares -- with the binary32 distance to the
+// light.  Same decisions here with less binary64 work:
+//   * t > 0.0001 on the double is the same comparison on the float (both sides are binary32 values);
+//   * ln = RN64(sqrt(S)) < len  is decided from S and len^2 (exact in binary64: 24 x 24 bits):
+//     S >= len^2 gives sqrt(S) >= len, hence ln >= len; S < len^2 (1 - 2^-50) gives sqrt(S) < len (1 - 2^-51), more
+//     than half a binary64 ulp below len, hence ln < len; only inside that window (a few ulps of binary64 wide:
+//     never seen) the square root itself is taken (out of line);
+//   * the objects are walked as the two lists of FrameParams (the result is an AND over all objects, so neither the
+//     order nor stopping at the first occluder changes it).
+static __device__ __noinline__ bool shadow_len_slow(double S, float len) { return __dsqrt_rn(S) < (double)len; }
+
+__device__ __forceinline__ void shadow_occluder(float t, float3 l, double L2, float len, bool &lit)
+{
+    if (t > 0.0001f) {
+        const double x = __dmul_rn((double)t, (double)l.x), y = __dmul_rn((double)t, (double)l.y), z = __dmul_rn((double)t, (double)l.z);
+        const double S = __fma_rn(z, z, __fma_rn(y, y, __dmul_rn(x, x)));
+        if (S < L2) {
+            if (S >= __dmul_rn(L2, 0x1.ffffffffffffcp-1)) { if (shadow_len_slow(S, len)) lit = false; }   // 1 - 2^-50
+            else lit = false;
+        }
+    }
+}
+
 __device__ __forceinline__ bool shadow_ray(const FrameParams &p, float3 pos)
 {
-    float3 lv = sub3(p.light, pos);
-    float3 l = normalize3(lv);
-    float len = length3(lv);
-    float3 new_pos = add3(pos, scale3(0.01f, l));
+    const float3 lv = sub3(p.light, pos);
+    const float3 l = normalize3(lv);
+    const float len = length3(lv);
+    const float3 new_pos = add3(pos, scale3(0.01f, l));
+    const double L2 = __dmul_rn((double)len, (double)len);
     bool lit = true;
+#pragma unroll
+    for (int i = 0; i < RT_MAX_SHAPES; i++) {
+        if (i >= p.nsph) break;
+        if (lit) {
+            const float4 s = p.sph[i];
+            const float3 pmc = sub3(new_pos, xyz(s));
+            const float b = dot3(l, pmc);
+            shadow_occluder(sphere_roots(b, b * b - dot3(pmc, pmc) + s.w), l, L2, len, lit);
+        }
+    }
 #pragma unroll 1
-    for (int i = 0; i < p.nshapes; i++) {
-        double t = (double)eval_ray(p.shapes[i], new_pos, l);
-        if (lit && t > (double)0.0001f) {
-            double ln = dlength3(__dmul_rn(t, (double)l.x), __dmul_rn(t, (double)l.y), __dmul_rn(t, (double)l.z));
-            if (ln < (double)len) lit = false;
+    for (int j = 0; j < p.npl; j++) {
+        const float3 n = xyz(p.pl_n[j]);
+        const float denom = dot3(n, l);
+        if (lit && !(denom < 0.001f && denom > -0.001f)) {
+            const float num = dot3(n, sub3(xyz(p.pl_p0[j]), new_pos));
+            if (num != 0.0f) shadow_occluder(__fdiv_rn(num, denom), l, L2, len, lit);   // t = +-0 is never > 0.0001
         }
     }
     return lit;
@@ -76,42 +111,69 @@ __device__ __forceinline__ float4 phong_shade(const FrameParams &p, float4 att, 
     return scale4(0.06f, att);
 }
 
-__global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
+// The camera rays of modes 3 and 4 use the tile test of the AO kernel (tile_candidates: the objects a ray of this
+// warp's 8x4 tile can hit at all; the jitter margin it includes is simply slack here) and the per-frame camera
+// constants.  A pixel that misses everything shows gamma(0 + background): three pow() of one fixed value, formed
+// when the background changes (rt_sky_gamma_kernel), not per pixel.
+#ifndef PHONG_TILE
+#define PHONG_TILE 1
+#endif
+struct PhongTile { unsigned cand; int x, yl; };
+__device__ __forceinline__ PhongTile phong_tile(const FrameParams &p)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x0 = blockIdx.x * TILE_W + ((warp & 1) << 3), y0 = blockIdx.y * TILE_H + ((warp >> 1) << 2);
+    PhongTile t;
+#if PHONG_TILE
+    t.cand = tile_candidates(p, ((float)x0 + 3.5f) * p.invW, ((float)(p.y0 + y0) + 1.5f) * p.invH);
+#else
+    t.cand = ((1u << p.nsph) - 1u) | (((1u << p.npl) - 1u) << 16);
+#endif
+    t.x = x0 + (lane & 7);
+    t.yl = y0 + (lane >> 3);
+    return t;
+}
+
+__global__ void __launch_bounds__(TRACE_THREADS, 8) rt_phong_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ float s_sky[3];
     for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
+    if (threadIdx.x < 3) s_sky[threadIdx.x] = o.sky[6 + threadIdx.x];   // gamma(0 + background), rt_sky_gamma_kernel
     __syncthreads();
-    int x, yl;
-    tile_pixel(x, yl);
+    const PhongTile tl = phong_tile(p);
+    const int x = tl.x, yl = tl.yl;
     const bool active = (x < p.W) && (yl < p.rows);
     unsigned n_shadow = 0;
     if (active) {
         const int y = p.y0 + yl;
         const size_t pix = (size_t)yl * p.W + x;
-        float3 dir = primary_dir(p, div_const((float)x, p.fW, p.invW), div_const((float)y, p.fH, p.invH));
-        float t;
-        int ind = closest_hit(p, p.cam, dir, 0.0f, t);
-        float4 col;
+        int ind = -1;
+        float t = -1.0f;
+        float3 dir = p.cam;
+        if (tl.cand) {
+            dir = primary_dir(p, div_const((float)x, p.fW, p.invW), div_const((float)y, p.fH, p.invH));
+            ind = closest_hit_primary_masked(p, dir, 0.0f, t, tl.cand);
+        }
+        float4 c = make_float4(s_sky[0], s_sky[1], s_sky[2], 0.0f);
         float4 g_normal = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        if (ind < 0) {
-            col = p.bg;
-        } else {
+        if (ind >= 0) {
             const DevShape &s = s_shapes[ind];
             float3 curr_pos = add3(p.cam, scale3(t, dir));
             bool lit = shadow_ray(p, curr_pos);
             n_shadow = 1;
             float3 normal = shape_normal(s, curr_pos);
             float4 att = make_float4(s.col.x, s.col.y, s.col.z, 0.0f);
-            col = phong_shade(p, att, curr_pos, dir, normal, lit);
+            float4 col = phong_shade(p, att, curr_pos, dir, normal, lit);
             g_normal = make_float4(normal.x, normal.y, normal.z, 1.0f);
+            // result_color = vec4(0) + phong(dir)
+            c = gamma_correct(0.0f + col.x, 0.0f + col.y, 0.0f + col.z);
         }
         if (p.pad0 & RT_FLAG_PHONG_GBUFFER) {   // extension: the record ao_compute.glsl:222-229,249-253 writes
             o.normal[pix] = g_normal;
             o.depth_xy[pix] = make_float2(ind < 0 ? 0.0f : t, 0.0f);
             o.depth_w[pix] = ind < 0 ? 0.0f : 1.0f;
         }
-        // result_color = vec4(0) + phong(dir)
-        const float4 c = gamma_correct(0.0f + col.x, 0.0f + col.y, 0.0f + col.z);
         o.color[pix] = c;
         gather_store(o.gather, yl, pix, c);
         o.hit[pix] = ind;
@@ -121,37 +183,42 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_phong_kernel(const __grid_co
     flush_stats<5>(o.stats, idx, val);
 }
 
-__global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
+__global__ void __launch_bounds__(TRACE_THREADS, 8) rt_hybrid_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
     __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ float s_sky[3];
     for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
+    if (threadIdx.x < 3) s_sky[threadIdx.x] = o.sky[6 + threadIdx.x];   // gamma(0 + background), rt_sky_gamma_kernel
     __syncthreads();
-    int x, yl;
-    tile_pixel(x, yl);
+    const PhongTile tl = phong_tile(p);
+    const int x = tl.x, yl = tl.yl;
     const bool active = (x < p.W) && (yl < p.rows);
     unsigned n_rays = 0, n_shaded = 0, n_refl = 0;
     if (active) {
         const int y = p.y0 + yl;
         const size_t pix = (size_t)yl * p.W + x;
-        float3 dir = primary_dir(p, div_const((float)x, p.fW, p.invW), div_const((float)y, p.fH, p.invH));
+        float3 dir = p.cam;
         float3 pos = p.cam;
-        float4 result = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float4 result = p.bg;
         float cw = 0.0f, a2w = 0.0f;
         int first_ind = -1;
         float4 g_normal = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         float g_t = 0.0f;
-        // hybrid(): h_compute.glsl:269-297, first segment peeled there, folded into the loop here
-        for (int i = p.RD; i > 0; i--) {
-            float t;
-            int ind = closest_hit(p, pos, dir, 0.001f, t);
-            n_rays++;
-            if (i == p.RD) first_ind = ind;
+        float t = -1.0f;
+        int ind = -1;
+        n_rays = 1;     // the camera ray's traversal counts whether or not the tile test shortened it
+        if (tl.cand) {
+            dir = primary_dir(p, div_const((float)x, p.fW, p.invW), div_const((float)y, p.fH, p.invH));
+            ind = closest_hit_primary_masked(p, dir, 0.001f, t, tl.cand);
+        }
+        first_ind = ind;
+        // hybrid(): h_compute.glsl:269-297, first segment peeled there, folded into the loop here.  A camera ray
+        // that misses everything leaves result = background (the loop's first pass with ind < 0).
+#pragma unroll 1
+        for (int i = p.RD; ind >= 0; i--) {
             float4 a0;
             bool stop = false;
-            if (ind < 0) {
-                a0 = p.bg;
-                stop = true;
-            } else {
+            {
                 const DevShape &s = s_shapes[ind];
                 float3 curr_pos = add3(pos, scale3(t, dir));
                 bool lit = shadow_ray(p, curr_pos);
@@ -177,9 +244,17 @@ __global__ void __launch_bounds__(TRACE_THREADS) rt_hybrid_kernel(const __grid_c
                 result = div4(add4(result, scale4(cw, a0)), 1.0f + cw);
                 cw = cw * a2w;
             }
-            if (stop) break;
+            if (stop || i == 1) break;
+            // next segment
+            ind = closest_hit(p, pos, dir, 0.001f, t);
+            n_rays++;
+            if (ind < 0) {
+                result = div4(add4(result, scale4(cw, p.bg)), 1.0f + cw);
+                break;
+            }
         }
-        const float4 c = gamma_correct(0.0f + result.x, 0.0f + result.y, 0.0f + result.z);
+        float4 c = make_float4(s_sky[0], s_sky[1], s_sky[2], 0.0f);
+        if (first_ind >= 0) c = gamma_correct(0.0f + result.x, 0.0f + result.y, 0.0f + result.z);
         o.color[pix] = c;
         gather_store(o.gather, yl, pix, c);
         o.hit[pix] = first_ind;
@@ -318,22 +393,38 @@ __device__ __forceinline__ float nb_weight(float4 nn, float nd, float nb, const 
 }
 
 constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 4;
-// tuning knobs, swept on B200 at config 4 (tools/gpu_pp_variants.sh; kernel ms):
-//   colours after the records, batch 4,  8 blocks/SM (64 regs)  0.398   <- the round's earlier version
-//   speculative colours,       batch 4,  6 blocks/SM (79 regs)  0.444
-//   speculative colours,       batch 2,  8 blocks/SM            0.355
-//   speculative colours,       batch 2, 10 blocks/SM (48 regs)  0.313   <- default
-//   speculative colours,       batch 1, 12 blocks/SM (40 regs)  0.318
-// The kernel is latency-bound on HBM (ncu: long_scoreboard 11 stall cycles per issue): resident warps buy more
-// than loads in flight per warp.
+// The pass is bound by HBM latency, not by arithmetic: what matters is how many dependent round trips a pixel makes
+// and how many bytes are in flight.  Round 1 walked the ring two frames at a time with the history colours requested
+// speculatively (0.313 ms at config 4, 0.72 of measured HBM bandwidth by algorithmic bytes, up to six dependent
+// trips per pixel).  Now a non-background pixel makes three: (1) raw colour + normal, (2) depth, the four neighbour
+// records and the normal / depth records of ALL the history frames (PP_BATCH = 7 = the whole ring of 8), (3) the
+// colours of exactly the frames the temporal test accepted.  Same arithmetic in the same order as the shader
+// (:175-201): the coefficients are evaluated in ring order and the walk stops at the first rejected frame; records
+// requested beyond that point are the only bytes moved in vain.
+// Tuning knobs, swept on B200 at config 4 (tools/gpu_pp_variants.sh):
 #ifndef PP_SPECULATE
-#define PP_SPECULATE 1
+#define PP_SPECULATE 1     // 1: request the colours together with the records (a rejected frame's colour is wasted)
 #endif
 #ifndef PP_MIN_BLOCKS
 #define PP_MIN_BLOCKS 10
 #endif
 #ifndef PP_BATCH
 #define PP_BATCH 2
+#endif
+#ifndef PP_EARLY
+#define PP_EARLY 0         // how many of the first batch's records are requested together with the neighbours
+#endif
+#ifndef PP_SLIM
+#define PP_SLIM 1          // history normals as xy + z (their w is never read): 5 registers per record instead of 6
+#endif
+#if PP_SLIM
+struct HistN { float2 xy; float z; };
+__device__ __forceinline__ HistN load_hist_normal(const float4 *p) { HistN n; n.xy = *reinterpret_cast<const float2 *>(p); n.z = reinterpret_cast<const float *>(p)[2]; return n; }
+__device__ __forceinline__ float3 hist_xyz(const HistN &n) { return make_float3(n.xy.x, n.xy.y, n.z); }
+#else
+typedef float4 HistN;
+__device__ __forceinline__ HistN load_hist_normal(const float4 *p) { return *p; }
+__device__ __forceinline__ float3 hist_xyz(const HistN &n) { return make_float3(n.x, n.y, n.z); }
 #endif
 
 __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_postprocess_kernel(const __grid_constant__ PostParams q)
@@ -362,92 +453,115 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
         if (nn.w > 0.99f) {
             n_nonbg = 1;
             const float2 dd = dslot[pix];
+            // the history's normal / depth records (first PP_BATCH frames = the whole ring when NF = 8): the first
+            // PP_EARLY of them are requested here, together with the neighbours, the rest after the spatial blend
+            HistN cn[PP_BATCH];
+            float4 hc[PP_BATCH];
+            float2 cd[PP_BATCH];
+            auto hist_off = [&](int i) -> size_t {
+                int cf = q.slot - i;
+                if (cf < 0) cf += q.NF;
+                return (size_t)cf * plane + pix;
+            };
+#pragma unroll
+            for (int b = 0; b < PP_BATCH; b++) {
+                if (b < PP_EARLY && 1 + b < q.NF) {
+                    const size_t off = hist_off(1 + b);
+                    cn[b] = load_hist_normal(q.ring_normal + off);
+                    cd[b] = q.ring_depth_xy[off];
+#if PP_SPECULATE
+                    hc[b] = q.ring_color[off];
+#endif
+                }
+            }
             const float new_depth = dd.x, new_bounces = dd.y;
             const bool flat = (q.edge_mode == RT_EDGE_FLAT32);
             const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            NbRec R, L, U, D;
-            R.color = L.color = U.color = D.color = z4;
-            float r = 0.0f, l = 0.0f, u = 0.0f, d = 0.0f;
+            // color = (color + u*up + d*down + l*left + r*right) / (1 + u + d + l + r)   (:173), accumulated in that
+            // order, one neighbour record alive at a time (an absent neighbour contributes 0 * vec4(0) like there)
+            float4 num = color;
+            float wsum = 1.0f;
+            {   // up
+                NbRec U; U.color = z4; float u = 0.0f;
+                if (y + 1 < q.H) {
+                    if (yl + 1 < q.rows) {
+                        U.color = q.raw[pix + q.W]; U.normal = nslot[pix + q.W]; U.depth = dslot[pix + q.W];
+                    } else {
+                        halo_read(q, q.halo_hi, x, U);
+                    }
+                    u = nb_weight(nn, new_depth, new_bounces, U);
+                }
+                num = add4(num, scale4(u, U.color)); wsum += u;
+            }
+            {   // down: `y - 1 > 0` on a uint (:150) is true for y = 0 and false for y = 1
+                NbRec D; D.color = z4; float d = 0.0f;
+                const bool has_d = flat ? (y != 1) : (y > 0);
+                if (has_d) {
+                    if (yl > 0) {
+                        D.color = q.raw[pix - q.W]; D.normal = nslot[pix - q.W]; D.depth = dslot[pix - q.W];
+                    } else {
+                        halo_read(q, q.halo_lo, x, D);
+                    }
+                    d = nb_weight(nn, new_depth, new_bounces, D);
+                }
+                num = add4(num, scale4(d, D.color)); wsum += d;
+            }
+            {   // left
+                NbRec L; L.color = z4; float l = 0.0f;
+                if (x > 0) {
+                    L.color = q.raw[pix - 1]; L.normal = nslot[pix - 1]; L.depth = dslot[pix - 1];
+                    l = nb_weight(nn, new_depth, new_bounces, L);
+                }
+                num = add4(num, scale4(l, L.color)); wsum += l;
+            }
+            {   // right: x < WIDTH is always true in the shader (:81); CLEAN uses x + 1 < WIDTH
+                NbRec R; R.color = z4; float r = 0.0f;
+                if (x + 1 < q.W) {
+                    R.color = q.raw[pix + 1]; R.normal = nslot[pix + 1]; R.depth = dslot[pix + 1];
+                    r = nb_weight(nn, new_depth, new_bounces, R);
+                } else if (flat) {
+                    // [f][W][y] is [f+1][0][y]; past the last slot it is the next array's [0][0][y]
+                    const size_t col0 = (size_t)yl * q.W;
+                    if (q.slot + 1 < q.NF) {
+                        const size_t off = (size_t)(q.slot + 1) * plane + col0;
+                        R.color = q.ring_color[off]; R.normal = q.ring_normal[off]; R.depth = q.ring_depth_xy[off];
+                    } else {
+                        R.color = q.ring_normal[col0];                   // pixels -> normals_buffer[0][0][y]
+                        float2 d0 = q.ring_depth_xy[col0];               // normals -> depth_buffer[0][0][y]
+                        R.normal = make_float4(d0.x, d0.y, 0.0f, q.ring_depth_w[col0]);
+                        R.depth = make_float2(0.0f, 0.0f);               // depth -> past the struct
+                    }
+                    r = nb_weight(nn, new_depth, new_bounces, R);
+                }
+                num = add4(num, scale4(r, R.color)); wsum += r;
+            }
+            color = div4(num, wsum);
 
-            // right: x < WIDTH is always true in the shader (:81); CLEAN uses x + 1 < WIDTH
-            if (x + 1 < q.W) {
-                R.color = q.raw[pix + 1]; R.normal = nslot[pix + 1]; R.depth = dslot[pix + 1];
-                r = nb_weight(nn, new_depth, new_bounces, R);
-            } else if (flat) {
-                // [f][W][y] is [f+1][0][y]; past the last slot it is the next array's [0][0][y]
-                const size_t col0 = (size_t)yl * q.W;
-                if (q.slot + 1 < q.NF) {
-                    const size_t off = (size_t)(q.slot + 1) * plane + col0;
-                    R.color = q.ring_color[off]; R.normal = q.ring_normal[off]; R.depth = q.ring_depth_xy[off];
-                } else {
-                    R.color = q.ring_normal[col0];                   // pixels -> normals_buffer[0][0][y]
-                    float2 d0 = q.ring_depth_xy[col0];               // normals -> depth_buffer[0][0][y]
-                    R.normal = make_float4(d0.x, d0.y, 0.0f, q.ring_depth_w[col0]);
-                    R.depth = make_float2(0.0f, 0.0f);               // depth -> past the struct
-                }
-                r = nb_weight(nn, new_depth, new_bounces, R);
-            }
-            if (x > 0) {
-                L.color = q.raw[pix - 1]; L.normal = nslot[pix - 1]; L.depth = dslot[pix - 1];
-                l = nb_weight(nn, new_depth, new_bounces, L);
-            }
-            if (y + 1 < q.H) {
-                if (yl + 1 < q.rows) {
-                    U.color = q.raw[pix + q.W]; U.normal = nslot[pix + q.W]; U.depth = dslot[pix + q.W];
-                } else {
-                    halo_read(q, q.halo_hi, x, U);
-                }
-                u = nb_weight(nn, new_depth, new_bounces, U);
-            }
-            // down: `y - 1 > 0` on a uint (:150) is true for y = 0 and false for y = 1
-            const bool has_d = flat ? (y != 1) : (y > 0);
-            if (has_d) {
-                if (yl > 0) {
-                    D.color = q.raw[pix - q.W]; D.normal = nslot[pix - q.W]; D.depth = dslot[pix - q.W];
-                } else {
-                    halo_read(q, q.halo_lo, x, D);
-                }
-                d = nb_weight(nn, new_depth, new_bounces, D);
-            }
-            // color = (color + u*up + d*down + l*left + r*right) / (1 + u + d + l + r)   (:173)
-            float4 num = add4(add4(add4(add4(color, scale4(u, U.color)), scale4(d, D.color)), scale4(l, L.color)),
-                              scale4(r, R.color));
-            color = div4(num, 1.0f + u + d + l + r);
-
-            // temporal blend over the previous NF-1 ring slots (:175-201).  The shader walks the ring one
-            // frame at a time and stops at the first rejected frame; done literally that is a chain of up to
-            // NF-1 dependent round trips to HBM.  Here the normal/depth records AND the colours of PP_BATCH frames
-            // are requested together and the coefficients evaluated in ring order: one round trip per batch, same
-            // arithmetic in the same order (a colour whose frame is rejected is simply not used).
+            // temporal blend over the previous NF-1 ring slots (:175-201): the records were requested above (first
+            // batch) so that they travel together with the neighbours; coefficients in ring order, stop at the first
+            // rejected frame, then the colours of the accepted ones.
             float4 color_sum = z4;
             float denominator = 0.9f;
             bool go = true;
             for (int i0 = 1; go && i0 < q.NF; i0 += PP_BATCH) {
-                float4 cn[PP_BATCH], hc[PP_BATCH];
-                float2 cd[PP_BATCH];
-                size_t off[PP_BATCH];
-                float coeff[PP_BATCH];
 #pragma unroll
                 for (int b = 0; b < PP_BATCH; b++) {
-                    int cf = q.slot - (i0 + b);
-                    if (cf < 0) cf += q.NF;
-                    off[b] = (size_t)cf * plane + pix;
-                    if (i0 + b < q.NF) {
-                        cn[b] = q.ring_normal[off[b]];
-                        cd[b] = q.ring_depth_xy[off[b]];
+                    if ((i0 > 1 || b >= PP_EARLY) && i0 + b < q.NF) {
+                        const size_t off = hist_off(i0 + b);
+                        cn[b] = load_hist_normal(q.ring_normal + off);
+                        cd[b] = q.ring_depth_xy[off];
 #if PP_SPECULATE
-                        // 94 % of the evaluated history frames are accepted (config 4): ask for the colour with the
-                        // record instead of after it -- one round trip to HBM per batch instead of two
-                        hc[b] = q.ring_color[off[b]];
+                        hc[b] = q.ring_color[off];
 #endif
                     }
                 }
+                float coeff[PP_BATCH];
                 int acc = 0;
 #pragma unroll
                 for (int b = 0; b < PP_BATCH; b++) {
                     if (go && i0 + b < q.NF) {
                         n_eval++;
-                        float normal_dot = dot3(xyz(nn), xyz(cn[b]));
+                        float normal_dot = dot3(xyz(nn), hist_xyz(cn[b]));
                         float depth_diff = 1.0f - clampf(fabsf(new_depth - cd[b].x), 0.0f, 1.0f);
                         float bounces_diff = 1.0f - clampf(div_const(fabsf(new_bounces - cd[b].y), 1.7f, RT_INV1P7), 0.0f, 1.0f);
                         coeff[b] = normal_dot * depth_diff * bounces_diff;
@@ -457,7 +571,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
 #if !PP_SPECULATE
 #pragma unroll
                 for (int b = 0; b < PP_BATCH; b++)
-                    if (b < acc) hc[b] = q.ring_color[off[b]];
+                    if (b < acc) hc[b] = q.ring_color[hist_off(i0 + b)];
 #endif
 #pragma unroll
                 for (int b = 0; b < PP_BATCH; b++)
@@ -477,7 +591,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
     unsigned val[3] = { n_nonbg, n_eval, n_acc };
     const int tid = threadIdx.y * PP_BLOCK_X + threadIdx.x;
     const unsigned gw = (blockIdx.x + blockIdx.y * gridDim.x) * ((PP_BLOCK_X * PP_BLOCK_Y) >> 5) + (tid >> 5);
-    unsigned long long *st = q.stats + (gw % STAT_STRIPES) * ST_COUNT;
+    unsigned long long *st = q.stats + (gw % STAT_STRIPES) * STAT_STRIDE;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
         unsigned v = __reduce_add_sync(0xffffffffu, val[k]);
