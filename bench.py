@@ -286,7 +286,10 @@ class Setup:
                 plan = bands.replan_from_times(plan, [float(x.item()) for x in allt], H)
         self.plan = plan
         y0, rows = plan[rank]
-        self.rt = rtb.RayTracer(W, H, AA, device=local, band_y0=y0, band_rows=rows, band_index=rank, band_count=world)
+        # two frames in flight (RT_FLAG_PIPELINE): the tail of a frame's kernels and the short second pass of mode 1
+        # are filled with the next frame's trace kernel
+        self.rt = rtb.RayTracer(W, H, AA, device=local, band_y0=y0, band_rows=rows, band_index=rank, band_count=world,
+                                flags=(rtb.FLAG_PIPELINE if args.pipeline else 0))
         self.rt.set_stream(env.stream.cuda_stream)
         self.rt.upload_scene(fr.shapes, fr.n)
         eng = bands.GpuBandEngine(self.rt)
@@ -321,6 +324,7 @@ class Setup:
         self.br.gather_finish(self.pending["works"])
         self.pending["works"] = []
         self.br.gather_flush()
+        self.rt.stream_wait_frames()     # the timing events live on the context's stream: behind the frames in flight
 
     def gather_description(self) -> str:
         w, d = self.env.world, self.direct
@@ -372,8 +376,10 @@ def timed_region(env: Env, su: Setup, K: int, Wm: int, sampler=None) -> dict:
     if sampler is not None:
         sampler.mark_start()
     e0.record()
+    th = time.perf_counter()
     for i in range(Wm, Wm + K):
         su.step(inputs[i])
+    host_ms = (time.perf_counter() - th) * 1e3      # what the host needs to enqueue the K frames
     su.drain()
     e1.record()
     env.barrier()
@@ -394,7 +400,7 @@ def timed_region(env: Env, su: Setup, K: int, Wm: int, sampler=None) -> dict:
     tot = {k: float(v) for k, v in zip(keys, cnt.tolist())}
     ms = float(tms.item())
     rays = tot["rays_closest"] + tot["rays_shadow"]
-    return {"ms": ms, "ms_own": ms_own, "rays": rays, "tot": tot, "mrays": rays / (ms * 1e-3) / 1e6}
+    return {"ms": ms, "ms_own": ms_own, "rays": rays, "tot": tot, "mrays": rays / (ms * 1e-3) / 1e6, "host_ms": host_ms}
 
 
 def kernel_leg(env: Env, su: Setup, frames: int) -> dict:
@@ -458,10 +464,12 @@ def rooflines(env: Env, su: Setup, kl: dict, peak_tf: float) -> dict:
 
 def per_rank_report(env: Env, su: Setup, tr: dict, kl: dict, K: int):
     mine = {"rank": env.rank, "rows": su.plan[env.rank][1], "step_ms": round(tr["ms_own"] / K, 5),
+            "host_enqueue_ms": round(tr["host_ms"] / K, 5),
             "trace_kernel_ms": round(kl["trace_ms"], 5)}
     if "post_ms" in kl:
         mine["post_kernel_ms"] = round(kl["post_ms"], 5)
-    # what the rank spends per frame outside its own kernels: launch gaps, waits for the neighbours' halo rows
+    # step time minus the kernels' own times (each timed alone): positive = launch gaps and waits for the
+    # neighbours' halo rows, negative = what the overlap of consecutive frames saves
     mine["other_ms"] = round(mine["step_ms"] - kl["trace_ms"] - kl.get("post_ms", 0.0), 5)
     if env.world == 1:
         return [mine]
@@ -508,6 +516,7 @@ def run_b200(args) -> None:
             "data": "synthetic", "impl": "b200",
             "config": fr.config(),
             "run": {"parallelism": f"row-bands x{world}", "bands": su.plan, "gather": su.gather_description(),
+                    "frames_in_flight": 2 if args.pipeline else 1,
                     "l2": "no input reuse: ~1.4 KB of kernel parameters in, each frame writes a different "
                           "ring slot (8 x %.0f MB > 126 MB L2)" % (fr.W * fr.H * 44 / 1e6)},
             "rays_per_frame": tr["rays"] / K,
@@ -1008,6 +1017,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     ap.add_argument("--no-other-configs", dest="other_configs", action="store_false")
     ap.add_argument("--no-parity-check", dest="parity_check", action="store_false")
+    ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",
+                    help="one frame at a time on the context's stream instead of RT_FLAG_PIPELINE")
     ap.add_argument("--even-bands", action="store_true", help="equal-height bands instead of cost-weighted")
     ap.add_argument("--fence", default="flags", choices=["flags", "allreduce"],
                     help="N > 1, direct gather: fence = rt_fence (peer-memory flags, no host-side "

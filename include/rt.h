@@ -71,7 +71,16 @@ enum {
      * frame is finished by aop_postprocessing like a mode-1 frame -- rt_render_frame leaves the colour in the
      * raw plane and rt_halo_pack / rt_postprocess blend it spatially and temporally into pixels[slot], using
      * the normals and depths RT_FLAG_PHONG_GBUFFER (required) has written. */
-    RT_FLAG_PHONG_POSTPROCESS = 2
+    RT_FLAG_PHONG_POSTPROCESS = 2,
+    /* Two frames in flight.  The kernels of consecutive frames are enqueued on two internal streams in turn, each
+     * frame ordered after exactly what it depends on (the frame before it only where the post-processing pass
+     * reads that frame's result), so that the tail of one frame's kernels, the short passes of mode 1 and the
+     * wait for the neighbouring bands' halo rows are filled with the next frame's trace kernel.  The results are
+     * the same bits.  What changes for the caller: work enqueued by rt_render_frame / rt_halo_pack / rt_postprocess
+     * is NOT ordered with the caller's stream any more; every other entry point that touches results (downloads,
+     * rt_device_ptr, rt_get_stats, rt_fence, rt_synchronize, ...) first makes the context's stream wait for the
+     * frames issued so far.  Device pointers from rt_device_ptr are valid until the next rt_render_frame. */
+    RT_FLAG_PIPELINE = 4
 };
 
 /* buffers of rt_download / rt_upload / rt_device_ptr */
@@ -174,6 +183,10 @@ const char *rt_last_error(const rt_ctx *ctx); /* ctx may be NULL: last error of 
 /* run on this CUDA stream (a cudaStream_t; NULL = the context's own stream) */
 int rt_set_stream(rt_ctx *ctx, void *cuda_stream);
 int rt_synchronize(rt_ctx *ctx);
+/* RT_FLAG_PIPELINE: the context's stream waits (on the device) for the frames issued so far -- what a caller
+ * enqueues before it puts its own work (an event, a kernel reading rt_device_ptr memory) behind them.  Without the
+ * flag the frames are on that stream anyway and this does nothing. */
+int rt_stream_wait_frames(rt_ctx *ctx);
 /* per-kernel CUDA-event timing into rt_stats.ms_* (off by default: it adds two event records) */
 int rt_set_timing(rt_ctx *ctx, int enabled);
 

@@ -14,6 +14,7 @@ MODE_AO_PP, MODE_AO, MODE_PHONG, MODE_HYBRID = 1, 2, 3, 4
 EDGE_FLAT32, EDGE_CLEAN = 0, 1
 FLAG_PHONG_GBUFFER = 1
 FLAG_PHONG_POSTPROCESS = 2
+FLAG_PIPELINE = 4
 BUF_COLOR, BUF_NORMAL, BUF_DEPTH, BUF_HIT_INDEX, BUF_IMAGE, BUF_RAW_COLOR, BUF_DEPTH_XY, BUF_DEPTH_W = range(8)
 LAYOUT_ROW_MAJOR, LAYOUT_REFERENCE = 0, 1
 MAX_SHAPES, MAX_AA, MAX_FRAMES = 10, 16, 16
@@ -40,7 +41,7 @@ class rt_halo_info(C.Structure):
 
 EXPORTS = (
     "rt_abi_version", "rt_device_count", "rt_create", "rt_destroy", "rt_last_error", "rt_set_stream",
-    "rt_synchronize", "rt_set_timing", "rt_upload_scene", "rt_render_frame", "rt_halo_pack", "rt_get_halo",
+    "rt_synchronize", "rt_stream_wait_frames", "rt_set_timing", "rt_upload_scene", "rt_render_frame", "rt_halo_pack", "rt_get_halo",
     "rt_postprocess", "rt_download", "rt_upload", "rt_download_async", "rt_download_rgba8_async", "rt_download_color_overlapped", "rt_readback_wait", "rt_device_ptr", "rt_get_stats",
     "rt_reset_stats", "rt_reset_ring", "rt_debug_eval_math", "rt_measure_fp32_peak",
     "rt_set_frame_target", "rt_set_frame_targets", "rt_frame_download_overlapped", "rt_stream_wait_readback", "rt_band_to_frame_overlapped", "rt_frame_create", "rt_frame_destroy", "rt_peer_export", "rt_peer_import",
@@ -68,6 +69,7 @@ def load():
     L.rt_last_error.restype = C.c_char_p
     L.rt_set_stream.argtypes = [vp, vp]
     L.rt_synchronize.argtypes = [vp]
+    L.rt_stream_wait_frames.argtypes = [vp]
     L.rt_set_timing.argtypes = [vp, i32]
     L.rt_upload_scene.argtypes = [vp, vp, i32]
     L.rt_render_frame.argtypes = [vp, i32, vp, vp]

@@ -77,6 +77,10 @@ class RayTracer:
     def synchronize(self):
         self._check(self.lib.rt_synchronize(self.h))
 
+    def stream_wait_frames(self):
+        """rt_stream_wait_frames: with FLAG_PIPELINE, the context's stream waits for the frames issued so far"""
+        self._check(self.lib.rt_stream_wait_frames(self.h))
+
     def set_timing(self, on: bool):
         self._check(self.lib.rt_set_timing(self.h, int(on)))
 

@@ -82,10 +82,7 @@ class GpuBandEngine:
         self.send_hi = device_tensor(info.send_hi, info.row_bytes, d)
         self.recv_lo = device_tensor(info.recv_lo, info.row_bytes, d)
         self.recv_hi = device_tensor(info.recv_hi, info.row_bytes, d)
-        self._color = []
-        for s in range(tracer.NF):
-            p, n = tracer.device_ptr(L.BUF_COLOR, s)
-            self._color.append(device_tensor(p, n, d))
+        self._buf_color = L.BUF_COLOR
 
     def render_frame(self, mode, uniforms, rand_buffer):
         self.rt.render_frame(mode, uniforms, rand_buffer)
@@ -112,8 +109,10 @@ class GpuBandEngine:
         self.rt.postprocess()
 
     def band_color(self, slot: int):
-        """float32 tensor [rows*W*4] of pixels[slot] for this band (row-major)"""
-        return self._color[slot]
+        """float32 tensor [rows*W*4] of pixels[slot] for this band (row-major).  Looked up per call: a ring slot
+        moves to another physical plane with every frame that rewrites it (rt_device_ptr)."""
+        p, n = self.rt.device_ptr(self._buf_color, slot)
+        return device_tensor(p, n, self.rt.device)
 
 
 def shares_to_row_end(height: int, weights) -> List[int]:

@@ -147,8 +147,8 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                                 // the shader returns before touching normals/depth: the slot keeps what an
                                 // earlier frame left there (ao_compute.glsl:199-208 precede :222-229)
                                 keep_normal = true;
-                                dx = o.depth_xy[pix].x;
-                                dw = o.depth_w[pix];
+                                dx = o.old_depth_xy[pix].x;
+                                dw = o.old_depth_w[pix];
                             }
                         } else {
                             live = true;
@@ -256,7 +256,7 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
             c = gamma_correct(div_aa(p, ar), div_aa(p, ag), div_aa(p, ab));
         o.color[pix] = c;
         gather_store(o.gather, yl, pix, c);   // rt_set_frame_targets: the assembled frame, maybe over NVLink
-        if (!keep_normal) o.normal[pix] = make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
+        o.normal[pix] = keep_normal ? o.old_normal[pix] : make_float4(nrm.x, nrm.y, nrm.z, nrm_w);
         o.depth_xy[pix] = make_float2(div_aa(p, dx), div_aa(p, dy));
         o.depth_w[pix] = div_aa(p, dw);
         o.hit[pix] = hit0;

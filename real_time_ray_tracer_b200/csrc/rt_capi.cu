@@ -23,12 +23,32 @@ struct rt_ctx {
     size_t npix = 0; // rows * width
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
-    // ring planes, each [NF][rows*W]
+    // Ring planes, each [NF + 2][rows*W]: NF + 2 PHYSICAL slots behind the NF ring slots of the contract.  A frame
+    // that writes normals / depth (modes 1, 2; modes 3, 4 under RT_FLAG_PHONG_GBUFFER) takes the physical slot that
+    // was retired two frames earlier, and the slot's previous one is retired in turn (phys[] maps ring slot ->
+    // physical slot, retired[] is the queue).  That is what lets two frames be in flight (RT_FLAG_PIPELINE): the
+    // trace kernel of frame k+1 writes planes nobody reads while the post-processing kernel of frame k still
+    // walks the whole ring, including the slot frame k+1 replaces.
     float4 *ring_color = nullptr, *ring_normal = nullptr;
     float2 *ring_depth_xy = nullptr;
     float *ring_depth_w = nullptr;
-    float4 *raw = nullptr; // mode-1 trace output of the current frame
-    int *hit = nullptr;
+    int phys[RT_MAX_FRAMES] = {};
+    int retired[2] = { 0, 0 };
+    float4 *raw[2] = { nullptr, nullptr }; // trace output of a frame that rt_postprocess finishes, by frame parity
+    int *hit[2] = { nullptr, nullptr };    // hit-index plane, by frame parity
+    // RT_FLAG_PIPELINE: frames alternate between two internal streams; see begin_frame / end_frame
+    bool pipeline = false;
+    cudaStream_t fstream[2] = { nullptr, nullptr };
+    cudaEvent_t ev_done[4] = { nullptr, nullptr, nullptr, nullptr }; // frame k complete (and every frame before it)
+    cudaEvent_t ev_user = nullptr, ev_join[2] = { nullptr, nullptr };
+    unsigned long long frame_no = 0;   // frames rendered so far; the frame being built is frame_no - 1
+    bool fork_pending = false;         // work was enqueued on `stream` that the next frames must follow
+    bool fork_seen[2] = { true, true };
+    bool serialize_next = false;       // the next frame must follow the previous one completely
+    int prev_slot = -1;
+    bool prev_post = false;
+    bool prev_waited = false;          // the frame being built already waits for its predecessor
+    int last_par = 0;
     void *halo[4] = { nullptr, nullptr, nullptr, nullptr }; // send_lo, send_hi, recv_lo[2], recv_hi[2] (two rows each: frame parity of linked bands)
     void *staging = nullptr; // npix * 16 bytes, layout conversions of rt_download / rt_upload (synchronous users only)
     uchar4 *rgba8 = nullptr; // 2 x npix 8-bit pixels, rt_download_rgba8_async (allocated on first use)
@@ -65,8 +85,9 @@ struct rt_ctx {
     cudaEvent_t ev_quant[2] = { nullptr, nullptr }, ev_copy[2] = { nullptr, nullptr };
     bool copy_pending[2] = { false, false };
     bool timing = false;
-    cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
+    cudaEvent_t ev[2][4] = {};   // per frame parity: trace begin / end, post-processing begin / end
     bool ev_trace_valid = false, ev_post_valid = false;
+    int ev_parity = 0;
     std::string err;
 };
 
@@ -108,7 +129,14 @@ static void free_all(rt_ctx *c)
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
-    cudaFree(c->raw); cudaFree(c->hit); cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->sky);
+    for (int i = 0; i < 2; i++) { cudaFree(c->raw[i]); cudaFree(c->hit[i]); }
+    cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->sky);
+    for (int i = 0; i < 2; i++) {
+        if (c->fstream[i]) cudaStreamDestroy(c->fstream[i]);
+        if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]);
+    }
+    for (cudaEvent_t e : c->ev_done) if (e) cudaEventDestroy(e);
+    if (c->ev_user) cudaEventDestroy(c->ev_user);
     cudaFree(c->rgba8); cudaFree(c->pack_count);
     if (c->ev_fence_in) cudaEventDestroy(c->ev_fence_in);
     if (c->ev_fence_done) cudaEventDestroy(c->ev_fence_done);
@@ -116,7 +144,7 @@ static void free_all(rt_ctx *c)
     if (c->fence_stream) cudaStreamDestroy(c->fence_stream);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
-    for (cudaEvent_t e : c->ev) if (e) cudaEventDestroy(e);
+    for (int i = 0; i < 2; i++) for (cudaEvent_t e : c->ev[i]) if (e) cudaEventDestroy(e);
     for (int i = 0; i < 2; i++) {
         if (c->ev_quant[i]) cudaEventDestroy(c->ev_quant[i]);
         if (c->ev_copy[i]) cudaEventDestroy(c->ev_copy[i]);
@@ -136,7 +164,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     if (cfg->num_frames < 1 || cfg->num_frames > RT_MAX_FRAMES) return fail(nullptr, RT_EINVAL, "rt_create: num_frames must be 1..%d", RT_MAX_FRAMES);
     if (cfg->edge_mode != RT_EDGE_FLAT32 && cfg->edge_mode != RT_EDGE_CLEAN) return fail(nullptr, RT_EINVAL, "rt_create: bad edge_mode");
     for (int r : cfg->reserved) if (r != 0) return fail(nullptr, RT_EINVAL, "rt_create: reserved fields must be 0");
-    if (cfg->flags & ~(RT_FLAG_PHONG_GBUFFER | RT_FLAG_PHONG_POSTPROCESS)) return fail(nullptr, RT_EINVAL, "rt_create: unknown flags 0x%x", cfg->flags);
+    if (cfg->flags & ~(RT_FLAG_PHONG_GBUFFER | RT_FLAG_PHONG_POSTPROCESS | RT_FLAG_PIPELINE)) return fail(nullptr, RT_EINVAL, "rt_create: unknown flags 0x%x", cfg->flags);
     if ((cfg->flags & RT_FLAG_PHONG_POSTPROCESS) && !(cfg->flags & RT_FLAG_PHONG_GBUFFER))
         return fail(nullptr, RT_EINVAL, "rt_create: RT_FLAG_PHONG_POSTPROCESS needs RT_FLAG_PHONG_GBUFFER (the pass reads normals and depths)");
     int rows = cfg->band_rows ? cfg->band_rows : cfg->height - cfg->band_y0;
@@ -144,7 +172,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     int bcount = cfg->band_count ? cfg->band_count : 1;
     if (cfg->band_index < 0 || cfg->band_index >= bcount) return fail(nullptr, RT_EINVAL, "rt_create: bad band_index");
     if (bcount == 1 && rows != cfg->height) return fail(nullptr, RT_EINVAL, "rt_create: a partial band needs band_count > 1");
-    if ((long long)cfg->width * cfg->height * cfg->num_frames >= (1ll << 31)) return fail(nullptr, RT_EINVAL, "rt_create: W*H*num_frames must fit 31 bits");
+    if ((long long)cfg->width * cfg->height * (cfg->num_frames + 2) >= (1ll << 31)) return fail(nullptr, RT_EINVAL, "rt_create: W*H*(num_frames+2) must fit 31 bits");
 
     int ndev = rt_device_count();
     if (ndev <= 0) return fail(nullptr, RT_ENODEVICE, "rt_create: no CUDA device (this library has no CPU path)");
@@ -157,7 +185,11 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     c->cfg.band_count = bcount;
     c->rows = rows;
     c->npix = (size_t)rows * cfg->width;
-    const size_t ring = c->npix * cfg->num_frames;
+    const size_t ring = c->npix * (cfg->num_frames + 2);
+    for (int i = 0; i < cfg->num_frames; i++) c->phys[i] = i;
+    c->retired[0] = cfg->num_frames; c->retired[1] = cfg->num_frames + 1;
+    c->pipeline = (cfg->flags & RT_FLAG_PIPELINE) != 0;
+    if (const char *k = getenv("RT_PIPELINE")) c->pipeline = strcmp(k, "0") != 0;   // test sweeps: force it on / off
     cudaError_t e = cudaSetDevice(cfg->device);
     auto alloc0 = [&](void **p, size_t bytes) {
         if (e != cudaSuccess) return;
@@ -180,8 +212,14 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0((void **)&c->ring_normal, ring * sizeof(float4));
     alloc0((void **)&c->ring_depth_xy, ring * sizeof(float2));
     alloc0((void **)&c->ring_depth_w, ring * sizeof(float));
-    alloc0((void **)&c->raw, c->npix * sizeof(float4));
-    alloc0((void **)&c->hit, c->npix * sizeof(int));
+    for (int i = 0; i < 2; i++) {
+        alloc0((void **)&c->raw[i], c->npix * sizeof(float4));
+        alloc0((void **)&c->hit[i], c->npix * sizeof(int));
+        if (e == cudaSuccess && c->pipeline) e = cudaStreamCreateWithFlags(&c->fstream[i], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming);
+    }
+    for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming);
     alloc0(&c->staging, c->npix * sizeof(float4));
     alloc0((void **)&c->stats, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long));
     alloc0((void **)&c->sky, 12 * sizeof(float));
@@ -197,7 +235,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width) * (i >= 2 ? 2 : 1));
     alloc0((void **)&c->pack_count, sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long));
-    for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
+    for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i >> 2][i & 3]);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
         int code = (e == cudaErrorMemoryAllocation) ? RT_ENOMEM : RT_ECUDA;
@@ -212,6 +250,78 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
 
 void rt_destroy(rt_ctx *ctx) { free_all(ctx); }
 
+// ---- frame scheduling (RT_FLAG_PIPELINE) ---------------------------------------------------------------------
+// Without the flag every kernel goes on the context's stream, in order, and nothing below does anything.  With it,
+// frame k's kernels go on fstream[k & 1]:
+//     [after ev_done[k-3]] trace_k  [after ev_done[k-1]] (halo pack_k, post-processing_k)  -> ev_done[k]
+// * stream order puts frame k behind frame k-2; ev_done[j] also stands for every frame before j (each frame waits
+//   for its predecessor before it ends), so after ev_done[k-3] only frame k-1 can still be running;
+// * trace_k may run beside frame k-1: it writes a physical slot retired two frames ago (last read by the passes of
+//   frames <= k-3 and by trace_{k-2}), the raw / hit planes of its parity, and reads the slot's previous record,
+//   which frame k-1 does not write -- unless both frames name the same ring slot, or frame k writes its colour in
+//   place (modes 3/4 without G-buffer) while frame k-1's pass may be reading the ring: then it waits for k-1 first;
+// * the halo pack and the post-processing pass read frame k-1's result (the history, the wrapped row of FLAT32) and
+//   share the halo rows with frame k-1's pass: they follow ev_done[k-1].
+// The context's stream carries no kernels then; entry points that hand results to the caller make it wait for the
+// frame streams (join_frames), entry points through which the caller changes state that later frames depend on
+// (uploads, resets, fences, a new stream) make the next frames wait for it (mark_fork).
+static inline cudaStream_t cur_stream(rt_ctx *c) { return c->pipeline ? c->fstream[(c->frame_no - 1) & 1] : c->stream; }
+static inline void mark_fork(rt_ctx *c) { if (c->pipeline) c->fork_pending = true; }
+
+static cudaError_t join_frames(rt_ctx *c)
+{
+    if (!c->pipeline) return cudaSuccess;
+    for (int i = 0; i < 2; i++) {
+        cudaError_t e = cudaEventRecord(c->ev_join[i], c->fstream[i]);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, c->ev_join[i], 0);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+static cudaError_t sync_fork(rt_ctx *c, int par)
+{
+    cudaError_t e = cudaSuccess;
+    if (!c->pipeline) return e;
+    if (c->fork_pending) {
+        e = cudaEventRecord(c->ev_user, c->stream);
+        c->fork_seen[0] = c->fork_seen[1] = false;
+        c->fork_pending = false;
+    }
+    if (e == cudaSuccess && !c->fork_seen[par]) {
+        e = cudaStreamWaitEvent(c->fstream[par], c->ev_user, 0);
+        c->fork_seen[par] = true;
+    }
+    return e;
+}
+
+static cudaError_t wait_prev_frame(rt_ctx *c)
+{
+    const unsigned long long k = c->frame_no - 1;
+    if (!c->pipeline || k < 1) return cudaSuccess;
+    return cudaStreamWaitEvent(c->fstream[k & 1], c->ev_done[(k - 1) & 3], 0);
+}
+
+static cudaError_t begin_frame(rt_ctx *c, int slot, bool inplace)
+{
+    const unsigned long long k = c->frame_no++;
+    if (!c->pipeline) return cudaSuccess;
+    cudaStream_t S = c->fstream[k & 1];
+    cudaError_t e = sync_fork(c, (int)(k & 1));
+    if (e == cudaSuccess && k >= 3) e = cudaStreamWaitEvent(S, c->ev_done[(k - 3) & 3], 0);
+    const bool serial = c->serialize_next || slot == c->prev_slot || (inplace && c->prev_post);
+    if (e == cudaSuccess && serial) e = wait_prev_frame(c);
+    c->serialize_next = false;
+    return e;
+}
+
+static cudaError_t end_frame(rt_ctx *c)
+{
+    if (!c->pipeline) return cudaSuccess;
+    const unsigned long long k = c->frame_no - 1;
+    return cudaEventRecord(c->ev_done[k & 3], c->fstream[k & 1]);
+}
+
 int rt_set_stream(rt_ctx *c, void *cuda_stream)
 {
     if (!c) return RT_EINVAL;
@@ -219,6 +329,8 @@ int rt_set_stream(rt_ctx *c, void *cuda_stream)
     if (ns != c->stream) {
         // what is still pending on the old stream (kernels, the sky constants) stays ahead of the new one
         CU(c, cudaSetDevice(c->cfg.device));
+        CU(c, join_frames(c));
+        mark_fork(c);
         CU(c, cudaEventRecord(c->ev_stream_switch, c->stream));
         CU(c, cudaStreamWaitEvent(ns, c->ev_stream_switch, 0));
     }
@@ -226,10 +338,19 @@ int rt_set_stream(rt_ctx *c, void *cuda_stream)
     return RT_OK;
 }
 
+int rt_stream_wait_frames(rt_ctx *c)
+{
+    if (!c) return RT_EINVAL;
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
+    return RT_OK;
+}
+
 int rt_synchronize(rt_ctx *c)
 {
     if (!c) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
+    for (int i = 0; i < 2; i++) if (c->fstream[i]) CU(c, cudaStreamSynchronize(c->fstream[i]));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaStreamSynchronize(c->copy_stream)); // outstanding rt_download_rgba8_async read-backs
     CU(c, cudaStreamSynchronize(c->fence_stream));
@@ -364,33 +485,71 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
         c->rand_last = p.rand[2 * c->cfg.aa - 1];
     }
 
+    // a frame left without its second pass is closed as aop_compute alone leaves it: pixels[slot] = the raw colour
+    if (c->frame_pending_post) {
+        CU(c, wait_prev_frame(c));
+        CU(c, cudaMemcpyAsync(c->ring_color + (size_t)c->phys[c->last_slot] * c->npix, c->raw[c->last_par], c->npix * sizeof(float4),
+                              cudaMemcpyDeviceToDevice, cur_stream(c)));
+        CU(c, end_frame(c));
+        c->frame_pending_post = false;
+    }
+    const bool sky_changed = !c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0;
+    if (sky_changed) c->serialize_next = true;      // the constants are shared by the frames in flight
+    // frames that write normals / depth take a fresh physical slot; modes 3/4 without the G-buffer extension leave
+    // both as they are (p_compute.glsl:223-246) and write their colour in place
+    const bool writes_gbuffer = ao || (c->cfg.flags & RT_FLAG_PHONG_GBUFFER);
+    CU(c, begin_frame(c, slot, !writes_gbuffer));
+    const int par = (int)((c->frame_no - 1) & 1);
+    cudaStream_t S = cur_stream(c);
+    const int p_old = c->phys[slot];
+    int p_new = p_old;
+    if (writes_gbuffer) {
+        p_new = c->retired[0];
+        c->retired[0] = c->retired[1];
+        c->retired[1] = p_old;
+        c->phys[slot] = p_new;
+    }
+
     TraceOut o{};
-    const size_t off = (size_t)slot * c->npix;
-    o.color = post ? c->raw : c->ring_color + off;
+    const size_t off = (size_t)p_new * c->npix, off_old = (size_t)p_old * c->npix;
+    o.color = post ? c->raw[par] : c->ring_color + off;
     o.normal = c->ring_normal + off;
     o.depth_xy = c->ring_depth_xy + off;
     o.depth_w = c->ring_depth_w + off;
-    o.hit = c->hit;
+    o.old_normal = c->ring_normal + off_old;
+    o.old_depth_xy = c->ring_depth_xy + off_old;
+    o.old_depth_w = c->ring_depth_w + off_old;
+    o.hit = c->hit[par];
     o.stats = c->stats;
     o.ao_kernel = c->ao_kernel;
     o.sky = c->sky;
-    if (!c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0) {
+    if (sky_changed) {
         // first frame, or the background changed (scene toggle, src/main.cpp:229-255)
-        CU(c, launch_sky_gamma(p.bg, p.AA, c->sky, c->stream));
+        CU(c, launch_sky_gamma(p.bg, p.AA, c->sky, S));
         c->sky_bg = p.bg;
         c->sky_valid = true;
+        c->serialize_next = true;   // the next frame (other stream) reads them too
     }
-    // mode 1: the trace output is raw; the post-processing pass writes the frame
+    // a frame that rt_postprocess finishes: the trace output is raw; the post-processing pass writes the frame
     GatherTargets g = band_gather_targets(c), none = {};
     o.gather = post ? none : g;
     c->gather_post = post ? g : none;
-    if (c->timing) CU(c, cudaEventRecord(c->ev[0], c->stream));
-    CU(c, launch_trace(p, o, c->stream));
-    if (c->timing) { CU(c, cudaEventRecord(c->ev[1], c->stream)); c->ev_trace_valid = true; }
+    c->ev_parity = par;
+    if (c->timing) CU(c, cudaEventRecord(c->ev[par][0], S));
+    CU(c, launch_trace(p, o, S));
+    if (c->timing) { CU(c, cudaEventRecord(c->ev[par][1], S)); c->ev_trace_valid = true; }
     c->last_mode = mode;
     c->last_slot = slot;
+    c->last_par = par;
     c->frame_pending_post = post;
     c->halo_packed = false;
+    c->prev_waited = false;
+    c->prev_slot = slot;
+    c->prev_post = post;
+    if (!post) {
+        CU(c, wait_prev_frame(c));   // ev_done[k] stands for every frame up to k
+        CU(c, end_frame(c));
+    }
     return RT_OK;
 }
 
@@ -400,7 +559,8 @@ static void fill_post(rt_ctx *c, PostParams &q)
     q.y0 = c->cfg.band_y0; q.rows = c->rows;
     q.slot = c->last_slot; q.edge_mode = c->cfg.edge_mode;
     q.band_index = c->cfg.band_index; q.band_count = c->cfg.band_count;
-    q.raw = c->raw; q.ring_color = c->ring_color; q.ring_normal = c->ring_normal;
+    memcpy(q.phys, c->phys, sizeof q.phys);
+    q.raw = c->raw[c->last_par]; q.ring_color = c->ring_color; q.ring_normal = c->ring_normal;
     q.ring_depth_xy = c->ring_depth_xy; q.ring_depth_w = c->ring_depth_w;
     q.send_lo = c->halo[0]; q.send_hi = c->halo[1];
     // linked bands alternate between two receive rows: frame k+1's rows may arrive while frame k's are still read
@@ -440,8 +600,18 @@ int rt_halo_pack(rt_ctx *c)
         q.sig_prev_hi = (r > 0) ? c->peers.box[r - 1] + MB_HALO_HI : nullptr;
         q.pack_count = c->pack_count;
     }
-    CU(c, launch_halo_pack(q, c->stream));
+    // the pack reads frame k-1's result (the wrapped row's first element under FLAT32) and, with linked bands or a
+    // single band, writes halo rows that frame k-1's pass may still be reading: it follows frame k-1
+    const int fpar = c->last_par;
+    CU(c, sync_fork(c, fpar));
+    if (!c->prev_waited) { CU(c, wait_prev_frame(c)); c->prev_waited = true; }
+    CU(c, launch_halo_pack(q, cur_stream(c)));
     c->halo_packed = true;
+    if (c->cfg.band_count > 1 && !c->halo_direct) {
+        // the caller moves the rows (rt_get_halo) on the context's stream: behind the pack, ahead of the pass
+        CU(c, join_frames(c));
+        mark_fork(c);
+    }
     return RT_OK;
 }
 
@@ -459,7 +629,9 @@ int rt_postprocess(rt_ctx *c)
     if (!c) return RT_EINVAL;
     if (!c->frame_pending_post) return fail(c, RT_ESTATE, "rt_postprocess: the last frame was not rendered in mode 1");
     CU(c, cudaSetDevice(c->cfg.device));
-    if (c->timing) CU(c, cudaEventRecord(c->ev[2], c->stream));
+    cudaStream_t S = cur_stream(c);
+    const int fpar = c->last_par;
+    if (c->timing) CU(c, cudaEventRecord(c->ev[fpar][2], S));
     if (!c->halo_packed) {
         if (c->cfg.band_count > 1) return fail(c, RT_ESTATE, "rt_postprocess: call rt_halo_pack and exchange the halo rows first");
         if (c->cfg.edge_mode == RT_EDGE_FLAT32) {
@@ -469,9 +641,12 @@ int rt_postprocess(rt_ctx *c)
     }
     PostParams q{};
     fill_post(c, q);
-    CU(c, launch_postprocess(q, c->stream));
-    if (c->timing) { CU(c, cudaEventRecord(c->ev[3], c->stream)); c->ev_post_valid = true; }
+    CU(c, sync_fork(c, fpar));
+    if (!c->prev_waited) { CU(c, wait_prev_frame(c)); c->prev_waited = true; }   // the history is frame k-1's result
+    CU(c, launch_postprocess(q, S));
+    if (c->timing) { CU(c, cudaEventRecord(c->ev[fpar][3], S)); c->ev_post_valid = true; }
     c->frame_pending_post = false;
+    CU(c, end_frame(c));
     return RT_OK;
 }
 
@@ -532,7 +707,9 @@ int rt_fence(rt_ctx *c)
     if (!c) return RT_EINVAL;
     if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence: call rt_link_peers first");
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     CU(c, launch_fence(c->peers, c->link_rank, c->link_world, ++c->fence_epoch, c->stream));
+    mark_fork(c);     // a barrier on the context's stream: the next frames stay behind it
     return RT_OK;
 }
 
@@ -541,6 +718,7 @@ int rt_fence_async(rt_ctx *c)
     if (!c) return RT_EINVAL;
     if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence_async: call rt_link_peers first");
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     CU(c, cudaEventRecord(c->ev_fence_in, c->stream));
     CU(c, cudaStreamWaitEvent(c->fence_stream, c->ev_fence_in, 0));
     CU(c, launch_fence(c->peers, c->link_rank, c->link_world, ++c->fence_epoch, c->fence_stream));
@@ -564,6 +742,7 @@ int rt_fence_status(rt_ctx *c, int *timed_out)
     if (!c || !timed_out) return RT_EINVAL;
     if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence_status: call rt_link_peers first");
     CU(c, cudaSetDevice(c->cfg.device));
+    for (int i = 0; i < 2; i++) if (c->fstream[i]) CU(c, cudaStreamSynchronize(c->fstream[i]));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaStreamSynchronize(c->fence_stream));
     unsigned long long st = 0;
@@ -661,16 +840,16 @@ static int plane_ptr(rt_ctx *c, int buffer, int slot, void **ptr, size_t *elem)
     const bool ringed = (buffer == RT_BUF_COLOR || buffer == RT_BUF_NORMAL || buffer == RT_BUF_DEPTH ||
                          buffer == RT_BUF_DEPTH_XY || buffer == RT_BUF_DEPTH_W);
     if (ringed && (slot < 0 || slot >= c->cfg.num_frames)) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
-    const size_t off = ringed ? (size_t)slot * c->npix : 0;
+    const size_t off = ringed ? (size_t)c->phys[slot] * c->npix : 0;
     switch (buffer) {
     case RT_BUF_COLOR: *ptr = c->ring_color + off; *elem = 16; return RT_OK;
     case RT_BUF_NORMAL: *ptr = c->ring_normal + off; *elem = 16; return RT_OK;
     case RT_BUF_DEPTH_XY: *ptr = c->ring_depth_xy + off; *elem = 8; return RT_OK;
     case RT_BUF_DEPTH_W: *ptr = c->ring_depth_w + off; *elem = 4; return RT_OK;
-    case RT_BUF_HIT_INDEX: *ptr = c->hit; *elem = 4; return RT_OK;
-    case RT_BUF_RAW_COLOR: *ptr = c->raw; *elem = 16; return RT_OK;
+    case RT_BUF_HIT_INDEX: *ptr = c->hit[c->last_par]; *elem = 4; return RT_OK;
+    case RT_BUF_RAW_COLOR: *ptr = c->raw[c->last_par]; *elem = 16; return RT_OK;
     case RT_BUF_IMAGE: // img_output == pixels[slot of the last frame] (ao_compute.glsl:338-339)
-        *ptr = c->ring_color + (size_t)c->last_slot * c->npix; *elem = 16; return RT_OK;
+        *ptr = c->ring_color + (size_t)c->phys[c->last_slot] * c->npix; *elem = 16; return RT_OK;
     default: return fail(c, RT_EINVAL, "unknown buffer %d", buffer);
     }
 }
@@ -679,6 +858,7 @@ int rt_device_ptr(rt_ctx *c, int buffer, int slot, void **out_ptr, size_t *out_b
 {
     if (!c || !out_ptr) return RT_EINVAL;
     if (buffer == RT_BUF_DEPTH) return fail(c, RT_EINVAL, "rt_device_ptr: depth is stored as RT_BUF_DEPTH_XY + RT_BUF_DEPTH_W planes");
+    if (c->pipeline) { CU(c, cudaSetDevice(c->cfg.device)); CU(c, join_frames(c)); mark_fork(c); }   // the caller may write through it
     size_t elem = 0;
     int rc = plane_ptr(c, buffer, slot, out_ptr, &elem);
     if (rc == RT_OK && out_bytes) *out_bytes = elem * c->npix;
@@ -690,12 +870,13 @@ int rt_download(rt_ctx *c, int buffer, int slot, int layout, void *host, size_t 
     if (!c || !host) return RT_EINVAL;
     if (layout != RT_LAYOUT_ROW_MAJOR && layout != RT_LAYOUT_REFERENCE) return fail(c, RT_EINVAL, "rt_download: bad layout");
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     const void *src = nullptr;
     size_t elem = 16;
     if (buffer == RT_BUF_DEPTH) {
         if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
         if (bytes != c->npix * 16) return fail(c, RT_EINVAL, "rt_download: expected %zu bytes, got %zu", c->npix * 16, bytes);
-        const size_t off = (size_t)slot * c->npix;
+        const size_t off = (size_t)c->phys[slot] * c->npix;
         if (layout == RT_LAYOUT_ROW_MAJOR) {
             CU(c, launch_expand_depth(c->ring_depth_xy + off, c->ring_depth_w + off, (float4 *)c->staging, c->npix, c->stream));
             src = c->staging;
@@ -732,6 +913,7 @@ int rt_download_async(rt_ctx *c, int buffer, int slot, void *pinned_host, size_t
 {
     if (!c || !pinned_host) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     void *p = nullptr;
     size_t elem = 0;
     if (buffer == RT_BUF_DEPTH) return fail(c, RT_EINVAL, "rt_download_async: depth needs rt_download");
@@ -748,6 +930,7 @@ int rt_download_rgba8_async(rt_ctx *c, int slot, void *pinned_host, size_t bytes
     if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
     if (bytes != c->npix * 4) return fail(c, RT_EINVAL, "rt_download_rgba8_async: expected %zu bytes, got %zu", c->npix * 4, bytes);
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     // Two alternating halves of a device buffer of its own (rt_download / rt_upload use `staging`).  The conversion runs on the context's stream (after the
     // frame's kernels); the PCIe copy runs on an internal copy stream behind an event, so it overlaps the next
     // frame's kernels; a half is converted into again only after the copy that last read it has finished.
@@ -757,7 +940,7 @@ int rt_download_rgba8_async(rt_ctx *c, int slot, void *pinned_host, size_t bytes
     c->rgba8_flip ^= 1;
     uchar4 *dst = c->rgba8 + (size_t)h * half;
     if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));
-    CU(c, launch_quantize_rgba8(c->ring_color + (size_t)slot * c->npix, dst, c->npix, c->stream));
+    CU(c, launch_quantize_rgba8(c->ring_color + (size_t)c->phys[slot] * c->npix, dst, c->npix, c->stream));
     CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
     CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
     CU(c, cudaMemcpyAsync(pinned_host, dst, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
@@ -772,11 +955,12 @@ int rt_download_color_overlapped(rt_ctx *c, int slot, void *pinned_host, size_t 
     if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
     if (bytes != c->npix * 16) return fail(c, RT_EINVAL, "rt_download_color_overlapped: expected %zu bytes, got %zu", c->npix * 16, bytes);
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     const int h = c->rgba8_flip;    // same two event slots as the 8-bit read-back: rt_readback_wait covers both
     c->rgba8_flip ^= 1;
     CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
     CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
-    CU(c, cudaMemcpyAsync(pinned_host, c->ring_color + (size_t)slot * c->npix, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    CU(c, cudaMemcpyAsync(pinned_host, c->ring_color + (size_t)c->phys[slot] * c->npix, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
     CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
     c->copy_pending[h] = true;
     return RT_OK;
@@ -791,6 +975,7 @@ int rt_frame_download_overlapped(rt_ctx *c, const void *frame, int y0, int rows,
     if (bytes != (size_t)rows * row_bytes)
         return fail(c, RT_EINVAL, "rt_frame_download_overlapped: expected %zu bytes, got %zu", (size_t)rows * row_bytes, bytes);
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     const int h = c->rgba8_flip;
     c->rgba8_flip ^= 1;
     CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
@@ -807,12 +992,13 @@ int rt_band_to_frame_overlapped(rt_ctx *c, int slot, void *frame)
     if (!c || !frame) return RT_EINVAL;
     if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     const int h = c->rgba8_flip;
     c->rgba8_flip ^= 1;
     CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
     CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
     // contiguous rows on both sides; `frame` may be an imported mapping: the copy engine moves it over NVLink
-    CU(c, cudaMemcpyAsync((float4 *)frame + (size_t)c->cfg.band_y0 * c->cfg.width, c->ring_color + (size_t)slot * c->npix,
+    CU(c, cudaMemcpyAsync((float4 *)frame + (size_t)c->cfg.band_y0 * c->cfg.width, c->ring_color + (size_t)c->phys[slot] * c->npix,
                           c->npix * 16, cudaMemcpyDefault, c->copy_stream));
     CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
     c->copy_pending[h] = true;
@@ -847,6 +1033,8 @@ int rt_upload(rt_ctx *c, int buffer, int slot, int layout, const void *host, siz
         return fail(c, RT_EINVAL, "rt_upload: buffer %d is not writable", buffer);
     if (bytes != c->npix * 16) return fail(c, RT_EINVAL, "rt_upload: expected %zu bytes, got %zu", c->npix * 16, bytes);
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
+    mark_fork(c);
     float4 *tmp = nullptr;
     CU(c, cudaMalloc((void **)&tmp, bytes));
     cudaError_t e = cudaMemcpyAsync(tmp, host, bytes, cudaMemcpyHostToDevice, c->stream);
@@ -860,7 +1048,7 @@ int rt_upload(rt_ctx *c, int buffer, int slot, int layout, const void *host, siz
         if (buffer == RT_BUF_DEPTH) {
             if (slot < 0 || slot >= c->cfg.num_frames) rc = fail(c, RT_EINVAL, "slot %d outside the ring", slot);
             else {
-                const size_t off = (size_t)slot * c->npix;
+                const size_t off = (size_t)c->phys[slot] * c->npix;
                 e = launch_split_depth(rowmajor, c->ring_depth_xy + off, c->ring_depth_w + off, c->npix, c->stream);
             }
         } else {
@@ -881,13 +1069,17 @@ int rt_reset_ring(rt_ctx *c)
 {
     if (!c) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
-    const size_t ring = c->npix * c->cfg.num_frames;
+    const size_t ring = c->npix * (c->cfg.num_frames + 2);
+    CU(c, join_frames(c));
+    mark_fork(c);
     CU(c, cudaMemsetAsync(c->ring_color, 0, ring * sizeof(float4), c->stream));
     CU(c, cudaMemsetAsync(c->ring_normal, 0, ring * sizeof(float4), c->stream));
     CU(c, cudaMemsetAsync(c->ring_depth_xy, 0, ring * sizeof(float2), c->stream));
     CU(c, cudaMemsetAsync(c->ring_depth_w, 0, ring * sizeof(float), c->stream));
-    CU(c, cudaMemsetAsync(c->raw, 0, c->npix * sizeof(float4), c->stream));
-    CU(c, cudaMemsetAsync(c->hit, 0, c->npix * sizeof(int), c->stream));
+    for (int i = 0; i < 2; i++) {
+        CU(c, cudaMemsetAsync(c->raw[i], 0, c->npix * sizeof(float4), c->stream));
+        CU(c, cudaMemsetAsync(c->hit[i], 0, c->npix * sizeof(int), c->stream));
+    }
     c->frame_pending_post = false;
     return RT_OK;
 }
@@ -896,6 +1088,7 @@ int rt_get_stats(rt_ctx *c, rt_stats *out)
 {
     if (!c || !out) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
     const size_t bytes = STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long);
     CU(c, cudaMemcpyAsync(c->stats_host, c->stats, bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
@@ -910,8 +1103,8 @@ int rt_get_stats(rt_ctx *c, rt_stats *out)
     out->pp_nonbackground = t[ST_PP_NONBACKGROUND]; out->pp_hist_evaluated = t[ST_PP_HIST_EVALUATED];
     out->pp_hist_accepted = t[ST_PP_HIST_ACCEPTED];
     float ms = 0.0f;
-    if (c->timing && c->ev_trace_valid && cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) out->ms_trace_last = ms;
-    if (c->timing && c->ev_post_valid && cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]) == cudaSuccess) out->ms_post_last = ms;
+    if (c->timing && c->ev_trace_valid && cudaEventElapsedTime(&ms, c->ev[c->ev_parity][0], c->ev[c->ev_parity][1]) == cudaSuccess) out->ms_trace_last = ms;
+    if (c->timing && c->ev_post_valid && cudaEventElapsedTime(&ms, c->ev[c->ev_parity][2], c->ev[c->ev_parity][3]) == cudaSuccess) out->ms_post_last = ms;
     cudaGetLastError();
     return RT_OK;
 }
@@ -920,6 +1113,8 @@ int rt_reset_stats(rt_ctx *c)
 {
     if (!c) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
+    mark_fork(c);
     CU(c, cudaMemsetAsync(c->stats, 0, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long), c->stream));
     return RT_OK;
 }

@@ -315,8 +315,8 @@ __global__ void rt_halo_pack_kernel(const __grid_constant__ PostParams q)
 __device__ __forceinline__ void halo_pack_rows(const PostParams &q, int x)
 {
     const size_t plane = (size_t)q.rows * q.W;
-    const float4 *nslot = q.ring_normal + (size_t)q.slot * plane;
-    const float2 *dslot = q.ring_depth_xy + (size_t)q.slot * plane;
+    const float4 *nslot = q.ring_normal + (size_t)q.phys[q.slot] * plane;
+    const float2 *dslot = q.ring_depth_xy + (size_t)q.phys[q.slot] * plane;
     if (q.send_lo) {
         HaloRow lo = halo_row_view(q.send_lo, q.W);
         lo.color[x] = q.raw[x];
@@ -333,13 +333,13 @@ __device__ __forceinline__ void halo_pack_rows(const PostParams &q, int x)
             hi.normal[x] = nslot[top + x - 1];
             hi.depth[x] = dslot[top + x - 1];
         } else if (q.slot >= 1) {
-            const size_t last = (size_t)(q.slot - 1) * plane + top + q.W - 1;
+            const size_t last = (size_t)q.phys[q.slot - 1] * plane + top + q.W - 1;
             hi.color[0] = q.ring_color[last];
             hi.normal[0] = q.ring_normal[last];
             hi.depth[0] = q.ring_depth_xy[last];
         } else {
             // slot 0, x 0: one element before each array = the last element of the array before it
-            const size_t last = (size_t)(q.NF - 1) * plane + top + q.W - 1;
+            const size_t last = (size_t)q.phys[q.NF - 1] * plane + top + q.W - 1;
             hi.color[0] = q.rand_last;          // pixels[-1]  = rand_buffer[2*AA-1]
             hi.normal[0] = q.ring_color[last];  // normals[-1] = pixels[NF-1][W-1][H-1]
             float4 n = q.ring_normal[last];     // depth[-1]   = normals_buffer[NF-1][W-1][H-1]
@@ -446,8 +446,8 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
         const int y = q.y0 + yl;
         const size_t plane = (size_t)q.rows * q.W;
         const size_t pix = (size_t)yl * q.W + x;
-        const float4 *nslot = q.ring_normal + (size_t)q.slot * plane;
-        const float2 *dslot = q.ring_depth_xy + (size_t)q.slot * plane;
+        const float4 *nslot = q.ring_normal + (size_t)q.phys[q.slot] * plane;
+        const float2 *dslot = q.ring_depth_xy + (size_t)q.phys[q.slot] * plane;
         float4 color = q.raw[pix];
         const float4 nn = nslot[pix];
         if (nn.w > 0.99f) {
@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             auto hist_off = [&](int i) -> size_t {
                 int cf = q.slot - i;
                 if (cf < 0) cf += q.NF;
-                return (size_t)cf * plane + pix;
+                return (size_t)q.phys[cf] * plane + pix;
             };
 #pragma unroll
             for (int b = 0; b < PP_BATCH; b++) {
@@ -523,12 +523,13 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
                     // [f][W][y] is [f+1][0][y]; past the last slot it is the next array's [0][0][y]
                     const size_t col0 = (size_t)yl * q.W;
                     if (q.slot + 1 < q.NF) {
-                        const size_t off = (size_t)(q.slot + 1) * plane + col0;
+                        const size_t off = (size_t)q.phys[q.slot + 1] * plane + col0;
                         R.color = q.ring_color[off]; R.normal = q.ring_normal[off]; R.depth = q.ring_depth_xy[off];
                     } else {
-                        R.color = q.ring_normal[col0];                   // pixels -> normals_buffer[0][0][y]
-                        float2 d0 = q.ring_depth_xy[col0];               // normals -> depth_buffer[0][0][y]
-                        R.normal = make_float4(d0.x, d0.y, 0.0f, q.ring_depth_w[col0]);
+                        const size_t s0 = (size_t)q.phys[0] * plane + col0;
+                        R.color = q.ring_normal[s0];                     // pixels -> normals_buffer[0][0][y]
+                        float2 d0 = q.ring_depth_xy[s0];                 // normals -> depth_buffer[0][0][y]
+                        R.normal = make_float4(d0.x, d0.y, 0.0f, q.ring_depth_w[s0]);
                         R.depth = make_float2(0.0f, 0.0f);               // depth -> past the struct
                     }
                     r = nb_weight(nn, new_depth, new_bounces, R);
@@ -583,7 +584,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             }
             color = div4(add4(scale4(0.9f, color), color_sum), denominator);
         }
-        q.ring_color[(size_t)q.slot * plane + pix] = color; // pixels[new_frame] and img_output
+        q.ring_color[(size_t)q.phys[q.slot] * plane + pix] = color; // pixels[new_frame] and img_output
         gather_store(q.gather, yl, pix, color);             // rt_set_frame_targets: the assembled frame, maybe over NVLink
     }
     // per-warp flush, no block barrier: a warp of background pixels must not wait for its block-mates

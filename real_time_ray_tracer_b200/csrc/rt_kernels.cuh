@@ -109,6 +109,12 @@ struct TraceOut {
     float4 *normal;   // ring normal plane of the slot
     float2 *depth_xy; // ring depth.xy plane of the slot
     float *depth_w;   // ring depth.w plane of the slot
+    // What the slot held BEFORE this frame (the shaders leave normals / depth untouched behind an emissive primary
+    // hit, ao_compute.glsl:199-208): every frame that writes normals / depth goes into a fresh physical slot (see
+    // rt_ctx in rt_capi.cu), so the stale record is read from -- and the normal copied over from -- the old one.
+    const float4 *old_normal;
+    const float2 *old_depth_xy;
+    const float *old_depth_w;
     int *hit;         // hit-index plane
     unsigned long long *stats; // [STAT_STRIPES][STAT_STRIDE]
     int ao_kernel;    // AO_KERNEL_*
@@ -138,7 +144,8 @@ struct PostParams {
     int slot, edge_mode;
     int band_index, band_count;
     const float4 *raw;    // aop_compute output of this frame
-    float4 *ring_color;   // [NF][rows*W]
+    int phys[RT_MAX_FRAMES]; // ring slot -> physical slot of the planes below (NF + 2 of them; rt_capi.cu)
+    float4 *ring_color;   // [NF + 2][rows*W]
     const float4 *ring_normal;
     const float2 *ring_depth_xy;
     const float *ring_depth_w;

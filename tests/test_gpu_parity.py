@@ -984,3 +984,50 @@ def test_full_size_properties_1080p():
         o.render(2, u, rb, rows=(500, 508))
         assert same_bits(o.get(orc.PIXELS, slot)[500:508], a[500:508])
         o.close()
+
+
+def test_pipelined_frames_are_the_same_bits():
+    """RT_FLAG_PIPELINE: two frames in flight on two internal streams.  A sequence built to hit every ordering rule
+    -- mode-1 runs (the pass of frame k beside the trace of frame k+1), the same ring slot twice in a row, modes 3/4
+    writing their colour in place right after a mode-1 frame, a background change (scene toggle) in the middle, a
+    frame whose second pass is never called -- is rendered WITHOUT any synchronisation in between and every ring
+    slot, the hit indices and the counters are compared with the oracle at the end and at two points in the middle."""
+    W, H, AA = 322, 181, 4
+    sc = Scenario("scene1", keys=("d", "e"))
+    o = orc.Oracle(W, H, AA)
+    o.set_scene(sc.shapes, sc.n)
+    rt = rtb.RayTracer(W, H, AA, flags=rtb.FLAG_PIPELINE)
+    rt.upload_scene(sc.shapes, sc.n)
+    # (mode, slot override or None, postprocess?)
+    plan = [(1, None, True)] * 10 + [(2, None, True), (1, None, True), (3, None, True), (1, None, True), (4, None, True),
+            (4, None, True), (1, 3, True), (1, 3, True), (2, 3, True), (1, None, True), (1, None, False), (1, None, True),
+            (1, None, True)] + [(1, None, True)] * 9
+    check_at = {9, 22, len(plan) - 1}
+    sc6 = Scenario("scene6")
+    for k, (mode, slot_o, post) in enumerate(plan):
+        slot, u, rb = sc.next(mode, AA)
+        if slot_o is not None:
+            u = u.copy(); u[0, 1] = slot_o; slot = slot_o
+        if k == 14:   # another scene, black background, from here on
+            rt.upload_scene(sc6.shapes, sc6.n)
+            o.set_scene(sc6.shapes, sc6.n)
+            sc.bg, sc.n = sc6.bg.copy(), sc6.n
+        if k >= 14:
+            u = u.copy(); u[0, 2] = sc6.n; u[6] = sc6.bg
+        rt.render_frame(mode, u, rb)
+        o.render(mode, u, rb)
+        if mode == 1 and post:
+            rt.postprocess()
+            o.postprocess()
+        if k in check_at:
+            for s_ in range(8):
+                for buf, which, name in ((rtb.BUF_COLOR, orc.PIXELS, "color"), (rtb.BUF_NORMAL, orc.NORMALS, "normal"),
+                                         (rtb.BUF_DEPTH, orc.DEPTH, "depth")):
+                    got, want = rt.download(buf, s_), o.get(which, s_)
+                    assert same_bits(got, want), f"after frame {k}, slot {s_} {name}: {diff_report(got, want)}"
+            assert np.array_equal(rt.download(rtb.BUF_HIT_INDEX), o.get(orc.HIT_INDEX)), f"after frame {k}: hit index"
+    st, so = rt.stats(), o.stats()
+    for kk, v in so.items():
+        assert st[kk] == v, (kk, st[kk], v)
+    rt.close()
+    o.close()
