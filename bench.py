@@ -302,7 +302,7 @@ class Setup:
         if self.direct is not None:
             self.direct.split = False
             if self.direct.halo_direct and not args.mode1_store_gather:
-                self.direct.mode1_gather = "copy"
+                self.direct.mode1_gather = args.mode1_gather
         self.br = bands.BandedRenderer(eng, W, H, plan, rank, world, direct=self.direct)
         # rank 0 assembles frames in two alternating buffers so the gather of frame k overlaps the trace of k+1
         self.fulls = [env.torch.empty(W * H * 4, dtype=env.torch.float32, device=env.dev()) for _ in range(2)] \
@@ -332,8 +332,10 @@ class Setup:
             return "none"
         if d is None:
             return "nccl p2p"
-        if self.fr.mode == 1 and d.mode1_gather == "copy":
-            g = "band copies into rank 0's image under the next frame's trace kernel, closed by one rt_fence at the end"
+        if self.fr.mode == 1 and d.mode1_gather in ("copy", "copy8", "none"):
+            what = {"copy": "float4 band copies", "copy8": "8-bit RGBA band copies (quantised on the device)",
+                    "none": "NO gather (diagnostic): nothing"}[d.mode1_gather]
+            g = what + " into rank 0's image under the next frame's trace kernel, closed by one rt_fence at the end"
         else:
             g = "direct NVLink stores into rank 0's image, one rt_fence per frame on the library's fence stream"
         return g + (f"; halo rows stored into the neighbours and awaited inside the post-processing kernel"
@@ -344,8 +346,10 @@ class Setup:
         rt_fence kernel of a frame whose bands the kernels store into the frame image"""
         n = 3 if self.fr.mode == 1 else 1
         d = self.direct
-        if d is not None and d.halo_direct and not (self.fr.mode == 1 and d.mode1_gather == "copy"):
+        if d is not None and d.halo_direct and not (self.fr.mode == 1 and d.mode1_gather in ("copy", "copy8", "none")):
             n += 1
+        if d is not None and self.fr.mode == 1 and d.mode1_gather == "copy8":
+            n += 1      # the quantisation kernel
         return n
 
     def close(self):
@@ -610,10 +614,15 @@ def parity_check(env: Env, su: Setup, frames: int = 9) -> dict:
     W, H = fr.W, fr.H
     seq = Frames(fr.name)
     ins = [seq.next() for _ in range(frames)]
+    run_gather = su.direct.mode1_gather if su.direct is not None else None
+    check8 = world > 1 and fr.mode == 1 and run_gather == "copy8"
+    extra = seq.next() if check8 else None       # one more frame through the 8-bit gather the timed loop used
     rt.reset_ring()
     env.barrier()
     if su.direct is not None:
         su.br.frame_fence = "stream"
+        if run_gather in ("copy8", "none"):
+            su.direct.mode1_gather = "copy"      # the float4 image is the stricter check
     last_k = None
     for (slot, u, rb) in ins:
         last_k = su.br.frame_k
@@ -621,7 +630,7 @@ def parity_check(env: Env, su: Setup, frames: int = 9) -> dict:
     su.drain()
     env.barrier()
     slot = ins[-1][0]
-    got = None
+    got = got8 = None
     if rank == 0:
         if world == 1:
             got = rt.download(rtb.BUF_COLOR, slot)
@@ -629,6 +638,15 @@ def parity_check(env: Env, su: Setup, frames: int = 9) -> dict:
             got = su.direct.frame(last_k).cpu().numpy().reshape(H, W, 4)
         else:
             got = su.fulls[(su.pending["k"] - 1) & 1].cpu().numpy().reshape(H, W, 4)
+    if su.direct is not None:
+        su.direct.mode1_gather = run_gather
+    if check8:
+        k8 = su.br.frame_k
+        su.step(extra)
+        su.drain()
+        env.barrier()
+        if rank == 0:
+            got8 = su.direct.frame(k8).view(torch.uint8)[:W * H * 4].cpu().numpy().reshape(H, W, 4)
     res = {"frames": frames, "vs_single_gpu": None, "vs_oracle_rows": 0, "ok": True}
     if rank == 0:
         same = lambda a, b: bool(np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32)))  # noqa: E731
@@ -640,9 +658,17 @@ def parity_check(env: Env, su: Setup, frames: int = 9) -> dict:
                     if fr.mode == 1:
                         one.postprocess()
                 want = one.download(rtb.BUF_COLOR, slot)
+                if check8:
+                    one.render_frame(fr.mode, extra[1], extra[2])
+                    one.postprocess()
+                    want8 = one.download_rgba8(extra[0])
             ok = same(got, want)
             res["vs_single_gpu"] = "bit-exact" if ok else f"{int((got.view(np.uint32) != want.view(np.uint32)).sum())} words differ"
             res["ok"] = res["ok"] and ok
+            if check8:
+                ok8 = bool(np.array_equal(got8, want8))
+                res["rgba8_gather_vs_single_gpu"] = "byte-exact" if ok8 else f"{int((got8 != want8).sum())} bytes differ"
+                res["ok"] = res["ok"] and ok8
         else:
             res["vs_single_gpu"] = "n/a (one GPU: the banded path is the whole-frame context)"
         from oracle import oracle as orc
@@ -1028,6 +1054,9 @@ def main():
     ap.add_argument("--mode1-store-gather", action="store_true",
                     help="N > 1, mode 1: the post-processing kernel stores into rank 0's image (NVLink-ingress-bound at "
                          "8 GPUs) instead of the copy that overlaps the next frame's trace kernel")
+    ap.add_argument("--mode1-gather", default="copy", choices=["copy", "copy8", "none"],
+                    help="N > 1, mode 1, device-timed loop: what travels to rank 0 under the next frame's trace kernel: the "
+                         "float4 colour bands, the 8-bit displayable image, or nothing (compute only, diagnostic)")
     ap.add_argument("--e2e-own-bands", action="store_true",
                     help="N > 1 e2e: every rank reads back its own (compute-balanced) band instead of a share "
                          "of the frame assembled with rt_set_frame_targets")

@@ -51,6 +51,7 @@ def lib():
         L.rto_destroy.argtypes = [C.c_void_p]
         L.rto_set_threads.argtypes = [C.c_void_p, C.c_int]
         L.rto_set_phong_gbuffer.argtypes = [C.c_void_p, C.c_int]
+        L.rto_set_rectangles.argtypes = [C.c_void_p, C.c_int]
         L.rto_set_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.rto_render.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.rto_render_rows.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
@@ -74,7 +75,7 @@ class Oracle:
     converted from the reference's x-major [W][H] struct layout."""
 
     def __init__(self, width, height, aa=4, recursion_depth=20, num_frames=8, edge_mode=0, threads=None,
-                 phong_gbuffer=False):
+                 phong_gbuffer=False, rectangles=False):
         self.cfg = RtoConfig(width, height, aa, recursion_depth, num_frames, edge_mode)
         self.L = lib()
         self.h = self.L.rto_create(C.byref(self.cfg))
@@ -82,6 +83,8 @@ class Oracle:
             raise MemoryError("rto_create failed")
         if phong_gbuffer:
             self.L.rto_set_phong_gbuffer(self.h, 1)
+        if rectangles:
+            self.L.rto_set_rectangles(self.h, 1)
         self.L.rto_set_threads(self.h, threads if threads else len(os.sched_getaffinity(0)))
         self.W, self.H, self.AA, self.NF = width, height, aa, num_frames
 

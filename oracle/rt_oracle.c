@@ -38,6 +38,7 @@
 #endif
 
 #define SPHERE_ID 1
+#define RECTANGLE_ID 3
 #define PLANE_ID 5
 #define MAX_SHAPES 10
 #define HEADER_VEC4 7
@@ -77,6 +78,7 @@ typedef struct rto_ctx {
     rto_stats stats;
     int nthreads;
     int phong_gbuffer;      /* extension (README to-do): modes 3/4 also write normals/depth of the first hit */
+    int rectangles;         /* extension (README to-do): the rectangle records are intersected */
     unsigned char *pathlen; /* optional analysis aid: segments walked per (pixel, sample), [y][x][aa] */
 } rto_ctx;
 
@@ -138,6 +140,12 @@ void rto_destroy(rto_ctx *c)
  * write, with one sample. */
 void rto_set_phong_gbuffer(rto_ctx *c, int on) { if (c) c->phong_gbuffer = on; }
 
+/* Extension beyond the shaders: the reference's host packs rectangle records (src/main.cpp:444-467,
+ * src/geom_objs/rectangle.h:8-22) and its eval_ray has the call commented out because no rectangle_eval_ray
+ * exists anywhere (ao_compute.glsl:130-133).  With on != 0 the record is intersected as defined at
+ * rectangle_eval_ray below; off (default) = the shaders' behaviour: id 3 is never hit. */
+void rto_set_rectangles(rto_ctx *c, int on) { if (c) c->rectangles = on; }
+
 /* analysis aid (schedule simulations in DESIGN.md): caller-owned buffer of W*H*AA bytes, or NULL */
 void rto_set_pathlen_buffer(rto_ctx *c, unsigned char *buf) { if (c) c->pathlen = buf; }
 
@@ -186,11 +194,32 @@ static inline float plane_eval_ray(const rto_ctx *c, rtr_v3 pos, rtr_v3 dir, int
     return rtr_dot3(normal, rtr_sub3(p0, pos)) / denom;
 }
 
+/* rectangle_eval_ray -- DEFINED HERE (the reference has none).  Record (src/main.cpp:455-466): [0] = (normal, 0),
+ * [1] = (up, emissive), [2] = (right, 0), [3] = (lower left vertex, reflectivity), [4] = (colour, 3).
+ * The plane test of plane_eval_ray with p0 = the lower left vertex, then the hit point's coordinates along the two
+ * edges: a = dot(p - llv, right) / dot(right, right), b = dot(p - llv, up) / dot(up, up); a hit needs both in
+ * [0, 1].  Every operation binary32, dot() as everywhere else, p = pos + t * dir as a multiply then an add. */
+static inline float rectangle_eval_ray(const rto_ctx *c, rtr_v3 pos, rtr_v3 dir, int i)
+{
+    rtr_v3 normal = rtr_xyz(SHAPE(c, i, 0));
+    float denom = rtr_dot3(normal, dir);
+    if (denom < 0.001f && denom > -0.001f) return -1.0f;
+    rtr_v3 llv = rtr_xyz(SHAPE(c, i, 3));
+    float t = rtr_dot3(normal, rtr_sub3(llv, pos)) / denom;
+    rtr_v3 d = rtr_sub3(rtr_add3(pos, rtr_scale3(t, dir)), llv);
+    rtr_v3 right = rtr_xyz(SHAPE(c, i, 2)), up = rtr_xyz(SHAPE(c, i, 1));
+    float a = rtr_dot3(d, right) / rtr_dot3(right, right);
+    float b = rtr_dot3(d, up) / rtr_dot3(up, up);
+    if (a < 0.0f || a > 1.0f || b < 0.0f || b > 1.0f) return -1.0f;
+    return t;
+}
+
 static inline float eval_ray(const rto_ctx *c, rtr_v3 pos, rtr_v3 dir, int i)
 {
     int id = (int)SHAPE(c, i, 4).w;
     if (id == SPHERE_ID) return sphere_eval_ray(c, pos, dir, i);
     if (id == PLANE_ID) return plane_eval_ray(c, pos, dir, i);
+    if (id == RECTANGLE_ID && c->rectangles) return rectangle_eval_ray(c, pos, dir, i);
     return -1.0f;
 }
 

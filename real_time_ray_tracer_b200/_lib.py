@@ -44,7 +44,7 @@ EXPORTS = (
     "rt_synchronize", "rt_stream_wait_frames", "rt_set_timing", "rt_upload_scene", "rt_render_frame", "rt_halo_pack", "rt_get_halo",
     "rt_postprocess", "rt_download", "rt_upload", "rt_download_async", "rt_download_rgba8_async", "rt_download_color_overlapped", "rt_readback_wait", "rt_device_ptr", "rt_get_stats",
     "rt_reset_stats", "rt_reset_ring", "rt_debug_eval_math", "rt_measure_fp32_peak",
-    "rt_set_frame_target", "rt_set_frame_targets", "rt_frame_download_overlapped", "rt_stream_wait_readback", "rt_band_to_frame_overlapped", "rt_frame_create", "rt_frame_destroy", "rt_peer_export", "rt_peer_import",
+    "rt_set_frame_target", "rt_set_frame_targets", "rt_frame_download_overlapped", "rt_stream_wait_readback", "rt_band_to_frame_overlapped", "rt_band_to_frame_rgba8_overlapped", "rt_frame_create", "rt_frame_destroy", "rt_peer_export", "rt_peer_import",
     "rt_peer_release", "rt_mailbox_create", "rt_mailbox_destroy", "rt_link_peers", "rt_fence", "rt_fence_async", "rt_fence_join", "rt_fence_status",
 )
 
@@ -93,6 +93,7 @@ def load():
     L.rt_frame_download_overlapped.argtypes = [vp, vp, i32, i32, vp, sz]
     L.rt_stream_wait_readback.argtypes = [vp]
     L.rt_band_to_frame_overlapped.argtypes = [vp, i32, vp]
+    L.rt_band_to_frame_rgba8_overlapped.argtypes = [vp, i32, vp]
     L.rt_frame_create.argtypes = [i32, i32, i32, C.POINTER(vp)]
     L.rt_frame_destroy.argtypes = [i32, vp]
     L.rt_peer_export.argtypes = [i32, vp, C.c_char_p]

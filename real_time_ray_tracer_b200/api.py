@@ -128,6 +128,11 @@ class RayTracer:
         (own or imported), on the library's copy stream"""
         self._check(self.lib.rt_band_to_frame_overlapped(self.h, slot, C.c_void_p(frame_ptr)))
 
+    def band_to_frame_rgba8_overlapped(self, slot: int, frame_ptr: int):
+        """rt_band_to_frame_rgba8_overlapped: this band's colour plane of pixels[slot], quantised to 8-bit RGBA, ->
+        its rows of an 8-bit frame image (own or imported), on the library's copy stream"""
+        self._check(self.lib.rt_band_to_frame_rgba8_overlapped(self.h, slot, C.c_void_p(frame_ptr)))
+
     def stream_wait_readback(self):
         """rt_stream_wait_readback: the context's stream waits (on the device) for the read-backs issued so far"""
         self._check(self.lib.rt_stream_wait_readback(self.h))

@@ -99,6 +99,9 @@ class GpuBandEngine:
     def band_to_frame(self, slot, ptr):
         self.rt.band_to_frame_overlapped(slot, ptr)
 
+    def band_to_frame_rgba8(self, slot, ptr):
+        self.rt.band_to_frame_rgba8_overlapped(slot, ptr)
+
     def fence(self):
         self.rt.fence()
 
@@ -164,7 +167,9 @@ class DirectGather:
         self.split = owners == "rows"   # owners="rows" only: False = gather to rank 0's image after all
         # how a mode-1 frame reaches rank 0's image: "store" = from the post-processing kernel, like the other
         # modes; "copy" = rt_band_to_frame_overlapped after it, overlapping the next frame's trace kernel (the
-        # frame is then complete after the NEXT frame's halo fence, or BandedRenderer.gather_flush)
+        # frame is then complete after the next fence on the stream, or BandedRenderer.gather_flush);
+        # "copy8" = the same with the 8-bit displayable image (rt_band_to_frame_rgba8_overlapped: a quarter of the
+        # bytes; the image occupies the first quarter of the frame buffer); "none" = the bands stay where they are
         self.mode1_gather = "store"
         if owners == "rows":
             if tracer is None:
@@ -326,7 +331,7 @@ class BandedRenderer:
 
     def _copy_gather(self, mode: int) -> bool:
         d = self.direct
-        return (self._post(mode) and self.world > 1 and d is not None and d.mode1_gather == "copy"
+        return (self._post(mode) and self.world > 1 and d is not None and d.mode1_gather in ("copy", "copy8", "none")
                 and not (d.owners == "rows" and d.split))
 
     def exchange_halo(self):
@@ -376,7 +381,10 @@ class BandedRenderer:
             if self._copy:
                 # copy engine, behind the post-processing kernel and under the next frame's trace kernel; the
                 # next fence on this stream (a single-pass frame's, or gather_flush) waits for it and closes the frame
-                self.e.band_to_frame(slot, self.direct.target(self.frame_k))
+                if self.direct.mode1_gather == "copy8":
+                    self.e.band_to_frame_rgba8(slot, self.direct.target(self.frame_k))
+                elif self.direct.mode1_gather == "copy":
+                    self.e.band_to_frame(slot, self.direct.target(self.frame_k))
                 self._copy_pending = True
             else:
                 # the bands are already in (or on their way into) the image(s) of frame_k: fence only

@@ -949,6 +949,29 @@ int rt_download_rgba8_async(rt_ctx *c, int slot, void *pinned_host, size_t bytes
     return RT_OK;
 }
 
+int rt_band_to_frame_rgba8_overlapped(rt_ctx *c, int slot, void *frame8)
+{
+    if (!c || !frame8) return RT_EINVAL;
+    if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
+    CU(c, cudaSetDevice(c->cfg.device));
+    CU(c, join_frames(c));
+    const size_t half = (c->npix + 3) & ~(size_t)3;
+    if (!c->rgba8) CU(c, cudaMalloc((void **)&c->rgba8, 2 * half * sizeof(uchar4)));
+    const int h = c->rgba8_flip;
+    c->rgba8_flip ^= 1;
+    uchar4 *dst = c->rgba8 + (size_t)h * half;
+    if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));
+    CU(c, launch_quantize_rgba8(c->ring_color + (size_t)c->phys[slot] * c->npix, dst, c->npix, c->stream));
+    CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    // contiguous rows on both sides; `frame8` may be an imported mapping: the copy engine moves it over NVLink
+    CU(c, cudaMemcpyAsync((uchar4 *)frame8 + (size_t)c->cfg.band_y0 * c->cfg.width, dst, c->npix * sizeof(uchar4),
+                          cudaMemcpyDefault, c->copy_stream));
+    CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
+    c->copy_pending[h] = true;
+    return RT_OK;
+}
+
 int rt_download_color_overlapped(rt_ctx *c, int slot, void *pinned_host, size_t bytes)
 {
     if (!c || !pinned_host) return RT_EINVAL;
