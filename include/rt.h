@@ -33,6 +33,9 @@ extern "C" {
 
 /* compile-time limits (reference: NUM_SHAPES 10 src/main.cpp:34; AA 4 :31) */
 #define RT_MAX_SHAPES 10
+/* upper bound of rt_config.max_shapes: scenes above RT_MAX_SHAPES objects keep their object table in shared
+ * memory instead of the kernel parameters (no tile test; the object loops are rolled) */
+#define RT_MAX_SHAPES_LIMIT 256
 #define RT_MAX_AA 16
 #define RT_MAX_FRAMES 16
 
@@ -80,7 +83,14 @@ enum {
      * is NOT ordered with the caller's stream any more; every other entry point that touches results (downloads,
      * rt_device_ptr, rt_get_stats, rt_fence, rt_synchronize, ...) first makes the context's stream wait for the
      * frames issued so far.  Device pointers from rt_device_ptr are valid until the next rt_render_frame. */
-    RT_FLAG_PIPELINE = 4
+    RT_FLAG_PIPELINE = 4,
+    /* Extension (reference README to-do): records with id 3 -- rectangles, packed by the reference's
+     * host (src/main.cpp:444-467: [0] = (normal, 0), [1] = (up, emissive), [2] = (right, 0), [3] = (lower left
+     * vertex, reflectivity), [4] = (colour, 3)) but never intersected by its shaders (the call is commented out,
+     * ao_compute.glsl:130-133, and no rectangle_eval_ray exists) -- are intersected: the plane test through the
+     * lower left vertex, then 0 <= dot(p - llv, e) / dot(e, e) <= 1 for both edges e (definition:
+     * oracle/rt_oracle.c rectangle_eval_ray).  Off (0) = the shaders' behaviour: such a record is never hit. */
+    RT_FLAG_RECTANGLES = 8
 };
 
 /* buffers of rt_download / rt_upload / rt_device_ptr */
@@ -136,7 +146,9 @@ typedef struct rt_config {
     int32_t band_index;      /* position of this band in the frame, 0 .. band_count-1 */
     int32_t band_count;      /* number of bands the frame is split into (1 = no halo exchange) */
     int32_t flags;           /* RT_FLAG_* */
-    int32_t reserved[4];     /* must be 0 */
+    int32_t max_shapes;      /* most objects rt_upload_scene accepts: 0 = RT_MAX_SHAPES (the reference's
+                                NUM_SHAPES), up to RT_MAX_SHAPES_LIMIT */
+    int32_t reserved[3];     /* must be 0 */
 } rt_config;
 
 /* ray / work counters accumulated since rt_reset_stats; "ray" = one closest-hit traversal of the

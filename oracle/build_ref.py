@@ -17,6 +17,14 @@ translation unit lives in a temporary directory and is deleted):
     indexing, same storage);
   * every floating literal gets an ``f`` suffix (GLSL literals are binary32).
 
+A second flavour (``rectangles=True``, libglsl_ref_<W>x<H>_aa<AA>_rect.so) additionally ENABLES the branch the
+shaders keep commented out in eval_ray (ao_compute.glsl:130-133 and the same lines of aop_compute / p_compute /
+h_compute) and supplies the one function that branch calls and the reference never wrote, rectangle_eval_ray, as
+GLSL text (RECTANGLE_EVAL_RAY_GLSL below: the definition SURVEY 8(f) / include/rt.h RT_FLAG_RECTANGLES give), and
+gives the hit's `vec3 normal;` -- which the shaders leave unassigned for "other shapes" -- the record's normal.
+Everything around it -- the object loop, shading, the G-buffer -- stays the reference's text, so the oracle's
+handling of a rectangle hit is pinned by it; only the intersection itself is this repo's definition.
+
 It is the strongest available stand-in for "the reference's GLSL run on a CPU": there is no
 GL/Vulkan stack or software rasteriser on this machine or on the GPU box.  The library is
 only ever loaded by tests/ and by bench.py's reference arm.
@@ -41,6 +49,63 @@ SHADERS = [  # (namespace, file, writes image?)
     ("sh_p", "p_compute.glsl"),
     ("sh_h", "h_compute.glsl"),
 ]
+
+# the missing function, in the shaders' own dialect (modelled on plane_eval_ray, ao_compute.glsl:109-117); record layout
+# src/main.cpp:455-466: [0] = (normal, 0), [1] = (up, emissive), [2] = (right, 0), [3] = (lower left vertex, refl)
+RECTANGLE_EVAL_RAY_GLSL = """
+float rectangle_eval_ray(vec3 pos, vec3 dir, int shape_index)
+{
+	vec3 normal = simple_shapes[shape_index][0].xyz;
+	float denom = dot(normal, dir);
+	if (denom < 0.001 && denom > -0.001)
+		return -1;
+	vec3 llv = simple_shapes[shape_index][3].xyz;
+	float t = dot(normal, llv - pos) / denom;
+	vec3 d = (pos + t * dir) - llv;
+	vec3 right = simple_shapes[shape_index][2].xyz;
+	vec3 up = simple_shapes[shape_index][1].xyz;
+	float a = dot(d, right) / dot(right, right);
+	float b = dot(d, up) / dot(up, up);
+	if (a < 0.0 || a > 1.0 || b < 0.0 || b > 1.0)
+		return -1;
+	return t;
+}
+"""
+
+
+def enable_rectangles(text: str) -> str:
+    """uncomment `// if (shape_id == RECTANGLE_ID) { return rectangle_eval_ray(...); }` and put the function
+    in front of eval_ray"""
+    lines = text.splitlines()
+    out = []
+    i = 0
+    done = False
+    normals = 0
+    while i < len(lines):
+        if re.match(r"\s*//\s*if \(shape_id == RECTANGLE_ID\)", lines[i]):
+            blk = lines[i:i + 4]
+            if not (re.match(r"\s*//\s*\{", blk[1]) and "rectangle_eval_ray" in blk[2] and re.match(r"\s*//\s*\}", blk[3])):
+                raise RuntimeError("the commented-out rectangle branch does not look as expected")
+            out += [re.sub(r"^(\s*)//\s?", r"\1", b) for b in blk]
+            i += 4
+            done = True
+            continue
+        if re.match(r"float eval_ray\(", lines[i]):
+            out += RECTANGLE_EVAL_RAY_GLSL.splitlines()
+        # the hit's normal: the shaders leave `vec3 normal;` unassigned for "other shapes... not yet implemented"
+        # (ao_compute.glsl:211-220, p_compute.glsl:198-203, h_compute.glsl:225-230); a rectangle's is record [0]
+        m = re.match(r"(\s*)vec3 normal;\s*$", lines[i])
+        if m:
+            out.append(m.group(1) + "vec3 normal = simple_shapes[ind][0].xyz;")
+            normals += 1
+            i += 1
+            continue
+        out.append(lines[i])
+        i += 1
+    if not done or normals != 1:
+        raise RuntimeError("no commented-out rectangle branch / `vec3 normal;` declaration found")
+    return "\n".join(out)
+
 
 _FLOAT_LIT = re.compile(r"(?<![\w.])(\d+\.\d*|\.\d+)(?![\w.])")
 
@@ -212,13 +277,14 @@ int glslref_max_threads(void)
 """
 
 
-def lib_path(width: int, height: int, aa: int) -> str:
-    return os.path.join(OUT_DIR, f"libglsl_ref_{width}x{height}_aa{aa}.so")
+def lib_path(width: int, height: int, aa: int, rectangles: bool = False) -> str:
+    return os.path.join(OUT_DIR, f"libglsl_ref_{width}x{height}_aa{aa}{'_rect' if rectangles else ''}.so")
 
 
-def build(width: int = 440, height: int = 330, aa: int = 4, force: bool = False, verbose: bool = False) -> str:
+def build(width: int = 440, height: int = 330, aa: int = 4, force: bool = False, verbose: bool = False,
+          rectangles: bool = False) -> str:
     """Build (if needed) and return the library path.  Requires /root/reference."""
-    out = lib_path(width, height, aa)
+    out = lib_path(width, height, aa, rectangles)
     if os.path.exists(out) and not force:
         return out
     if not os.path.isdir(REF_RES):
@@ -227,7 +293,10 @@ def build(width: int = 440, height: int = 330, aa: int = 4, force: bool = False,
     parts = ['#include "glsl_shim.h"\n']
     for ns, fn in SHADERS:
         with open(os.path.join(REF_RES, fn)) as f:
-            parts.append(transform(f.read(), ns, width, height, aa))
+            text = f.read()
+        if rectangles and fn != "aop_postprocessing.glsl":
+            text = enable_rectangles(text)
+        parts.append(transform(text, ns, width, height, aa))
     parts.append(HARNESS)
     with tempfile.TemporaryDirectory(prefix="glslref_") as td:
         src = os.path.join(td, "glsl_ref_tu.cpp")
@@ -250,5 +319,6 @@ if __name__ == "__main__":
     ap.add_argument("--height", type=int, default=330)
     ap.add_argument("--aa", type=int, default=4)
     ap.add_argument("--force", action="store_true")
+    ap.add_argument("--rectangles", action="store_true")
     a = ap.parse_args()
-    print(build(a.width, a.height, a.aa, a.force, verbose=True))
+    print(build(a.width, a.height, a.aa, a.force, verbose=True, rectangles=a.rectangles))

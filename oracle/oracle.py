@@ -48,6 +48,8 @@ def lib():
         L = C.CDLL(build_oracle())
         L.rto_create.restype = C.c_void_p
         L.rto_create.argtypes = [C.POINTER(RtoConfig)]
+        L.rto_create_ex.restype = C.c_void_p
+        L.rto_create_ex.argtypes = [C.POINTER(RtoConfig), C.c_int]
         L.rto_destroy.argtypes = [C.c_void_p]
         L.rto_set_threads.argtypes = [C.c_void_p, C.c_int]
         L.rto_set_phong_gbuffer.argtypes = [C.c_void_p, C.c_int]
@@ -75,10 +77,10 @@ class Oracle:
     converted from the reference's x-major [W][H] struct layout."""
 
     def __init__(self, width, height, aa=4, recursion_depth=20, num_frames=8, edge_mode=0, threads=None,
-                 phong_gbuffer=False, rectangles=False):
+                 phong_gbuffer=False, rectangles=False, max_shapes=10):
         self.cfg = RtoConfig(width, height, aa, recursion_depth, num_frames, edge_mode)
         self.L = lib()
-        self.h = self.L.rto_create(C.byref(self.cfg))
+        self.h = self.L.rto_create_ex(C.byref(self.cfg), max_shapes)
         if not self.h:
             raise MemoryError("rto_create failed")
         if phong_gbuffer:
@@ -164,8 +166,8 @@ def eval_math(kind, a, b=None):
 PROGRAMS = {"ao_compute": 0, "aop_compute": 1, "aop_postprocessing": 2, "p_compute": 3, "h_compute": 4}
 
 
-def glsl_ref_lib_path(width, height, aa):
-    return os.path.join(HERE, "_ref", f"libglsl_ref_{width}x{height}_aa{aa}.so")
+def glsl_ref_lib_path(width, height, aa, rectangles=False):
+    return os.path.join(HERE, "_ref", f"libglsl_ref_{width}x{height}_aa{aa}{'_rect' if rectangles else ''}.so")
 
 
 class GlslRef:
@@ -173,13 +175,14 @@ class GlslRef:
 
     Size and AA are compile-time constants of the library (as they are of the shaders)."""
 
-    def __init__(self, width=440, height=330, aa=4, build=True):
-        path = glsl_ref_lib_path(width, height, aa)
+    def __init__(self, width=440, height=330, aa=4, build=True, rectangles=False):
+        """``rectangles``: the flavour with the shaders' commented-out rectangle branch enabled (build_ref.py)"""
+        path = glsl_ref_lib_path(width, height, aa, rectangles)
         if not os.path.exists(path):
             if not build:
                 raise FileNotFoundError(path)
             from . import build_ref
-            path = build_ref.build(width, height, aa)
+            path = build_ref.build(width, height, aa, rectangles=rectangles)
         L = C.CDLL(path)
         L.glslref_create.restype = C.c_void_p
         L.glslref_destroy.argtypes = [C.c_void_p]

@@ -78,6 +78,7 @@ typedef struct rto_ctx {
     rto_stats stats;
     int nthreads;
     int phong_gbuffer;      /* extension (README to-do): modes 3/4 also write normals/depth of the first hit */
+    int max_shapes;         /* shape table size, MAX_SHAPES unless rto_create_ex said otherwise */
     int rectangles;         /* extension (README to-do): the rectangle records are intersected */
     unsigned char *pathlen; /* optional analysis aid: segments walked per (pixel, sample), [y][x][aa] */
 } rto_ctx;
@@ -98,16 +99,19 @@ static inline long long gidx(const rto_ctx *c, int f, long long x, long long y)
     return ((long long)f * c->cfg.width + x) * c->cfg.height + y;
 }
 
-rto_ctx *rto_create(const rto_config *cfg)
+/* max_shapes: the size of the shape table in the header (NUM_SHAPES = 10 in the reference, src/main.cpp:34;
+ * larger = the run-time table size of SURVEY 8(f), an extension: the traversal is the same loop over more records) */
+rto_ctx *rto_create_ex(const rto_config *cfg, int max_shapes)
 {
     if (!cfg || cfg->width <= 0 || cfg->height <= 0 || cfg->aa <= 0 ||
-        cfg->recursion_depth <= 0 || cfg->num_frames <= 0)
+        cfg->recursion_depth <= 0 || cfg->num_frames <= 0 || max_shapes < 1)
         return NULL;
     rto_ctx *c = (rto_ctx *)calloc(1, sizeof(rto_ctx));
     if (!c) return NULL;
     c->cfg = *cfg;
     c->npix = (long long)cfg->width * cfg->height;
-    c->rand_off = HEADER_VEC4 + MAX_SHAPES * 5;
+    c->max_shapes = max_shapes;
+    c->rand_off = HEADER_VEC4 + max_shapes * 5;
     c->pixels_off = c->rand_off + 2 * cfg->aa;
     c->normals_off = c->pixels_off + c->npix * cfg->num_frames;
     c->depth_off = c->normals_off + c->npix * cfg->num_frames;
@@ -127,6 +131,8 @@ rto_ctx *rto_create(const rto_config *cfg)
 #endif
     return c;
 }
+
+rto_ctx *rto_create(const rto_config *cfg) { return rto_create_ex(cfg, MAX_SHAPES); }
 
 void rto_destroy(rto_ctx *c)
 {
@@ -158,7 +164,7 @@ int rto_set_threads(rto_ctx *c, int n)
 /* shapes: n records of 5 vec4 (src/main.cpp:59-77, packer 395-469) */
 int rto_set_scene(rto_ctx *c, const float *shapes, int n)
 {
-    if (n < 0 || n > MAX_SHAPES) return -1;
+    if (n < 0 || n > c->max_shapes) return -1;
     memcpy(&SHAPE(c, 0, 0), shapes, (size_t)n * 5 * sizeof(rtr_v4));
     c->nshapes = n;
     return 0;
@@ -548,7 +554,7 @@ int rto_render_rows(rto_ctx *c, int mode, const float *uniforms, const float *ra
     if (rand_buffer) memcpy(&RANDB(c, 0), rand_buffer, (size_t)2 * c->cfg.aa * sizeof(rtr_v4));
     int frame = (int)U_MODE(c).y;
     if (frame < 0 || frame >= c->cfg.num_frames) return -2;
-    if ((int)U_MODE(c).z > MAX_SHAPES) return -3;
+    if ((int)U_MODE(c).z > c->max_shapes) return -3;
     c->slot = frame;
     const int W = c->cfg.width;
     rto_stats total;

@@ -9,7 +9,7 @@ hot path of JustinPrivitera/Real_Time_Ray_Tracer, behind the C ABI of include/rt
 """
 from . import host  # noqa: F401
 from ._lib import (BUF_COLOR, BUF_DEPTH, BUF_HIT_INDEX, BUF_IMAGE, BUF_NORMAL, BUF_RAW_COLOR,  # noqa: F401
-                   EDGE_CLEAN, EDGE_FLAT32, FLAG_PHONG_GBUFFER, FLAG_PHONG_POSTPROCESS, FLAG_PIPELINE, LAYOUT_REFERENCE, LAYOUT_ROW_MAJOR, MODE_AO, MODE_AO_PP,
+                   EDGE_CLEAN, EDGE_FLAT32, FLAG_PHONG_GBUFFER, FLAG_PHONG_POSTPROCESS, FLAG_PIPELINE, FLAG_RECTANGLES, LAYOUT_REFERENCE, LAYOUT_ROW_MAJOR, MODE_AO, MODE_AO_PP,
                    MODE_HYBRID, MODE_PHONG)
 from .api import Application, RayTracer, RtError  # noqa: F401
 

@@ -15,15 +15,17 @@ EDGE_FLAT32, EDGE_CLEAN = 0, 1
 FLAG_PHONG_GBUFFER = 1
 FLAG_PHONG_POSTPROCESS = 2
 FLAG_PIPELINE = 4
+FLAG_RECTANGLES = 8
 BUF_COLOR, BUF_NORMAL, BUF_DEPTH, BUF_HIT_INDEX, BUF_IMAGE, BUF_RAW_COLOR, BUF_DEPTH_XY, BUF_DEPTH_W = range(8)
 LAYOUT_ROW_MAJOR, LAYOUT_REFERENCE = 0, 1
 MAX_SHAPES, MAX_AA, MAX_FRAMES = 10, 16, 16
+MAX_SHAPES_LIMIT = 256
 
 
 class rt_config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("width", "height", "aa", "recursion_depth", "num_frames", "edge_mode",
                                          "device", "band_y0", "band_rows", "band_index", "band_count")] + \
-               [("flags", C.c_int32), ("reserved", C.c_int32 * 4)]
+               [("flags", C.c_int32), ("max_shapes", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 STAT_COUNTERS = ("rays_closest", "rays_shadow", "primary", "jittered", "seg_nonterminal", "seg_terminal",

@@ -28,10 +28,11 @@ class RayTracer:
 
     def __init__(self, width: int, height: int, aa: int = host.AA, recursion_depth: int = host.RECURSION_DEPTH,
                  num_frames: int = host.NUM_FRAMES, edge_mode: int = L.EDGE_FLAT32, device: int = 0,
-                 band_y0: int = 0, band_rows: int = 0, band_index: int = 0, band_count: int = 1, flags: int = 0):
+                 band_y0: int = 0, band_rows: int = 0, band_index: int = 0, band_count: int = 1, flags: int = 0,
+                 max_shapes: int = 0):
         self.lib = L.load()
         cfg = L.rt_config(width, height, aa, recursion_depth, num_frames, edge_mode, device,
-                          band_y0, band_rows, band_index, band_count, flags)
+                          band_y0, band_rows, band_index, band_count, flags, max_shapes)
         h = C.c_void_p()
         rc = self.lib.rt_create(C.byref(cfg), C.byref(h))
         if rc != L.RT_OK:

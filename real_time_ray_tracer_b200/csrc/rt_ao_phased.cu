@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel
                         vp = div_const(fy + jy, p.fH, p.invH);
                     }
                     dir = primary_dir(p, hp, vp);
-                    ind = closest_hit_primary(p, dir, 0.0001f, t);
+                    ind = closest_hit_primary<true>(p, p.cam, dir, 0.0001f, t);
                     first = (aa == 0);
                     if (first) hit0 = ind;
                     cr = p.bg.x; cg = p.bg.y; cb = p.bg.z;      // 1 * a0 == a0
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(PH_THREADS, PH_MIN_BLOCKS) rt_ao_phased_kernel
                     ao_bounce(p, s_shapes[ind], t, ru, dir, pos, normal);
                     if (first) { nrm = normal; nrm_w = 1.0f; dx = t; dw = 1.0f; }
                     if (i > 0) {                  // false only for recursion_depth == 1
-                        ind = closest_hit(p, pos, dir, 0.0001f, t);
+                        ind = closest_hit<true>(p, pos, dir, 0.0001f, t);
                         stop = true;
                         float a0r = p.bg.x, a0g = p.bg.y, a0b = p.bg.z;
                         if (ind >= 0) {

@@ -46,9 +46,10 @@ constexpr int PU_MIN_BLOCKS = PU_MIN_BLOCKS_N;
 constexpr int PU_CHUNK = 4;                     // samples whose state is parked in shared memory at a time
 constexpr int PU_FIELDS = 8;                    // survivor: dir.xyz, t, ids, ru.xyz   finished: colour.rgb, terminal depth
 
+template <int KIND>
 __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
-    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ DevShape s_small[RT_MAX_SHAPES];
     __shared__ float4 s_rand[2 * RT_MAX_AA];
     __shared__ float s_state[PU_CHUNK][PU_FIELDS][PU_THREADS];   // [sample][field][owner thread]
     __shared__ float s_sky[6];                                    // sum.rgb, gamma.rgb of an all-background pixel
@@ -58,8 +59,8 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
     __shared__ unsigned s_out[PU_THREADS / 32];                   // per warp: its pixels' survivors not finished yet
 #endif
     const int tid = threadIdx.x;
-#pragma unroll 1
-    for (int i = tid; i < p.nshapes; i += PU_THREADS) s_shapes[i] = p.shapes[i];
+    const SceneSel<KIND> scene(p, s_small);
+    const DevShape *s_shapes = scene.shapes();
 #pragma unroll 1
     for (int i = tid; i < 2 * p.AA; i += PU_THREADS) s_rand[i] = p.rand[i];
     if (tid < 6) s_sky[tid] = o.sky[tid];
@@ -81,7 +82,7 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
     // only background, and its heads skip the camera ray and the closest hit -- the sample ends there with the
     // background colour whatever the ray is -- but the warp still takes part in the barriers and pulls other
     // warps' survivors.  Otherwise the camera rays test the candidates only.
-    const unsigned cand = tile_candidates(p, ((float)(blockIdx.x * PU_TILE_W + ((warp & 1) << 3)) + 3.5f) * p.invW,
+    const unsigned cand = scene.candidates(((float)(blockIdx.x * PU_TILE_W + ((warp & 1) << 3)) + 3.5f) * p.invW,
                                           ((float)(p.y0 + blockIdx.y * PU_TILE_H + ((warp >> 1) << 2)) + 1.5f) * p.invH);
     const bool sky_tile = cand == 0u;
     unsigned n_nonterm = 0, n_term = 0;
@@ -134,7 +135,7 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                     ind = -1;
                     if (!sky_tile) {
                         dir = ao_camera_ray(p, aa, rf, rs, fx, fy);
-                        ind = closest_hit_primary_masked(p, dir, 0.0001f, t, cand);
+                        ind = scene.primary_masked(dir, 0.0001f, t, cand);
                     }
                     first = (aa == 0);
                     if (first) hit0 = ind;
@@ -190,7 +191,7 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
                 ao_bounce(p, s_shapes[ind], t, ru, dir, pos, normal);
                 if (first) { nrm = normal; nrm_w = 1.0f; dx = t; dw = 1.0f; }
                 if (i > 0) {                  // false only for recursion_depth == 1
-                    ind = closest_hit(p, pos, dir, 0.0001f, t);
+                    ind = scene.closest(pos, dir, 0.0001f, t);
                     stop = true;
                     float a0r = p.bg.x, a0g = p.bg.y, a0b = p.bg.z;
                     if (ind >= 0) {
@@ -283,7 +284,23 @@ __global__ void __launch_bounds__(PU_THREADS, PU_MIN_BLOCKS) rt_ao_pulled_kernel
 cudaError_t launch_ao_pulled(const FrameParams &p, const TraceOut &o, cudaStream_t s)
 {
     dim3 grid((p.W + PU_TILE_W - 1) / PU_TILE_W, (p.rows + PU_TILE_H - 1) / PU_TILE_H);
-    rt_ao_pulled_kernel<<<grid, PU_THREADS, 0, s>>>(p, o);
+    const int kind = scene_kind(p);
+    if (kind == SCENE_BIG) {
+        // static + dynamic shared memory pass 48 KB for the largest scenes
+        static bool raised[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !raised[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(rt_ao_pulled_kernel<SCENE_BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+            if (e != cudaSuccess) return e;
+            raised[dev] = true;
+        }
+        rt_ao_pulled_kernel<SCENE_BIG><<<grid, PU_THREADS, (size_t)p.big_vec4 * sizeof(uint4), s>>>(p, o);
+    } else if (kind == SCENE_SMALL_RECT) {
+        rt_ao_pulled_kernel<SCENE_SMALL_RECT><<<grid, PU_THREADS, 0, s>>>(p, o);
+    } else {
+        rt_ao_pulled_kernel<SCENE_SMALL><<<grid, PU_THREADS, 0, s>>>(p, o);
+    }
     return cudaGetLastError();
 }
 

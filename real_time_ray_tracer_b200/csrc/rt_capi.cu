@@ -61,8 +61,16 @@ struct rt_ctx {
     bool ao_cull = true;      // RT_AO_CULL=0 switches the tile test (tile_candidates) off (A/B)
     int ao_kernel = AO_KERNEL_PULLED; // RT_AO_KERNEL=phased selects the A/B partner
     unsigned long long *stats_host = nullptr; // pinned
-    DevShape shapes[RT_MAX_SHAPES]{};
+    DevShape shapes[RT_MAX_SHAPES_LIMIT]{};
+    rt_vec4 edges[RT_MAX_SHAPES_LIMIT][2]{};   // rectangles: (up, -), (right, -) of the record
     int nshapes = 0;
+    int max_shapes = RT_MAX_SHAPES;            // rt_config.max_shapes
+    // Scenes above RT_MAX_SHAPES objects (FrameParams::big): the lists travel as one block per frame, through a
+    // ring of pinned staging buffers (the host runs ahead of the frames) into one device block per frame parity.
+    uint4 *big_host[4] = { nullptr, nullptr, nullptr, nullptr };
+    cudaEvent_t ev_big[4]{};
+    uint4 *big_dev[2] = { nullptr, nullptr };
+    int big_cap_vec4 = 0;
     FrameParams fp{};
     int last_mode = 0, last_slot = 0;
     bool frame_pending_post = false, halo_packed = false;
@@ -138,6 +146,8 @@ static void free_all(rt_ctx *c)
     for (cudaEvent_t e : c->ev_done) if (e) cudaEventDestroy(e);
     if (c->ev_user) cudaEventDestroy(c->ev_user);
     cudaFree(c->rgba8); cudaFree(c->pack_count);
+    for (int i = 0; i < 4; i++) { if (c->big_host[i]) cudaFreeHost(c->big_host[i]); if (c->ev_big[i]) cudaEventDestroy(c->ev_big[i]); }
+    cudaFree(c->big_dev[0]); cudaFree(c->big_dev[1]);
     if (c->ev_fence_in) cudaEventDestroy(c->ev_fence_in);
     if (c->ev_fence_done) cudaEventDestroy(c->ev_fence_done);
     if (c->ev_stream_switch) cudaEventDestroy(c->ev_stream_switch);
@@ -164,7 +174,8 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     if (cfg->num_frames < 1 || cfg->num_frames > RT_MAX_FRAMES) return fail(nullptr, RT_EINVAL, "rt_create: num_frames must be 1..%d", RT_MAX_FRAMES);
     if (cfg->edge_mode != RT_EDGE_FLAT32 && cfg->edge_mode != RT_EDGE_CLEAN) return fail(nullptr, RT_EINVAL, "rt_create: bad edge_mode");
     for (int r : cfg->reserved) if (r != 0) return fail(nullptr, RT_EINVAL, "rt_create: reserved fields must be 0");
-    if (cfg->flags & ~(RT_FLAG_PHONG_GBUFFER | RT_FLAG_PHONG_POSTPROCESS | RT_FLAG_PIPELINE)) return fail(nullptr, RT_EINVAL, "rt_create: unknown flags 0x%x", cfg->flags);
+    if (cfg->max_shapes < 0 || cfg->max_shapes > RT_MAX_SHAPES_LIMIT) return fail(nullptr, RT_EINVAL, "rt_create: max_shapes must be 0 (= %d) .. %d", RT_MAX_SHAPES, RT_MAX_SHAPES_LIMIT);
+    if (cfg->flags & ~(RT_FLAG_PHONG_GBUFFER | RT_FLAG_PHONG_POSTPROCESS | RT_FLAG_PIPELINE | RT_FLAG_RECTANGLES)) return fail(nullptr, RT_EINVAL, "rt_create: unknown flags 0x%x", cfg->flags);
     if ((cfg->flags & RT_FLAG_PHONG_POSTPROCESS) && !(cfg->flags & RT_FLAG_PHONG_GBUFFER))
         return fail(nullptr, RT_EINVAL, "rt_create: RT_FLAG_PHONG_POSTPROCESS needs RT_FLAG_PHONG_GBUFFER (the pass reads normals and depths)");
     int rows = cfg->band_rows ? cfg->band_rows : cfg->height - cfg->band_y0;
@@ -188,6 +199,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     const size_t ring = c->npix * (cfg->num_frames + 2);
     for (int i = 0; i < cfg->num_frames; i++) c->phys[i] = i;
     c->retired[0] = cfg->num_frames; c->retired[1] = cfg->num_frames + 1;
+    c->max_shapes = cfg->max_shapes > RT_MAX_SHAPES ? cfg->max_shapes : RT_MAX_SHAPES;
     c->pipeline = (cfg->flags & RT_FLAG_PIPELINE) != 0;
     if (const char *k = getenv("RT_PIPELINE")) c->pipeline = strcmp(k, "0") != 0;   // test sweeps: force it on / off
     cudaError_t e = cudaSetDevice(cfg->device);
@@ -371,7 +383,7 @@ int rt_set_timing(rt_ctx *c, int enabled)
 int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
 {
     if (!c) return RT_EINVAL;
-    if (n < 0 || n > RT_MAX_SHAPES) return fail(c, RT_EINVAL, "rt_upload_scene: n_shapes %d outside 0..%d", n, RT_MAX_SHAPES);
+    if (n < 0 || n > c->max_shapes) return fail(c, RT_EINVAL, "rt_upload_scene: n_shapes %d outside 0..%d (rt_config.max_shapes)", n, c->max_shapes);
     if (n > 0 && !shapes) return fail(c, RT_EINVAL, "rt_upload_scene: null shapes");
     for (int i = 0; i < n; i++) {
         const rt_vec4 *v = shapes[i].v;
@@ -385,6 +397,8 @@ int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
         d.r2 = r2;
         d.id = (int)v[4].w;
         c->shapes[i] = d;
+        c->edges[i][0] = v[1];
+        c->edges[i][1] = v[2];
     }
     c->nshapes = n;
     return RT_OK;
@@ -396,9 +410,35 @@ static inline float3 f3(const rt_vec4 &v) { return make_float3(v.x, v.y, v.z); }
 // sphere_eval_ray / plane_eval_ray (ao_compute.glsl:75-117) compute from `pos` alone, for pos = the camera:
 // one binary32 operation per shader operation, dot = multiply then fused multiply-adds (rt_math.cuh).
 // volatile keeps the host compiler from contracting or reassociating anything.
-static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n, bool cull)
+struct CamSphere { float px, py, pz, dd; };
+static inline CamSphere cam_sphere(const float3 &cam, const DevShape &s)
 {
-    p.nsph = p.npl = 0;
+    volatile float px = cam.x - s.s0.x, py = cam.y - s.s0.y, pz = cam.z - s.s0.z;
+    volatile float xx = px * px;
+    volatile float dd = fmaf(pz, pz, fmaf(py, py, xx));
+    return { px, py, pz, dd };
+}
+// dot(n, q - cam): plane_eval_ray's numerator for rays that leave the camera
+static inline float cam_plane_num(const float3 &cam, const float4 &n, const float4 &q)
+{
+    volatile float qx = q.x - cam.x, qy = q.y - cam.y, qz = q.z - cam.z;
+    volatile float xx = n.x * qx;
+    volatile float num = fmaf(n.z, qz, fmaf(n.y, qy, xx));
+    return num;
+}
+static inline float self_dot(const rt_vec4 &e)
+{
+    volatile float xx = e.x * e.x;
+    volatile float d = fmaf(e.z, e.z, fmaf(e.y, e.y, xx));
+    return d;
+}
+static inline float vec_len(const float4 &n) { return sqrtf(n.x * n.x + n.y * n.y + n.z * n.z); }
+
+static void build_traversal_tables(FrameParams &p, const DevShape *shapes, const rt_vec4 (*edges)[2], int n, bool cull, bool rectangles)
+{
+    p.nsph = p.npl = p.nrc = 0;
+    p.big = nullptr;
+    p.big_vec4 = 0;
     const float3 cam = p.cam;
     // tile_candidates: the farthest a camera ray of an 8x4 tile gets from the tile's centre ray before
     // normalisation: 3.5 (1.5) pixels + the jitter's 0.084, rounded up to 3.7 (1.7), +10 %
@@ -409,25 +449,76 @@ static void build_traversal_tables(FrameParams &p, const DevShape *shapes, int n
     for (int i = 0; i < n; i++) {
         const DevShape &s = shapes[i];
         if (s.id == SPHERE_ID) {
-            volatile float px = cam.x - s.s0.x, py = cam.y - s.s0.y, pz = cam.z - s.s0.z;
-            volatile float xx = px * px;
-            volatile float dd = fmaf(pz, pz, fmaf(py, py, xx));
+            const CamSphere k = cam_sphere(cam, s);
             p.sph[p.nsph] = make_float4(s.s0.x, s.s0.y, s.s0.z, s.r2);
-            p.sph_cam[p.nsph] = make_float4(px, py, pz, dd);
-            const float gap = dd - s.r2;
-            p.sph_len[p.nsph] = sqrtf(dd) * 1.001f;
+            p.sph_cam[p.nsph] = make_float4(k.px, k.py, k.pz, k.dd);
+            const float gap = k.dd - s.r2;
+            p.sph_len[p.nsph] = sqrtf(k.dd) * 1.001f;
             p.sph_gap[p.nsph] = (gap > 0.0f) ? gap * 0.999f : -1.0f;
             p.sph_idx[p.nsph++] = i;
         } else if (s.id == PLANE_ID) {
-            volatile float qx = s.s3.x - cam.x, qy = s.s3.y - cam.y, qz = s.s3.z - cam.z;
-            volatile float xx = s.s0.x * qx;
-            volatile float num = fmaf(s.s0.z, qz, fmaf(s.s0.y, qy, xx));
-            p.pl_n[p.npl] = make_float4(s.s0.x, s.s0.y, s.s0.z, num);
+            p.pl_n[p.npl] = make_float4(s.s0.x, s.s0.y, s.s0.z, cam_plane_num(cam, s.s0, s.s3));
             p.pl_p0[p.npl] = make_float4(s.s3.x, s.s3.y, s.s3.z, 0.0f);
-            p.pl_len[p.npl] = sqrtf(s.s0.x * s.s0.x + s.s0.y * s.s0.y + s.s0.z * s.s0.z) * 1.001f;
+            p.pl_len[p.npl] = vec_len(s.s0) * 1.001f;
             p.pl_idx[p.npl++] = i;
-        } // any other id (rectangle = 3) is never intersected: ao_compute.glsl:130-135
+        } else if (s.id == RECTANGLE_ID && rectangles) {
+            const rt_vec4 &up = edges[i][0], &right = edges[i][1];
+            p.rc_n[p.nrc] = make_float4(s.s0.x, s.s0.y, s.s0.z, cam_plane_num(cam, s.s0, s.s3));
+            p.rc_p[p.nrc] = make_float4(s.s3.x, s.s3.y, s.s3.z, vec_len(s.s0) * 1.001f);
+            p.rc_r[p.nrc] = make_float4(right.x, right.y, right.z, self_dot(right));
+            p.rc_u[p.nrc] = make_float4(up.x, up.y, up.z, self_dot(up));
+            p.rc_idx[p.nrc++] = i;
+        } // any other id is never intersected: ao_compute.glsl:130-135
     }
+}
+
+// The same lists for a scene above RT_MAX_SHAPES objects, as one block (layout: big_tables_vec4 / big_tables in
+// rt_trace_common.cuh).  Returns its size in 16-byte units.
+static int build_big_tables(FrameParams &p, uint4 *dst, const DevShape *shapes, const rt_vec4 (*edges)[2], int n, bool rectangles)
+{
+    p.nsph = p.npl = p.nrc = 0;
+    p.cull_a = 0.0f;
+    for (int i = 0; i < n; i++) {
+        if (shapes[i].id == SPHERE_ID) p.nsph++;
+        else if (shapes[i].id == PLANE_ID) p.npl++;
+        else if (shapes[i].id == RECTANGLE_ID && rectangles) p.nrc++;
+    }
+    float4 *q = reinterpret_cast<float4 *>(dst);
+    memcpy(q, shapes, (size_t)n * sizeof(DevShape)); q += 4 * n;
+    float4 *sph = q; q += p.nsph;
+    float4 *sph_cam = q; q += p.nsph;
+    float4 *pl_n = q; q += p.npl;
+    float4 *pl_p0 = q; q += p.npl;
+    float4 *rc_n = q; q += p.nrc;
+    float4 *rc_p = q; q += p.nrc;
+    float4 *rc_r = q; q += p.nrc;
+    float4 *rc_u = q; q += p.nrc;
+    int *sph_idx = reinterpret_cast<int *>(q); q += big_idx_vec4(p.nsph);
+    int *pl_idx = reinterpret_cast<int *>(q); q += big_idx_vec4(p.npl);
+    int *rc_idx = reinterpret_cast<int *>(q); q += big_idx_vec4(p.nrc);
+    int a = 0, b = 0, r = 0;
+    const float3 cam = p.cam;
+    for (int i = 0; i < n; i++) {
+        const DevShape &s = shapes[i];
+        if (s.id == SPHERE_ID) {
+            const CamSphere k = cam_sphere(cam, s);
+            sph[a] = make_float4(s.s0.x, s.s0.y, s.s0.z, s.r2);
+            sph_cam[a] = make_float4(k.px, k.py, k.pz, k.dd);
+            sph_idx[a++] = i;
+        } else if (s.id == PLANE_ID) {
+            pl_n[b] = make_float4(s.s0.x, s.s0.y, s.s0.z, cam_plane_num(cam, s.s0, s.s3));
+            pl_p0[b] = make_float4(s.s3.x, s.s3.y, s.s3.z, 0.0f);
+            pl_idx[b++] = i;
+        } else if (s.id == RECTANGLE_ID && rectangles) {
+            const rt_vec4 &up = edges[i][0], &right = edges[i][1];
+            rc_n[r] = make_float4(s.s0.x, s.s0.y, s.s0.z, cam_plane_num(cam, s.s0, s.s3));
+            rc_p[r] = make_float4(s.s3.x, s.s3.y, s.s3.z, 0.0f);
+            rc_r[r] = make_float4(right.x, right.y, right.z, self_dot(right));
+            rc_u[r] = make_float4(up.x, up.y, up.z, self_dot(up));
+            rc_idx[r++] = i;
+        }
+    }
+    return (int)(reinterpret_cast<uint4 *>(q) - dst);
 }
 
 // the share of every frame target inside this band, as band-local row ranges (see GatherTargets)
@@ -478,8 +569,12 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     p.llc = f3(u->llc_minus_campos); p.horiz = f3(u->horizontal); p.vert = f3(u->vertical);
     p.cam = f3(u->camera_location); p.light = f3(u->light_pos);
     p.bg = make_float4(u->background.x, u->background.y, u->background.z, u->background.w);
-    memcpy(p.shapes, c->shapes, sizeof p.shapes);
-    build_traversal_tables(p, c->shapes, nobj, c->ao_cull);
+    const bool rectangles = (c->cfg.flags & RT_FLAG_RECTANGLES) != 0;
+    const bool big = nobj > RT_MAX_SHAPES;
+    if (!big) {
+        memcpy(p.shapes, c->shapes, sizeof p.shapes);
+        build_traversal_tables(p, c->shapes, c->edges, nobj, c->ao_cull, rectangles);
+    }
     if (rand_buffer) {
         memcpy(p.rand, rand_buffer, (size_t)c->cfg.aa * 2 * sizeof(float4));
         c->rand_last = p.rand[2 * c->cfg.aa - 1];
@@ -508,6 +603,26 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
         c->retired[0] = c->retired[1];
         c->retired[1] = p_old;
         c->phys[slot] = p_new;
+    }
+
+    if (big) {
+        // the lists of this frame: staged in the next pinned buffer of the ring (free once the copy that last read
+        // it is over), copied on the frame's stream into the block of the frame's parity -- whose last reader, the
+        // frame before the previous one, ran on this same stream
+        const int k = (int)(c->frame_no & 3);
+        if (!c->big_dev[0]) {
+            const size_t bytes = (size_t)big_tables_vec4(RT_MAX_SHAPES_LIMIT, RT_MAX_SHAPES_LIMIT, 0, 0) * sizeof(uint4) * 2;   // any mix of kinds fits
+            for (int i = 0; i < 4; i++) { CU(c, cudaMallocHost((void **)&c->big_host[i], bytes)); CU(c, cudaEventCreateWithFlags(&c->ev_big[i], cudaEventDisableTiming)); }
+            for (int i = 0; i < 2; i++) CU(c, cudaMalloc((void **)&c->big_dev[i], bytes));
+            c->big_cap_vec4 = (int)(bytes / sizeof(uint4));
+        }
+        CU(c, cudaEventSynchronize(c->ev_big[k]));
+        const int nv = build_big_tables(p, c->big_host[k], c->shapes, c->edges, nobj, rectangles);
+        if (nv > c->big_cap_vec4) return fail(c, RT_EINVAL, "rt_render_frame: object lists of %d bytes", nv * 16);
+        CU(c, cudaMemcpyAsync(c->big_dev[par], c->big_host[k], (size_t)nv * sizeof(uint4), cudaMemcpyHostToDevice, S));
+        CU(c, cudaEventRecord(c->ev_big[k], S));
+        p.big = c->big_dev[par];
+        p.big_vec4 = nv;
     }
 
     TraceOut o{};

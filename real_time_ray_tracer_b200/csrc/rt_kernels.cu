@@ -67,22 +67,35 @@ __device__ __forceinline__ void shadow_occluder(float t, float3 l, double L2, fl
     }
 }
 
-__device__ __forceinline__ bool shadow_ray(const FrameParams &p, float3 pos)
+template <bool RC, class TAB>
+__device__ __forceinline__ bool shadow_ray(const FrameParams &fp, const TAB &p, float3 pos)
 {
-    const float3 lv = sub3(p.light, pos);
+    const float3 lv = sub3(fp.light, pos);
     const float3 l = normalize3(lv);
     const float len = length3(lv);
     const float3 new_pos = add3(pos, scale3(0.01f, l));
     const double L2 = __dmul_rn((double)len, (double)len);
     bool lit = true;
+    if constexpr (TAB::BIG) {
+#pragma unroll 2
+        for (int i = 0; i < p.nsph; i++) {
+            if (lit) {
+                const float4 s = p.sph[i];
+                const float3 pmc = sub3(new_pos, xyz(s));
+                const float b = dot3(l, pmc);
+                shadow_occluder(sphere_roots(b, b * b - dot3(pmc, pmc) + s.w), l, L2, len, lit);
+            }
+        }
+    } else {
 #pragma unroll
-    for (int i = 0; i < RT_MAX_SHAPES; i++) {
-        if (i >= p.nsph) break;
-        if (lit) {
-            const float4 s = p.sph[i];
-            const float3 pmc = sub3(new_pos, xyz(s));
-            const float b = dot3(l, pmc);
-            shadow_occluder(sphere_roots(b, b * b - dot3(pmc, pmc) + s.w), l, L2, len, lit);
+        for (int i = 0; i < RT_MAX_SHAPES; i++) {
+            if (i >= p.nsph) break;
+            if (lit) {
+                const float4 s = p.sph[i];
+                const float3 pmc = sub3(new_pos, xyz(s));
+                const float b = dot3(l, pmc);
+                shadow_occluder(sphere_roots(b, b * b - dot3(pmc, pmc) + s.w), l, L2, len, lit);
+            }
         }
     }
 #pragma unroll 1
@@ -92,6 +105,20 @@ __device__ __forceinline__ bool shadow_ray(const FrameParams &p, float3 pos)
         if (lit && !(denom < 0.001f && denom > -0.001f)) {
             const float num = dot3(n, sub3(xyz(p.pl_p0[j]), new_pos));
             if (num != 0.0f) shadow_occluder(__fdiv_rn(num, denom), l, L2, len, lit);   // t = +-0 is never > 0.0001
+        }
+    }
+    if constexpr (RC) {
+#pragma unroll 1
+        for (int j = 0; j < p.nrc; j++) {
+            const float3 n = xyz(p.rc_n[j]);
+            const float denom = dot3(n, l);
+            if (lit && !(denom < 0.001f && denom > -0.001f)) {
+                const float num = dot3(n, sub3(xyz(p.rc_p[j]), new_pos));
+                if (num != 0.0f) {
+                    const float t = __fdiv_rn(num, denom);
+                    if (t > 0.0001f && rect_inside(t, new_pos, l, p.rc_p[j], p.rc_r[j], p.rc_u[j])) shadow_occluder(t, l, L2, len, lit);
+                }
+            }
         }
     }
     return lit;
@@ -119,29 +146,33 @@ __device__ __forceinline__ float4 phong_shade(const FrameParams &p, float4 att, 
 #define PHONG_TILE 1
 #endif
 struct PhongTile { unsigned cand; int x, yl; };
-__device__ __forceinline__ PhongTile phong_tile(const FrameParams &p)
+template <int KIND>
+__device__ __forceinline__ PhongTile phong_tile(const FrameParams &p, const SceneSel<KIND> &scene)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x0 = blockIdx.x * TILE_W + ((warp & 1) << 3), y0 = blockIdx.y * TILE_H + ((warp >> 1) << 2);
     PhongTile t;
 #if PHONG_TILE
-    t.cand = tile_candidates(p, ((float)x0 + 3.5f) * p.invW, ((float)(p.y0 + y0) + 1.5f) * p.invH);
+    t.cand = scene.candidates(((float)x0 + 3.5f) * p.invW, ((float)(p.y0 + y0) + 1.5f) * p.invH);
 #else
-    t.cand = ((1u << p.nsph) - 1u) | (((1u << p.npl) - 1u) << 16);
+    t.cand = 0xffffffffu;
 #endif
     t.x = x0 + (lane & 7);
     t.yl = y0 + (lane >> 3);
     return t;
 }
 
+template <int KIND>
 __global__ void __launch_bounds__(TRACE_THREADS, 8) rt_phong_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
-    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ DevShape s_small[RT_MAX_SHAPES];
     __shared__ float s_sky[3];
-    for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
+    const SceneSel<KIND> scene(p, s_small);
+    const auto &tab = scene.tab();
+    const DevShape *s_shapes = scene.shapes();
     if (threadIdx.x < 3) s_sky[threadIdx.x] = o.sky[6 + threadIdx.x];   // gamma(0 + background), rt_sky_gamma_kernel
     __syncthreads();
-    const PhongTile tl = phong_tile(p);
+    const PhongTile tl = phong_tile(p, scene);
     const int x = tl.x, yl = tl.yl;
     const bool active = (x < p.W) && (yl < p.rows);
     unsigned n_shadow = 0;
@@ -153,14 +184,14 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) rt_phong_kernel(const __grid
         float3 dir = p.cam;
         if (tl.cand) {
             dir = primary_dir(p, div_const((float)x, p.fW, p.invW), div_const((float)y, p.fH, p.invH));
-            ind = closest_hit_primary_masked(p, dir, 0.0f, t, tl.cand);
+            ind = scene.primary_masked(dir, 0.0f, t, tl.cand);
         }
         float4 c = make_float4(s_sky[0], s_sky[1], s_sky[2], 0.0f);
         float4 g_normal = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         if (ind >= 0) {
             const DevShape &s = s_shapes[ind];
             float3 curr_pos = add3(p.cam, scale3(t, dir));
-            bool lit = shadow_ray(p, curr_pos);
+            bool lit = shadow_ray<SceneSel<KIND>::RC>(p, tab, curr_pos);
             n_shadow = 1;
             float3 normal = shape_normal(s, curr_pos);
             float4 att = make_float4(s.col.x, s.col.y, s.col.z, 0.0f);
@@ -183,14 +214,17 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) rt_phong_kernel(const __grid
     flush_stats<5>(o.stats, idx, val);
 }
 
+template <int KIND>
 __global__ void __launch_bounds__(TRACE_THREADS, 8) rt_hybrid_kernel(const __grid_constant__ FrameParams p, const __grid_constant__ TraceOut o)
 {
-    __shared__ DevShape s_shapes[RT_MAX_SHAPES];
+    __shared__ DevShape s_small[RT_MAX_SHAPES];
     __shared__ float s_sky[3];
-    for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) s_shapes[i] = p.shapes[i];
+    const SceneSel<KIND> scene(p, s_small);
+    const auto &tab = scene.tab();
+    const DevShape *s_shapes = scene.shapes();
     if (threadIdx.x < 3) s_sky[threadIdx.x] = o.sky[6 + threadIdx.x];   // gamma(0 + background), rt_sky_gamma_kernel
     __syncthreads();
-    const PhongTile tl = phong_tile(p);
+    const PhongTile tl = phong_tile(p, scene);
     const int x = tl.x, yl = tl.yl;
     const bool active = (x < p.W) && (yl < p.rows);
     unsigned n_rays = 0, n_shaded = 0, n_refl = 0;
@@ -209,7 +243,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) rt_hybrid_kernel(const __gri
         n_rays = 1;     // the camera ray's traversal counts whether or not the tile test shortened it
         if (tl.cand) {
             dir = primary_dir(p, div_const((float)x, p.fW, p.invW), div_const((float)y, p.fH, p.invH));
-            ind = closest_hit_primary_masked(p, dir, 0.001f, t, tl.cand);
+            ind = scene.primary_masked(dir, 0.001f, t, tl.cand);
         }
         first_ind = ind;
         // hybrid(): h_compute.glsl:269-297, first segment peeled there, folded into the loop here.  A camera ray
@@ -221,7 +255,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) rt_hybrid_kernel(const __gri
             {
                 const DevShape &s = s_shapes[ind];
                 float3 curr_pos = add3(pos, scale3(t, dir));
-                bool lit = shadow_ray(p, curr_pos);
+                bool lit = shadow_ray<SceneSel<KIND>::RC>(p, tab, curr_pos);
                 float3 normal = shape_normal(s, curr_pos);
                 a0 = phong_shade(p, s.col, curr_pos, dir, normal, lit);
                 n_shaded++;
@@ -246,7 +280,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) rt_hybrid_kernel(const __gri
             }
             if (stop || i == 1) break;
             // next segment
-            ind = closest_hit(p, pos, dir, 0.001f, t);
+            ind = scene.closest(pos, dir, 0.001f, t);
             n_rays++;
             if (ind < 0) {
                 result = div4(add4(result, scale4(cw, p.bg)), 1.0f + cw);
@@ -274,11 +308,18 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
     dim3 grid((p.W + TILE_W - 1) / TILE_W, (p.rows + TILE_H - 1) / TILE_H);
     dim3 block(TRACE_THREADS);
     if (p.mode == RT_MODE_AO_PP || p.mode == RT_MODE_AO)
-        return (o.ao_kernel == AO_KERNEL_PHASED) ? launch_ao_phased(p, o, s) : launch_ao_pulled(p, o, s);
-    else if (p.mode == RT_MODE_PHONG)
-        rt_phong_kernel<<<grid, block, 0, s>>>(p, o);
-    else
-        rt_hybrid_kernel<<<grid, block, 0, s>>>(p, o);
+        return (o.ao_kernel == AO_KERNEL_PHASED && !p.big_vec4) ? launch_ao_phased(p, o, s) : launch_ao_pulled(p, o, s);
+    const size_t big = (size_t)p.big_vec4 * sizeof(uint4);
+    const int kind = scene_kind(p);
+    if (p.mode == RT_MODE_PHONG) {
+        if (kind == SCENE_BIG) rt_phong_kernel<SCENE_BIG><<<grid, block, big, s>>>(p, o);
+        else if (kind == SCENE_SMALL_RECT) rt_phong_kernel<SCENE_SMALL_RECT><<<grid, block, 0, s>>>(p, o);
+        else rt_phong_kernel<SCENE_SMALL><<<grid, block, 0, s>>>(p, o);
+    } else {
+        if (kind == SCENE_BIG) rt_hybrid_kernel<SCENE_BIG><<<grid, block, big, s>>>(p, o);
+        else if (kind == SCENE_SMALL_RECT) rt_hybrid_kernel<SCENE_SMALL_RECT><<<grid, block, 0, s>>>(p, o);
+        else rt_hybrid_kernel<SCENE_SMALL><<<grid, block, 0, s>>>(p, o);
+    }
     return cudaGetLastError();
 }
 

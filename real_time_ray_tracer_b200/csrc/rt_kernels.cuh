@@ -10,6 +10,7 @@ namespace rt {
 
 constexpr int SPHERE_ID = 1; // resources/ao_compute.glsl:15-17
 constexpr int PLANE_ID = 5;
+constexpr int RECTANGLE_ID = 3; // src/geom_objs/rectangle.h:6; intersected only under RT_FLAG_RECTANGLES
 
 // One scene object, rebuilt from the reference's vec4[5] record (src/main.cpp:59-77) by
 // rt_upload_scene.  r2 = radius * radius in binary32, the product the shader forms per test.
@@ -28,6 +29,7 @@ struct DevShape {
 // warp-uniform addresses.  This replaces the per-frame 55.8 MB SSBO upload of
 // src/main.cpp:598-602: ~1.4 KB travel per frame.
 struct FrameParams {
+    static constexpr bool BIG = false;  // the traversal functions read the lists below (see BigTables)
     int W, H, AA, RD, NF;
     int y0, rows; // row band [y0, y0 + rows)
     int slot, nshapes, edge_mode, mode;
@@ -43,7 +45,7 @@ struct FrameParams {
     // the camera (formed on the host with the shader's operation order).
     int nsph, npl;
     float invAA;   // 1 / AA when AA is a power of two (then x * invAA == x / AA bit for bit), else 0: divide
-    int pad2;
+    int nrc;       // rectangles (RT_FLAG_RECTANGLES; 0 without it: the shaders never intersect them)
     float4 sph[RT_MAX_SHAPES];     // centre.xyz, radius * radius
     float4 sph_cam[RT_MAX_SHAPES]; // cam - centre, dot(cam - centre, cam - centre)
     float4 pl_n[RT_MAX_SHAPES];    // normal.xyz, dot(normal, p0 - cam)
@@ -56,8 +58,37 @@ struct FrameParams {
     // (jitter included).  cull_a == 0 switches the test off (RT_AO_CULL=0).
     float sph_len[RT_MAX_SHAPES], sph_gap[RT_MAX_SHAPES], pl_len[RT_MAX_SHAPES];
     float cull_a;
+    // rectangles: the plane through the lower left vertex plus the two edges (rectangle_eval_ray, oracle/rt_oracle.c)
+    float4 rc_n[RT_MAX_SHAPES];    // normal.xyz, dot(normal, llv - cam)
+    float4 rc_p[RT_MAX_SHAPES];    // llv.xyz, |normal| * 1.001 (tile test)
+    float4 rc_r[RT_MAX_SHAPES];    // right.xyz, dot(right, right)
+    float4 rc_u[RT_MAX_SHAPES];    // up.xyz, dot(up, up)
+    int rc_idx[RT_MAX_SHAPES];
+    // A scene above RT_MAX_SHAPES objects (rt_config.max_shapes): the same lists, sized by the scene, as one block
+    // in device memory that every thread block copies to shared memory first (layout: big_tables()).  The arrays
+    // above are unused then; nsph / npl / nrc / nshapes still count.
+    const uint4 *big;
+    int big_vec4;                  // size of the block in 16-byte units; 0 = small scene
+    int pad3;
     float4 rand[2 * RT_MAX_AA];
 };
+
+// The lists of a big scene, as pointers into the block's shared-memory copy.  Same member names as FrameParams, so
+// the traversal functions (rt_trace_common.cuh) are written once, over either.
+struct BigTables {
+    static constexpr bool BIG = true;
+    int nsph, npl, nrc, nshapes;
+    const DevShape *shapes;
+    const float4 *sph, *sph_cam, *pl_n, *pl_p0, *rc_n, *rc_p, *rc_r, *rc_u;
+    const int *sph_idx, *pl_idx, *rc_idx;
+};
+// sizes in 16-byte units of the sections of the block, in this order: shapes, sph, sph_cam, pl_n, pl_p0, rc_n, rc_p,
+// rc_r, rc_u, sph_idx, pl_idx, rc_idx (the index lists padded to a multiple of four entries)
+__host__ __device__ inline int big_idx_vec4(int n) { return (n + 3) / 4; }
+__host__ __device__ inline int big_tables_vec4(int nshapes, int nsph, int npl, int nrc)
+{
+    return nshapes * 4 + 2 * nsph + 2 * npl + 4 * nrc + big_idx_vec4(nsph) + big_idx_vec4(npl) + big_idx_vec4(nrc);
+}
 
 // Statistics live in STAT_STRIPES copies (one 128-byte line each); a warp adds to stripe (its global index %
 // STAT_STRIPES).  With 16 stripes the reductions of a 1080p mode-4 frame (65 000 warps x 6 counters) queued up on 96

@@ -45,13 +45,6 @@ __device__ __forceinline__ float plane_eval_ray(float3 pos, float3 dir, float4 s
     return __fdiv_rn(dot3(n, sub3(xyz(s3), pos)), denom);
 }
 
-__device__ __forceinline__ float eval_ray(const DevShape &s, float3 pos, float3 dir)
-{
-    if (s.id == SPHERE_ID) return sphere_eval_ray(pos, dir, s.s0, s.r2);
-    if (s.id == PLANE_ID) return plane_eval_ray(pos, dir, s.s0, s.s3);
-    return -1.0f;
-}
-
 // ---------------------------------------------------------------------------------------------
 // closest hit (ao_compute.glsl:183-194 / p_compute.glsl:177-188 / h_compute.glsl:199-210)
 // ---------------------------------------------------------------------------------------------
@@ -100,6 +93,33 @@ __device__ __forceinline__ void plane_candidate(float num, float denom, int idx,
     }
 }
 
+// rectangle_eval_ray (defined by oracle/rt_oracle.c; the reference packs the records, src/main.cpp:444-467, and has
+// no intersection for them): plane_eval_ray through the lower left vertex, then the hit point's coordinates along
+// the two edges, a = dot(d, right) / dot(right, right), b = dot(d, up) / dot(up, up) with d = (pos + t dir) - llv,
+// both of which must lie in [0, 1].  The edge test only gates, so it runs after the cheap rejections.
+__device__ __forceinline__ bool rect_inside(float t, float3 pos, float3 dir, float4 llv, float4 right, float4 up)
+{
+    const float3 d = sub3(add3(pos, scale3(t, dir)), xyz(llv));
+    const float a = __fdiv_rn(dot3(d, xyz(right)), right.w);
+    const float b = __fdiv_rn(dot3(d, xyz(up)), up.w);
+    return !(a < 0.0f || a > 1.0f || b < 0.0f || b > 1.0f);
+}
+
+template <class TAB>
+__device__ __forceinline__ void rect_candidate(const TAB &s, int j, float num, float3 pos, float3 dir, float tmin, Closest &c)
+{
+    const float denom = dot3(xyz(s.rc_n[j]), dir);
+    if (denom < 0.001f && denom > -0.001f) return;
+    if (num == 0.0f && tmin >= 0.0f) return;    // as plane_candidate
+    const float res_t = __fdiv_rn(num, denom);
+    const unsigned bits = __float_as_uint(res_t);
+    const int idx = s.rc_idx[j];
+    if (res_t > tmin && (bits < c.tb || (bits == c.tb && idx < c.ind)) && rect_inside(res_t, pos, dir, s.rc_p[j], s.rc_r[j], s.rc_u[j])) {
+        c.tb = bits;
+        c.ind = idx;
+    }
+}
+
 // x / AA (ao_compute.glsl:330-331).  For a power-of-two AA, x * (1/AA) is the same real number, hence the same
 // correctly rounded result, and it has no range check: the zero depths of a sky pixel send whole warps down the
 // divide's slow path otherwise.
@@ -108,21 +128,41 @@ __device__ __forceinline__ float div_aa(const FrameParams &p, float x)
     return (p.invAA != 0.0f) ? x * p.invAA : __fdiv_rn(x, (float)p.AA);
 }
 
-__device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, float3 dir, float tmin, float &t_out)
+// TAB = FrameParams (lists in the constant bank, at most RT_MAX_SHAPES entries, the sphere loop unrolled) or
+// BigTables (lists in shared memory, rolled loops).
+// RC: the rectangle list is walked at all (a kernel instance per case: the headline scenes have none and keep the
+// code, and the registers, they had).
+template <bool RC, class TAB>
+__device__ __forceinline__ int closest_hit(const TAB &p, float3 pos, float3 dir, float tmin, float &t_out)
 {
     Closest c = { 0xffffffffu, -1 };
+    if constexpr (TAB::BIG) {
+#pragma unroll 2
+        for (int i = 0; i < p.nsph; i++) {
+            const float4 s = p.sph[i];
+            const float3 pmc = sub3(pos, xyz(s));
+            const float b = dot3(dir, pmc);
+            sphere_candidate(b, b * b - dot3(pmc, pmc) + s.w, p.sph_idx[i], tmin, c);
+        }
+    } else {
 #pragma unroll
-    for (int i = 0; i < RT_MAX_SHAPES; i++) {
-        if (i >= p.nsph) break;
-        const float4 s = p.sph[i];
-        const float3 pmc = sub3(pos, xyz(s));
-        const float b = dot3(dir, pmc);
-        sphere_candidate(b, b * b - dot3(pmc, pmc) + s.w, p.sph_idx[i], tmin, c);
+        for (int i = 0; i < RT_MAX_SHAPES; i++) {
+            if (i >= p.nsph) break;
+            const float4 s = p.sph[i];
+            const float3 pmc = sub3(pos, xyz(s));
+            const float b = dot3(dir, pmc);
+            sphere_candidate(b, b * b - dot3(pmc, pmc) + s.w, p.sph_idx[i], tmin, c);
+        }
     }
 #pragma unroll 1
     for (int j = 0; j < p.npl; j++) {
         const float3 n = xyz(p.pl_n[j]);
         plane_candidate(dot3(n, sub3(xyz(p.pl_p0[j]), pos)), dot3(n, dir), p.pl_idx[j], tmin, c);
+    }
+    if constexpr (RC) {
+#pragma unroll 1
+        for (int j = 0; j < p.nrc; j++)
+            rect_candidate(p, j, dot3(xyz(p.rc_n[j]), sub3(xyz(p.rc_p[j]), pos)), pos, dir, tmin, c);
     }
     t_out = (c.ind < 0) ? -1.0f : __uint_as_float(c.tb);
     return c.ind;
@@ -130,20 +170,34 @@ __device__ __forceinline__ int closest_hit(const FrameParams &p, float3 pos, flo
 
 // The same for rays that leave the camera: `pos - centre`, its squared length and the plane numerator
 // dot(n, p0 - pos) do not depend on the pixel (FrameParams::sph_cam, pl_n.w).
-__device__ __forceinline__ int closest_hit_primary(const FrameParams &p, float3 dir, float tmin, float &t_out)
+template <bool RC, class TAB>
+__device__ __forceinline__ int closest_hit_primary(const TAB &p, float3 cam, float3 dir, float tmin, float &t_out)
 {
     Closest c = { 0xffffffffu, -1 };
+    if constexpr (TAB::BIG) {
+#pragma unroll 2
+        for (int i = 0; i < p.nsph; i++) {
+            const float4 k = p.sph_cam[i];
+            const float b = dot3(dir, xyz(k));
+            sphere_candidate(b, b * b - k.w + p.sph[i].w, p.sph_idx[i], tmin, c);
+        }
+    } else {
 #pragma unroll
-    for (int i = 0; i < RT_MAX_SHAPES; i++) {
-        if (i >= p.nsph) break;
-        const float4 k = p.sph_cam[i];
-        const float b = dot3(dir, xyz(k));
-        sphere_candidate(b, b * b - k.w + p.sph[i].w, p.sph_idx[i], tmin, c);
+        for (int i = 0; i < RT_MAX_SHAPES; i++) {
+            if (i >= p.nsph) break;
+            const float4 k = p.sph_cam[i];
+            const float b = dot3(dir, xyz(k));
+            sphere_candidate(b, b * b - k.w + p.sph[i].w, p.sph_idx[i], tmin, c);
+        }
     }
 #pragma unroll 1
     for (int j = 0; j < p.npl; j++) {
         const float4 n = p.pl_n[j];
         plane_candidate(n.w, dot3(xyz(n), dir), p.pl_idx[j], tmin, c);
+    }
+    if constexpr (RC) {
+#pragma unroll 1
+        for (int j = 0; j < p.nrc; j++) rect_candidate(p, j, p.rc_n[j].w, cam, dir, tmin, c);
     }
     t_out = (c.ind < 0) ? -1.0f : __uint_as_float(c.tb);
     return c.ind;
@@ -160,7 +214,10 @@ __device__ __forceinline__ int closest_hit_primary(const FrameParams &p, float3 
 // is ruled out would never have produced a candidate, so leaving it out of the camera rays' closest hit changes
 // nothing.  A tile with NO candidate is what 40 % of config 2's warps are: sky.  Its samples all end on the camera
 // ray with the background colour, whatever the ray is, so the head skips the camera ray itself as well.
-// Returns sphere bits | plane bits << 16 (positions in FrameParams::sph / pl_n).
+// Returns sphere bits | plane bits << 16 (positions in FrameParams::sph / pl_n); the rectangles follow the planes in
+// the upper half (bit 16 + npl + j; the lists hold RT_MAX_SHAPES entries between them) and take the plane test of
+// their own plane.
+template <bool RC>
 __device__ __forceinline__ unsigned tile_candidates(const FrameParams &p, float hp0, float vp0)
 {
     unsigned sph_mask, pl_mask;
@@ -169,7 +226,7 @@ __device__ __forceinline__ unsigned tile_candidates(const FrameParams &p, float 
     const float3 d0 = scale3(inv, v0);
     const float s = p.cull_a * inv;
     sph_mask = (1u << p.nsph) - 1u;
-    pl_mask = (1u << p.npl) - 1u;
+    pl_mask = (1u << (p.npl + (RC ? p.nrc : 0))) - 1u;
     if (!(p.cull_a > 0.0f && s < 0.05f)) return sph_mask | (pl_mask << 16);   // off, degenerate camera, or tiles too wide for the margins
 #pragma unroll 1
     for (int i = 0; i < p.nsph; i++) {
@@ -184,14 +241,30 @@ __device__ __forceinline__ unsigned tile_candidates(const FrameParams &p, float 
         const float len = p.pl_len[j];
         if (n.w == 0.0f || q * (1.0f - s) - len * s > 1e-3f * len) pl_mask &= ~(1u << j);
     }
+    if constexpr (RC) {
+#pragma unroll 1
+        for (int j = 0; j < p.nrc; j++) {
+            const float4 n = p.rc_n[j];
+            const float dn = dot3(xyz(n), d0);
+            const float q = (n.w < 0.0f) ? dn : -dn;
+            const float len = p.rc_p[j].w;
+            if (n.w == 0.0f || q * (1.0f - s) - len * s > 1e-3f * len) pl_mask &= ~(1u << (p.npl + j));
+        }
+    }
     return sph_mask | (pl_mask << 16);
 }
 
 // closest_hit_primary over the tile's candidates only, in scene order (the tie rule needs ascending order)
+template <bool RC>
 __device__ __forceinline__ int closest_hit_primary_masked(const FrameParams &p, float3 dir, float tmin, float &t_out,
                                                           unsigned cand)
 {
     Closest c = { 0xffffffffu, -1 };
+    unsigned rc_cand = 0u;
+    if constexpr (RC) {
+        rc_cand = (cand >> 16) >> p.npl;
+        cand &= ~(0xffff0000u << p.npl);
+    }
 #pragma unroll 1
     for (unsigned m = cand & 0xffffu; m; m &= m - 1u) {
         const int i = __ffs((int)m) - 1;
@@ -205,9 +278,87 @@ __device__ __forceinline__ int closest_hit_primary_masked(const FrameParams &p, 
         const float4 n = p.pl_n[j];
         plane_candidate(n.w, dot3(xyz(n), dir), p.pl_idx[j], tmin, c);
     }
+    if constexpr (RC) {
+#pragma unroll 1
+        for (unsigned m = rc_cand; m; m &= m - 1u) {
+            const int j = __ffs((int)m) - 1;
+            rect_candidate(p, j, p.rc_n[j].w, p.cam, dir, tmin, c);
+        }
+    }
     t_out = (c.ind < 0) ? -1.0f : __uint_as_float(c.tb);
     return c.ind;
 }
+// The lists of a big scene in the block's shared-memory copy (layout: big_tables_vec4)
+__device__ __forceinline__ BigTables big_tables(const FrameParams &p, const uint4 *base)
+{
+    BigTables b;
+    b.nsph = p.nsph; b.npl = p.npl; b.nrc = p.nrc; b.nshapes = p.nshapes;
+    const float4 *q = reinterpret_cast<const float4 *>(base);
+    b.shapes = reinterpret_cast<const DevShape *>(q); q += 4 * p.nshapes;
+    b.sph = q; q += p.nsph;
+    b.sph_cam = q; q += p.nsph;
+    b.pl_n = q; q += p.npl;
+    b.pl_p0 = q; q += p.npl;
+    b.rc_n = q; q += p.nrc;
+    b.rc_p = q; q += p.nrc;
+    b.rc_r = q; q += p.nrc;
+    b.rc_u = q; q += p.nrc;
+    b.sph_idx = reinterpret_cast<const int *>(q); q += big_idx_vec4(p.nsph);
+    b.pl_idx = reinterpret_cast<const int *>(q); q += big_idx_vec4(p.npl);
+    b.rc_idx = reinterpret_cast<const int *>(q);
+    return b;
+}
+
+// What a trace kernel sees of the scene, by kernel instance:
+//   SCENE_SMALL       the lists inside the kernel parameters, no rectangles (every scene of the reference)
+//   SCENE_SMALL_RECT  the same with the rectangle list walked (RT_FLAG_RECTANGLES and the scene has some)
+//   SCENE_BIG         above RT_MAX_SHAPES objects: everything copied from FrameParams::big to dynamic shared memory
+// The object records are indexed by the hit, so the small kinds copy them to `small` (shared memory) as well.
+// The constructor is block-wide; __syncthreads() after it.
+enum { SCENE_SMALL = 0, SCENE_SMALL_RECT = 1, SCENE_BIG = 2 };
+extern __shared__ uint4 rt_dyn_smem[];
+template <int KIND> struct SceneSel {
+    static constexpr bool RC = (KIND == SCENE_SMALL_RECT);
+    const FrameParams &p;
+    const DevShape *sm;
+    __device__ __forceinline__ SceneSel(const FrameParams &p_, DevShape *small) : p(p_), sm(small)
+    {
+        for (int i = threadIdx.x; i < p.nshapes; i += blockDim.x) small[i] = p.shapes[i];
+    }
+    __device__ __forceinline__ const FrameParams &tab() const { return p; }
+    __device__ __forceinline__ const DevShape *shapes() const { return sm; }
+    __device__ __forceinline__ unsigned candidates(float hp0, float vp0) const { return tile_candidates<RC>(p, hp0, vp0); }
+    __device__ __forceinline__ int primary_masked(float3 dir, float tmin, float &t, unsigned cand) const
+    {
+        return closest_hit_primary_masked<RC>(p, dir, tmin, t, cand);
+    }
+    __device__ __forceinline__ int closest(float3 pos, float3 dir, float tmin, float &t) const
+    {
+        return closest_hit<RC>(p, pos, dir, tmin, t);
+    }
+};
+template <> struct SceneSel<SCENE_BIG> {
+    static constexpr bool RC = true;
+    BigTables bt;
+    float3 cam;
+    __device__ __forceinline__ SceneSel(const FrameParams &p, DevShape *) : cam(p.cam)
+    {
+        for (int i = threadIdx.x; i < p.big_vec4; i += blockDim.x) rt_dyn_smem[i] = __ldg(p.big + i);
+        bt = big_tables(p, rt_dyn_smem);
+    }
+    __device__ __forceinline__ const BigTables &tab() const { return bt; }
+    __device__ __forceinline__ const DevShape *shapes() const { return bt.shapes; }
+    __device__ __forceinline__ unsigned candidates(float, float) const { return 0xffffffffu; }   // no tile test
+    __device__ __forceinline__ int primary_masked(float3 dir, float tmin, float &t, unsigned) const
+    {
+        return closest_hit_primary<true>(bt, cam, dir, tmin, t);
+    }
+    __device__ __forceinline__ int closest(float3 pos, float3 dir, float tmin, float &t) const
+    {
+        return closest_hit<true>(bt, pos, dir, tmin, t);
+    }
+};
+__host__ __device__ inline int scene_kind(const FrameParams &p) { return p.big_vec4 ? SCENE_BIG : (p.nrc ? SCENE_SMALL_RECT : SCENE_SMALL); }
 
 __device__ __forceinline__ float3 shape_normal(const DevShape &s, float3 pt)
 {

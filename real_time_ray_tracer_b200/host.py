@@ -162,19 +162,60 @@ def init_scene6() -> scene:  # src/scene.h:111-167
     ])
 
 
+def init_scene5_rectangle() -> scene:
+    """scene5 with the emissive rectangle its source keeps commented out (src/scene.h:79-85) in place of the
+    emissive sphere: a light panel at y = 6 above the two spheres.  Rectangles are packed by the reference's host
+    but never intersected by its shaders; this scene is for FLAG_RECTANGLES."""
+    return scene([
+        make_rectangle((4, 6, 4), (0, 0, -8), (-8, 0, 0), (1.5, 1.5, 1.5), emissive=True),
+        make_sphere((0, 0, 0), 2, (0.2, 0.6, 0.8), reflectivity=0.4),
+        make_sphere((0, -35, 0), 33, (0.8, 0.6, 0.2)),
+    ])
+
+
+def init_scene_field(n_shapes: int, seed: int = 7) -> scene:
+    """A generated scene of ``n_shapes`` objects for contexts created with max_shapes > NUM_SHAPES: a floor plane,
+    an emissive sphere overhead, an emissive panel and a mirror wall (rectangles), and a field of small spheres of
+    mixed colour and reflectivity on a jittered grid in front of the default camera.  Deterministic in (n, seed)."""
+    if n_shapes < 4:
+        raise ValueError("init_scene_field needs at least 4 shapes")
+    rng = np.random.default_rng(seed)
+    shapes: List[shape] = [
+        make_plane((0, 1, 0), -4, (0.35, 0.35, 0.4)),
+        make_sphere((0, 40, -10), 20, (2.0, 2.0, 1.8), emissive=True),
+        make_rectangle((-6, 5, -2), (12, 0, 0), (0, 0, -8), (1.5, 1.4, 1.2), emissive=True),
+        make_rectangle((-14, -4, -18), (28, 0, 0), (0, 9, 0), (0.9, 0.9, 0.95), reflectivity=0.1),
+    ]
+    m = n_shapes - len(shapes)
+    cols = max(1, int(np.ceil(np.sqrt(m * 1.6))))
+    for k in range(m):
+        gx, gz = k % cols, k // cols
+        x = (gx - (cols - 1) / 2) * 2.1 + rng.uniform(-0.3, 0.3)
+        z = 6.0 - gz * 2.1 + rng.uniform(-0.3, 0.3)
+        r = rng.uniform(0.45, 0.95)
+        col = rng.uniform(0.15, 1.0, size=3)
+        refl = float(rng.choice([1.0, 1.0, 0.6, 0.3, 0.0]))
+        if k % 17 == 5:     # a few planes and rectangles between the spheres, so the lists interleave
+            shapes.append(make_rectangle((x - 0.8, -4, z), (1.6, 0, 0), (0, 2.5, 0), col, reflectivity=refl))
+        else:
+            shapes.append(make_sphere((x, -4 + r, z), r, col, reflectivity=refl))
+    return scene(shapes)
+
+
 SCENES = {"scene1": (init_scene1, SKY), "scene5": (init_scene5, BLACK), "scene6": (init_scene6, BLACK)}
 # mycam.v -> scene (src/main.cpp:229-255)
 SCENE_BY_V = {0: "scene1", 1: "scene5", 2: "scene6"}
 
 
-def load_shape_buffer(sc: scene, out: Optional[np.ndarray] = None) -> np.ndarray:
+def load_shape_buffer(sc: scene, out: Optional[np.ndarray] = None, max_shapes: int = NUM_SHAPES) -> np.ndarray:
     """Application::loadShapeBuffer (src/main.cpp:395-469): shapes -> vec4[n][5].
 
-    Lanes the reference never writes keep whatever ``out`` held (zeros by default)."""
+    Lanes the reference never writes keep whatever ``out`` held (zeros by default).  ``max_shapes``: the table size
+    (NUM_SHAPES in the reference; more for a context created with max_shapes)."""
     n = len(sc.shapes)
-    if n > NUM_SHAPES:
-        raise ValueError(f"at most {NUM_SHAPES} shapes (src/main.cpp:34), got {n}")
-    buf = out if out is not None else np.zeros((NUM_SHAPES, 5, 4), dtype=f32)
+    if n > max_shapes:
+        raise ValueError(f"at most {max_shapes} shapes (src/main.cpp:34), got {n}")
+    buf = out if out is not None else np.zeros((max_shapes, 5, 4), dtype=f32)
     for i, s in enumerate(sc.shapes):
         if s.id() == SPHERE_ID:
             buf[i, 0] = (*s.location, s.radius)

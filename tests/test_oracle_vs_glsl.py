@@ -103,3 +103,41 @@ def test_garbage_ring():
         slot = step(o, g, sc, 1)
         compare(o, g, slot, 1, f"garbage ring frame {k}")
     o.close(); g.close()
+
+
+# ---- rectangles (RT_FLAG_RECTANGLES): the shader text with its commented-out branch enabled ------------------
+def _have_rect_ref():
+    return os.path.exists(orc.glsl_ref_lib_path(W, H, AA, rectangles=True)) or os.path.isdir("/root/reference/resources")
+
+
+@pytest.mark.skipif(not _have_rect_ref(), reason="oracle/_ref rectangle library neither prebuilt nor buildable")
+@pytest.mark.parametrize("scene", ["scene5_rectangle", "mixed"])
+@pytest.mark.parametrize("mode", [1, 2, 3, 4])
+def test_rectangles_single_frame(scene, mode):
+    """The reference's eval_ray with `if (shape_id == RECTANGLE_ID) return rectangle_eval_ray(...)` uncommented
+    (ao_compute.glsl:130-133) and the missing function supplied as GLSL (oracle/build_ref.py): the oracle's
+    rectangle -- intersection, tie order in the object loop, normal, shading, G-buffer -- is the same bits."""
+    from tests.test_rectangles_big_scenes import rect_scenarios
+    sc = rect_scenarios()[scene]()
+    o, g = orc.Oracle(W, H, AA, rectangles=True), orc.GlslRef(W, H, AA, rectangles=True)
+    o.set_scene(sc.shapes, sc.n)
+    g.set_scene(sc.shapes, sc.n)
+    slot = step(o, g, sc, mode)
+    compare(o, g, slot, mode, f"{scene} mode {mode}")
+    rect_ids = [i for i, s in enumerate(sc.scene.shapes) if s.id() == 3]
+    assert np.isin(o.get(orc.HIT_INDEX), rect_ids).any()
+    o.close(); g.close()
+
+
+@pytest.mark.skipif(not _have_rect_ref(), reason="oracle/_ref rectangle library neither prebuilt nor buildable")
+def test_rectangles_mode1_sequence():
+    from tests.test_rectangles_big_scenes import rect_scenarios
+    sc = rect_scenarios(keys=("d", "w"))["mixed"]()
+    o, g = orc.Oracle(W, H, AA, rectangles=True), orc.GlslRef(W, H, AA, rectangles=True)
+    o.set_scene(sc.shapes, sc.n)
+    g.set_scene(sc.shapes, sc.n)
+    for k in range(10):
+        slot = step(o, g, sc, 1)
+        if k in (0, 4, 9):
+            compare(o, g, slot, 1, f"mixed frame {k}")
+    o.close(); g.close()

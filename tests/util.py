@@ -36,12 +36,17 @@ class Scenario:
     """scene + camera + light state; produces the uniforms of frame k like Application.render()."""
 
     def __init__(self, scene_name="scene1", aspect=host.ASPECT_RATIO, keys=(), light_movement=False,
-                 frametime=1.0 / 60.0, seed=0xC0FFEE):
-        f, bg = host.SCENES[scene_name]
-        self.scene = f()
-        self.bg = bg.copy()
+                 frametime=1.0 / 60.0, seed=0xC0FFEE, scene=None, bg=None, max_shapes=host.NUM_SHAPES):
+        """``scene`` (a host.scene) with background ``bg`` instead of one of the reference's named scenes;
+        ``max_shapes``: the shape table size (above NUM_SHAPES for a context created with max_shapes)"""
+        if scene is None:
+            f, bg0 = host.SCENES[scene_name]
+            scene = f()
+            bg = bg0 if bg is None else bg
+        self.scene = scene
+        self.bg = (host.BLACK if bg is None else bg).copy()
         self.n = len(self.scene.shapes)
-        self.shapes = host.load_shape_buffer(self.scene)
+        self.shapes = host.load_shape_buffer(self.scene, max_shapes=max_shapes)
         self.cam = host.camera()
         for k in keys:
             setattr(self.cam, k, 1)
