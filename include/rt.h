@@ -88,8 +88,10 @@ enum {
      * host (src/main.cpp:444-467: [0] = (normal, 0), [1] = (up, emissive), [2] = (right, 0), [3] = (lower left
      * vertex, reflectivity), [4] = (colour, 3)) but never intersected by its shaders (the call is commented out,
      * ao_compute.glsl:130-133, and no rectangle_eval_ray exists) -- are intersected: the plane test through the
-     * lower left vertex, then 0 <= dot(p - llv, e) / dot(e, e) <= 1 for both edges e (definition:
-     * oracle/rt_oracle.c rectangle_eval_ray).  Off (0) = the shaders' behaviour: such a record is never hit. */
+     * lower left vertex (p0 = llv in plane_eval_ray, ao_compute.glsl:109-117), then with d = (pos + t dir) - llv
+     * the hit needs 0 <= dot(d, e) / dot(e, e) <= 1 for both edges e = right, up; every operation binary32, dot()
+     * as everywhere else.  The hit's normal is record [0].  The CPU oracle states the same and is pinned to the
+     * shader text with that branch enabled.  Off (0) = the shaders' behaviour: never hit. */
     RT_FLAG_RECTANGLES = 8
 };
 

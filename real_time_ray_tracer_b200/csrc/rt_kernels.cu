@@ -434,14 +434,19 @@ __device__ __forceinline__ float nb_weight(float4 nn, float nd, float nb, const 
 }
 
 constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 4;
-// The pass is bound by HBM latency, not by arithmetic: what matters is how many dependent round trips a pixel makes
-// and how many bytes are in flight.  Round 1 walked the ring two frames at a time with the history colours requested
-// speculatively (0.313 ms at config 4, 0.72 of measured HBM bandwidth by algorithmic bytes, up to six dependent
-// trips per pixel).  Now a non-background pixel makes three: (1) raw colour + normal, (2) depth, the four neighbour
-// records and the normal / depth records of ALL the history frames (PP_BATCH = 7 = the whole ring of 8), (3) the
-// colours of exactly the frames the temporal test accepted.  Same arithmetic in the same order as the shader
-// (:175-201): the coefficients are evaluated in ring order and the walk stops at the first rejected frame; records
-// requested beyond that point are the only bytes moved in vain.
+// The pass is bound by HBM latency, not by arithmetic: what matters is how many dependent round trips a pixel makes,
+// how many bytes are in flight, and how many warps are resident to hide the rest.  A non-background pixel requests
+// (1) raw colour + normal, (2) depth and the four neighbour records, then walks the ring backwards PP_BATCH history
+// frames at a time with the colours requested speculatively together with the records that decide whether they are
+// used.  Same arithmetic in the same order as the shader (:175-201): the coefficients are evaluated in ring order
+// and the walk stops at the first rejected frame; a rejected frame's colour is the only traffic moved in vain.
+// Measured at config 4 (4K, moving camera; tools/gpu_pp_variants.sh, profiles/r2_pp_variants.txt):
+//   batch 2, speculative, 10 blocks/SM (48 registers), slim normals   0.293 ms   <- built
+//   the same with full float4 history normals (52 registers -> 9 blocks) 0.313 ms
+//   "three round trips": all 7 history records requested at once, colours only for accepted frames
+//                                                                     0.46 - 0.53 ms (spills; 5 blocks/SM)
+//   batch 4 / early records with the neighbours                        0.31 - 0.35 ms
+// Occupancy beats fewer round trips here.
 // Tuning knobs, swept on B200 at config 4 (tools/gpu_pp_variants.sh):
 #ifndef PP_SPECULATE
 #define PP_SPECULATE 1     // 1: request the colours together with the records (a rejected frame's colour is wasted)

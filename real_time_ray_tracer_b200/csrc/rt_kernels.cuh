@@ -58,7 +58,7 @@ struct FrameParams {
     // (jitter included).  cull_a == 0 switches the test off (RT_AO_CULL=0).
     float sph_len[RT_MAX_SHAPES], sph_gap[RT_MAX_SHAPES], pl_len[RT_MAX_SHAPES];
     float cull_a;
-    // rectangles: the plane through the lower left vertex plus the two edges (rectangle_eval_ray, oracle/rt_oracle.c)
+    // rectangles: the plane through the lower left vertex plus the two edges (include/rt.h, RT_FLAG_RECTANGLES)
     float4 rc_n[RT_MAX_SHAPES];    // normal.xyz, dot(normal, llv - cam)
     float4 rc_p[RT_MAX_SHAPES];    // llv.xyz, |normal| * 1.001 (tile test)
     float4 rc_r[RT_MAX_SHAPES];    // right.xyz, dot(right, right)

@@ -93,7 +93,7 @@ __device__ __forceinline__ void plane_candidate(float num, float denom, int idx,
     }
 }
 
-// rectangle_eval_ray (defined by oracle/rt_oracle.c; the reference packs the records, src/main.cpp:444-467, and has
+// rectangle_eval_ray (definition: include/rt.h, RT_FLAG_RECTANGLES; the reference packs the records, src/main.cpp:444-467, and has
 // no intersection for them): plane_eval_ray through the lower left vertex, then the hit point's coordinates along
 // the two edges, a = dot(d, right) / dot(right, right), b = dot(d, up) / dot(up, up) with d = (pos + t dir) - llv,
 // both of which must lie in [0, 1].  The edge test only gates, so it runs after the cheap rejections.
