@@ -746,7 +746,6 @@ int rt_postprocess(rt_ctx *c)
     CU(c, cudaSetDevice(c->cfg.device));
     cudaStream_t S = cur_stream(c);
     const int fpar = c->last_par;
-    if (c->timing) CU(c, cudaEventRecord(c->ev[fpar][2], S));
     if (!c->halo_packed) {
         if (c->cfg.band_count > 1) return fail(c, RT_ESTATE, "rt_postprocess: call rt_halo_pack and exchange the halo rows first");
         if (c->cfg.edge_mode == RT_EDGE_FLAT32) {
@@ -758,6 +757,9 @@ int rt_postprocess(rt_ctx *c)
     fill_post(c, q);
     CU(c, sync_fork(c, fpar));
     if (!c->prev_waited) { CU(c, wait_prev_frame(c)); c->prev_waited = true; }   // the history is frame k-1's result
+    // rt_stats.ms_post_last is the post-processing kernel's own duration: the pack kernel and the wait for the
+    // previous frame are before the first event
+    if (c->timing) CU(c, cudaEventRecord(c->ev[fpar][2], S));
     CU(c, launch_postprocess(q, S));
     if (c->timing) { CU(c, cudaEventRecord(c->ev[fpar][3], S)); c->ev_post_valid = true; }
     c->frame_pending_post = false;

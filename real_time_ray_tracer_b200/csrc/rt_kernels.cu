@@ -433,26 +433,38 @@ __device__ __forceinline__ float nb_weight(float4 nn, float nd, float nb, const 
     return normal_dot * depth_diff * bounces_diff + 0.2f;
 }
 
-constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 4;
+#ifndef PP_ROWS
+#define PP_ROWS 4
+#endif
+constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = PP_ROWS;
 // The pass is bound by HBM latency, not by arithmetic: what matters is how many dependent round trips a pixel makes,
 // how many bytes are in flight, and how many warps are resident to hide the rest.  A non-background pixel requests
 // (1) raw colour + normal, (2) depth and the four neighbour records, then walks the ring backwards PP_BATCH history
 // frames at a time with the colours requested speculatively together with the records that decide whether they are
 // used.  Same arithmetic in the same order as the shader (:175-201): the coefficients are evaluated in ring order
 // and the walk stops at the first rejected frame; a rejected frame's colour is the only traffic moved in vain.
-// Measured at config 4 (4K, moving camera; tools/gpu_pp_variants.sh, profiles/r2_pp_variants.txt):
-//   batch 2, speculative, 10 blocks/SM (48 registers), slim normals   0.293 ms   <- built
-//   the same with full float4 history normals (52 registers -> 9 blocks) 0.313 ms
-//   "three round trips": all 7 history records requested at once, colours only for accepted frames
-//                                                                     0.46 - 0.53 ms (spills; 5 blocks/SM)
-//   batch 4 / early records with the neighbours                        0.31 - 0.35 ms
-// Occupancy beats fewer round trips here.
+// Measured at config 4 (4K, moving camera; tools/gpu_pp_traffic.sh, profiles/r2_pp_variants.txt): the kernel's own
+// time by CUDA events / under ncu, DRAM bytes per launch against the 1504 MB the algorithm needs:
+//   batch 2, speculative, slim normals, 32-bit indices, 12 blocks/SM (40 registers)   0.273 ms / 250 us, 1.04x  <- built
+//   the same at 10 blocks/SM (48 registers)                                           0.288 ms / 267 us, 1.03x
+//   size_t indices, 10 blocks/SM (round 2's first build)                              0.294 ms / 268 us, 1.03x
+//   full float4 history normals (one register more per record in flight)              0.323 ms
+//   batch 1 / batch 3 / batch 4 (12, 12, 10 blocks)                                   0.292 / 0.341 / 0.377 ms
+//   first batch's records requested with the neighbours (PP_EARLY 1 / 2)              0.310 / 0.314 ms (spills)
+//   not speculative (colours only for accepted frames)                                0.336 ms, 1.005x
+//   "three round trips": all 7 history records at once, colours after the test       0.521 ms, 1.57x (spills)
+//   16 blocks/SM (32 registers)                                                       0.442 ms (spills)
+//   block 32x8 / 32x2 at the same occupancy                                           0.285 / 0.283 ms (with size_t)
+//   attribution: without the neighbour loads 0.271 (the same DRAM bytes: they are L1/L2 hits that cost latency),
+//   without the history walk 0.147, without both 0.076 ms
+// Occupancy beats fewer round trips here; at 250 us the launch moves 1563 MB = 6.2 TB/s, 0.96 of the measured copy
+// bandwidth, so what is left is the 4 % of traffic above the algorithmic bytes and the launch's ramp and tail.
 // Tuning knobs, swept on B200 at config 4 (tools/gpu_pp_variants.sh):
 #ifndef PP_SPECULATE
 #define PP_SPECULATE 1     // 1: request the colours together with the records (a rejected frame's colour is wasted)
 #endif
 #ifndef PP_MIN_BLOCKS
-#define PP_MIN_BLOCKS 10
+#define PP_MIN_BLOCKS 12
 #endif
 #ifndef PP_BATCH
 #define PP_BATCH 2
@@ -462,6 +474,14 @@ constexpr int PP_BLOCK_X = 32, PP_BLOCK_Y = 4;
 #endif
 #ifndef PP_SLIM
 #define PP_SLIM 1          // history normals as xy + z (their w is never read): 5 registers per record instead of 6
+#endif
+// Traffic attribution only (never defined in a product build; the results are then not the shader's): leave out
+// the neighbours / the history walk to see what each contributes to dram__bytes (tools/gpu_pp_traffic.sh).
+#ifndef PP_EXP_NO_NB
+#define PP_EXP_NO_NB 0
+#endif
+#ifndef PP_EXP_NO_HIST
+#define PP_EXP_NO_HIST 0
 #endif
 #if PP_SLIM
 struct HistN { float2 xy; float z; };
@@ -490,10 +510,11 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
     }
     if (active) {
         const int y = q.y0 + yl;
-        const size_t plane = (size_t)q.rows * q.W;
-        const size_t pix = (size_t)yl * q.W + x;
-        const float4 *nslot = q.ring_normal + (size_t)q.phys[q.slot] * plane;
-        const float2 *dslot = q.ring_depth_xy + (size_t)q.phys[q.slot] * plane;
+        // 32-bit element indices (rt_create: W * H * (NF + 2) < 2^31): half the registers of size_t offsets
+        const unsigned plane = (unsigned)q.rows * (unsigned)q.W;
+        const unsigned pix = (unsigned)yl * (unsigned)q.W + (unsigned)x;
+        const float4 *nslot = q.ring_normal + (unsigned)q.phys[q.slot] * plane;
+        const float2 *dslot = q.ring_depth_xy + (unsigned)q.phys[q.slot] * plane;
         float4 color = q.raw[pix];
         const float4 nn = nslot[pix];
         if (nn.w > 0.99f) {
@@ -504,15 +525,15 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             HistN cn[PP_BATCH];
             float4 hc[PP_BATCH];
             float2 cd[PP_BATCH];
-            auto hist_off = [&](int i) -> size_t {
+            auto hist_off = [&](int i) -> unsigned {
                 int cf = q.slot - i;
                 if (cf < 0) cf += q.NF;
-                return (size_t)q.phys[cf] * plane + pix;
+                return (unsigned)q.phys[cf] * plane + pix;
             };
 #pragma unroll
             for (int b = 0; b < PP_BATCH; b++) {
                 if (b < PP_EARLY && 1 + b < q.NF) {
-                    const size_t off = hist_off(1 + b);
+                    const unsigned off = hist_off(1 + b);
                     cn[b] = load_hist_normal(q.ring_normal + off);
                     cd[b] = q.ring_depth_xy[off];
 #if PP_SPECULATE
@@ -529,7 +550,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             float wsum = 1.0f;
             {   // up
                 NbRec U; U.color = z4; float u = 0.0f;
-                if (y + 1 < q.H) {
+                if (!PP_EXP_NO_NB && y + 1 < q.H) {
                     if (yl + 1 < q.rows) {
                         U.color = q.raw[pix + q.W]; U.normal = nslot[pix + q.W]; U.depth = dslot[pix + q.W];
                     } else {
@@ -541,7 +562,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             }
             {   // down: `y - 1 > 0` on a uint (:150) is true for y = 0 and false for y = 1
                 NbRec D; D.color = z4; float d = 0.0f;
-                const bool has_d = flat ? (y != 1) : (y > 0);
+                const bool has_d = !PP_EXP_NO_NB && (flat ? (y != 1) : (y > 0));
                 if (has_d) {
                     if (yl > 0) {
                         D.color = q.raw[pix - q.W]; D.normal = nslot[pix - q.W]; D.depth = dslot[pix - q.W];
@@ -554,7 +575,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             }
             {   // left
                 NbRec L; L.color = z4; float l = 0.0f;
-                if (x > 0) {
+                if (!PP_EXP_NO_NB && x > 0) {
                     L.color = q.raw[pix - 1]; L.normal = nslot[pix - 1]; L.depth = dslot[pix - 1];
                     l = nb_weight(nn, new_depth, new_bounces, L);
                 }
@@ -562,17 +583,18 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             }
             {   // right: x < WIDTH is always true in the shader (:81); CLEAN uses x + 1 < WIDTH
                 NbRec R; R.color = z4; float r = 0.0f;
-                if (x + 1 < q.W) {
+                if (PP_EXP_NO_NB) {
+                } else if (x + 1 < q.W) {
                     R.color = q.raw[pix + 1]; R.normal = nslot[pix + 1]; R.depth = dslot[pix + 1];
                     r = nb_weight(nn, new_depth, new_bounces, R);
                 } else if (flat) {
                     // [f][W][y] is [f+1][0][y]; past the last slot it is the next array's [0][0][y]
-                    const size_t col0 = (size_t)yl * q.W;
+                    const unsigned col0 = (unsigned)yl * (unsigned)q.W;
                     if (q.slot + 1 < q.NF) {
-                        const size_t off = (size_t)q.phys[q.slot + 1] * plane + col0;
+                        const unsigned off = (unsigned)q.phys[q.slot + 1] * plane + col0;
                         R.color = q.ring_color[off]; R.normal = q.ring_normal[off]; R.depth = q.ring_depth_xy[off];
                     } else {
-                        const size_t s0 = (size_t)q.phys[0] * plane + col0;
+                        const unsigned s0 = (unsigned)q.phys[0] * plane + col0;
                         R.color = q.ring_normal[s0];                     // pixels -> normals_buffer[0][0][y]
                         float2 d0 = q.ring_depth_xy[s0];                 // normals -> depth_buffer[0][0][y]
                         R.normal = make_float4(d0.x, d0.y, 0.0f, q.ring_depth_w[s0]);
@@ -589,12 +611,12 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             // rejected frame, then the colours of the accepted ones.
             float4 color_sum = z4;
             float denominator = 0.9f;
-            bool go = true;
+            bool go = !PP_EXP_NO_HIST;
             for (int i0 = 1; go && i0 < q.NF; i0 += PP_BATCH) {
 #pragma unroll
                 for (int b = 0; b < PP_BATCH; b++) {
                     if ((i0 > 1 || b >= PP_EARLY) && i0 + b < q.NF) {
-                        const size_t off = hist_off(i0 + b);
+                        const unsigned off = hist_off(i0 + b);
                         cn[b] = load_hist_normal(q.ring_normal + off);
                         cd[b] = q.ring_depth_xy[off];
 #if PP_SPECULATE
@@ -630,7 +652,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
             }
             color = div4(add4(scale4(0.9f, color), color_sum), denominator);
         }
-        q.ring_color[(size_t)q.phys[q.slot] * plane + pix] = color; // pixels[new_frame] and img_output
+        q.ring_color[(unsigned)q.phys[q.slot] * plane + pix] = color; // pixels[new_frame] and img_output
         gather_store(q.gather, yl, pix, color);             // rt_set_frame_targets: the assembled frame, maybe over NVLink
     }
     // per-warp flush, no block barrier: a warp of background pixels must not wait for its block-mates
