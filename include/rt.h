@@ -75,11 +75,12 @@ enum {
      * raw plane and rt_halo_pack / rt_postprocess blend it spatially and temporally into pixels[slot], using
      * the normals and depths RT_FLAG_PHONG_GBUFFER (required) has written. */
     RT_FLAG_PHONG_POSTPROCESS = 2,
-    /* Two frames in flight.  The kernels of consecutive frames are enqueued on two internal streams in turn, each
-     * frame ordered after exactly what it depends on (the frame before it only where the post-processing pass
-     * reads that frame's result), so that the tail of one frame's kernels, the short passes of mode 1 and the
-     * wait for the neighbouring bands' halo rows are filled with the next frame's trace kernel.  The results are
-     * the same bits.  What changes for the caller: work enqueued by rt_render_frame / rt_halo_pack / rt_postprocess
+    /* Frames in flight (three).  The trace kernels of consecutive frames are enqueued on internal streams in turn and
+     * the short passes that finish a frame (halo pack, post-processing) on one more stream of higher priority, each
+     * ordered after exactly what it depends on (the frame before it only where the post-processing pass reads that
+     * frame's result), so that the tail of one frame's kernels, the short passes of mode 1 and the wait for the
+     * neighbouring bands' halo rows are filled with the next frames' trace kernels.  The results are the same bits.
+     * What changes for the caller: work enqueued by rt_render_frame / rt_halo_pack / rt_postprocess
      * is NOT ordered with the caller's stream any more; every other entry point that touches results (downloads,
      * rt_device_ptr, rt_get_stats, rt_fence, rt_synchronize, ...) first makes the context's stream wait for the
      * frames issued so far.  Device pointers from rt_device_ptr are valid until the next rt_render_frame. */

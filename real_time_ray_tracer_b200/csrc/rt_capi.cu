@@ -17,36 +17,41 @@
 
 using namespace rt;
 
+constexpr int PIPE = 3;     // frames in flight under RT_FLAG_PIPELINE (and copies of the per-frame planes)
+constexpr int EVR = 8;      // ring of per-frame events (> PIPE + 1)
+
 struct rt_ctx {
     rt_config cfg{};
     int rows = 0;
     size_t npix = 0; // rows * width
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
-    // Ring planes, each [NF + 2][rows*W]: NF + 2 PHYSICAL slots behind the NF ring slots of the contract.  A frame
-    // that writes normals / depth (modes 1, 2; modes 3, 4 under RT_FLAG_PHONG_GBUFFER) takes the physical slot that
-    // was retired two frames earlier, and the slot's previous one is retired in turn (phys[] maps ring slot ->
-    // physical slot, retired[] is the queue).  That is what lets two frames be in flight (RT_FLAG_PIPELINE): the
-    // trace kernel of frame k+1 writes planes nobody reads while the post-processing kernel of frame k still
-    // walks the whole ring, including the slot frame k+1 replaces.
+    // Ring planes, each [NF + PIPE][rows*W]: NF + PIPE PHYSICAL slots behind the NF ring slots of the contract.  A
+    // frame that writes normals / depth (modes 1, 2; modes 3, 4 under RT_FLAG_PHONG_GBUFFER) takes the physical slot
+    // that was retired PIPE frames earlier, and the slot's previous one is retired in turn (phys[] maps ring slot ->
+    // physical slot, retired[] is the queue).  That is what lets PIPE frames be in flight (RT_FLAG_PIPELINE): the
+    // trace kernels of frames k+1, k+2 write planes nobody reads while the post-processing kernel of frame k still
+    // walks the whole ring, including the slots those frames replace.
     float4 *ring_color = nullptr, *ring_normal = nullptr;
     float2 *ring_depth_xy = nullptr;
     float *ring_depth_w = nullptr;
     int phys[RT_MAX_FRAMES] = {};
-    int retired[2] = { 0, 0 };
-    float4 *raw[2] = { nullptr, nullptr }; // trace output of a frame that rt_postprocess finishes, by frame parity
-    int *hit[2] = { nullptr, nullptr };    // hit-index plane, by frame parity
-    // RT_FLAG_PIPELINE: frames alternate between two internal streams; see begin_frame / end_frame
+    int retired[PIPE] = {};
+    float4 *raw[PIPE] = {}; // trace output of a frame that rt_postprocess finishes, by frame number mod PIPE
+    int *hit[PIPE] = {};    // hit-index plane, by frame number mod PIPE
+    // RT_FLAG_PIPELINE: the trace kernels of consecutive frames rotate over PIPE internal streams, the short passes
+    // that finish a frame (halo pack, post-processing) run on one more stream of higher priority; see begin_frame
     bool pipeline = false;
-    cudaStream_t fstream[2] = { nullptr, nullptr };
-    cudaEvent_t ev_done[4] = { nullptr, nullptr, nullptr, nullptr }; // frame k complete (and every frame before it)
-    cudaEvent_t ev_user = nullptr, ev_join[2] = { nullptr, nullptr };
+    cudaStream_t fstream[PIPE + 1] = {};            // [0 .. PIPE): trace streams, [PIPE]: the post stream
+    cudaEvent_t ev_done[EVR] = {};                   // frame k complete (and every frame before it)
+    cudaEvent_t ev_trace[EVR] = {};                  // trace kernel of frame k complete
+    cudaEvent_t ev_user = nullptr, ev_join[PIPE + 1] = {};
     unsigned long long frame_no = 0;   // frames rendered so far; the frame being built is frame_no - 1
     bool fork_pending = false;         // work was enqueued on `stream` that the next frames must follow
-    bool fork_seen[2] = { true, true };
-    bool serialize_next = false;       // the next frame must follow the previous one completely
-    int prev_slot = -1;
-    bool prev_post = false;
+    bool fork_seen[PIPE + 1] = { true, true, true, true };
+    int serialize_frames = 0;          // so many of the next frames must each follow their predecessor completely
+    int recent_slot[PIPE - 1] = { -1, -1 };    // ring slots of the PIPE - 1 frames before the one being built
+    bool recent_post[PIPE - 1] = { false, false };
     bool prev_waited = false;          // the frame being built already waits for its predecessor
     int last_par = 0;
     void *halo[4] = { nullptr, nullptr, nullptr, nullptr }; // send_lo, send_hi, recv_lo[2], recv_hi[2] (two rows each: frame parity of linked bands)
@@ -69,7 +74,7 @@ struct rt_ctx {
     // ring of pinned staging buffers (the host runs ahead of the frames) into one device block per frame parity.
     uint4 *big_host[4] = { nullptr, nullptr, nullptr, nullptr };
     cudaEvent_t ev_big[4]{};
-    uint4 *big_dev[2] = { nullptr, nullptr };
+    uint4 *big_dev[PIPE] = {};
     int big_cap_vec4 = 0;
     FrameParams fp{};
     int last_mode = 0, last_slot = 0;
@@ -93,7 +98,7 @@ struct rt_ctx {
     cudaEvent_t ev_quant[2] = { nullptr, nullptr }, ev_copy[2] = { nullptr, nullptr };
     bool copy_pending[2] = { false, false };
     bool timing = false;
-    cudaEvent_t ev[2][4] = {};   // per frame parity: trace begin / end, post-processing begin / end
+    cudaEvent_t ev[PIPE][4] = {};   // per frame number mod PIPE: trace begin / end, post-processing begin / end
     bool ev_trace_valid = false, ev_post_valid = false;
     int ev_parity = 0;
     std::string err;
@@ -137,24 +142,24 @@ static void free_all(rt_ctx *c)
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaFree(c->ring_color); cudaFree(c->ring_normal); cudaFree(c->ring_depth_xy); cudaFree(c->ring_depth_w);
-    for (int i = 0; i < 2; i++) { cudaFree(c->raw[i]); cudaFree(c->hit[i]); }
+    for (int i = 0; i < PIPE; i++) { cudaFree(c->raw[i]); cudaFree(c->hit[i]); cudaFree(c->big_dev[i]); }
     cudaFree(c->staging); cudaFree(c->stats); cudaFree(c->sky);
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i <= PIPE; i++) {
         if (c->fstream[i]) cudaStreamDestroy(c->fstream[i]);
         if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]);
     }
     for (cudaEvent_t e : c->ev_done) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_trace) if (e) cudaEventDestroy(e);
     if (c->ev_user) cudaEventDestroy(c->ev_user);
     cudaFree(c->rgba8); cudaFree(c->pack_count);
     for (int i = 0; i < 4; i++) { if (c->big_host[i]) cudaFreeHost(c->big_host[i]); if (c->ev_big[i]) cudaEventDestroy(c->ev_big[i]); }
-    cudaFree(c->big_dev[0]); cudaFree(c->big_dev[1]);
     if (c->ev_fence_in) cudaEventDestroy(c->ev_fence_in);
     if (c->ev_fence_done) cudaEventDestroy(c->ev_fence_done);
     if (c->ev_stream_switch) cudaEventDestroy(c->ev_stream_switch);
     if (c->fence_stream) cudaStreamDestroy(c->fence_stream);
     for (void *h : c->halo) cudaFree(h);
     if (c->stats_host) cudaFreeHost(c->stats_host);
-    for (int i = 0; i < 2; i++) for (cudaEvent_t e : c->ev[i]) if (e) cudaEventDestroy(e);
+    for (int i = 0; i < PIPE; i++) for (cudaEvent_t e : c->ev[i]) if (e) cudaEventDestroy(e);
     for (int i = 0; i < 2; i++) {
         if (c->ev_quant[i]) cudaEventDestroy(c->ev_quant[i]);
         if (c->ev_copy[i]) cudaEventDestroy(c->ev_copy[i]);
@@ -183,7 +188,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     int bcount = cfg->band_count ? cfg->band_count : 1;
     if (cfg->band_index < 0 || cfg->band_index >= bcount) return fail(nullptr, RT_EINVAL, "rt_create: bad band_index");
     if (bcount == 1 && rows != cfg->height) return fail(nullptr, RT_EINVAL, "rt_create: a partial band needs band_count > 1");
-    if ((long long)cfg->width * cfg->height * (cfg->num_frames + 2) >= (1ll << 31)) return fail(nullptr, RT_EINVAL, "rt_create: W*H*(num_frames+2) must fit 31 bits");
+    if ((long long)cfg->width * cfg->height * (cfg->num_frames + PIPE) >= (1ll << 31)) return fail(nullptr, RT_EINVAL, "rt_create: W*H*(num_frames+%d) must fit 31 bits", PIPE);
 
     int ndev = rt_device_count();
     if (ndev <= 0) return fail(nullptr, RT_ENODEVICE, "rt_create: no CUDA device (this library has no CPU path)");
@@ -196,9 +201,9 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     c->cfg.band_count = bcount;
     c->rows = rows;
     c->npix = (size_t)rows * cfg->width;
-    const size_t ring = c->npix * (cfg->num_frames + 2);
+    const size_t ring = c->npix * (cfg->num_frames + PIPE);
     for (int i = 0; i < cfg->num_frames; i++) c->phys[i] = i;
-    c->retired[0] = cfg->num_frames; c->retired[1] = cfg->num_frames + 1;
+    for (int i = 0; i < PIPE; i++) c->retired[i] = cfg->num_frames + i;
     c->max_shapes = cfg->max_shapes > RT_MAX_SHAPES ? cfg->max_shapes : RT_MAX_SHAPES;
     c->pipeline = (cfg->flags & RT_FLAG_PIPELINE) != 0;
     if (const char *k = getenv("RT_PIPELINE")) c->pipeline = strcmp(k, "0") != 0;   // test sweeps: force it on / off
@@ -224,13 +229,23 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0((void **)&c->ring_normal, ring * sizeof(float4));
     alloc0((void **)&c->ring_depth_xy, ring * sizeof(float2));
     alloc0((void **)&c->ring_depth_w, ring * sizeof(float));
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < PIPE; i++) {
         alloc0((void **)&c->raw[i], c->npix * sizeof(float4));
         alloc0((void **)&c->hit[i], c->npix * sizeof(int));
-        if (e == cudaSuccess && c->pipeline) e = cudaStreamCreateWithFlags(&c->fstream[i], cudaStreamNonBlocking);
+    }
+    int prio_least = 0, prio_greatest = 0;
+    if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+    for (int i = 0; i <= PIPE; i++) {
+        // the passes that finish a frame go first whenever SM slots free up: they are short, and the frames behind
+        // them (PIPE - 1 trace kernels are always ready to fill the machine) wait for their planes
+        if (e == cudaSuccess && c->pipeline)
+            e = cudaStreamCreateWithPriority(&c->fstream[i], cudaStreamNonBlocking, i == PIPE ? prio_greatest : prio_least);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming);
     }
-    for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+    for (int i = 0; i < EVR && e == cudaSuccess; i++) {
+        e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_trace[i], cudaEventDisableTiming);
+    }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming);
     alloc0(&c->staging, c->npix * sizeof(float4));
     alloc0((void **)&c->stats, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long));
@@ -247,7 +262,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     for (int i = 0; i < 4; i++) alloc0(&c->halo[i], halo_row_bytes(cfg->width) * (i >= 2 ? 2 : 1));
     alloc0((void **)&c->pack_count, sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMallocHost((void **)&c->stats_host, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long));
-    for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i >> 2][i & 3]);
+    for (int i = 0; i < 4 * PIPE && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i >> 2][i & 3]);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
         int code = (e == cudaErrorMemoryAllocation) ? RT_ENOMEM : RT_ECUDA;
@@ -264,26 +279,35 @@ void rt_destroy(rt_ctx *ctx) { free_all(ctx); }
 
 // ---- frame scheduling (RT_FLAG_PIPELINE) ---------------------------------------------------------------------
 // Without the flag every kernel goes on the context's stream, in order, and nothing below does anything.  With it,
-// frame k's kernels go on fstream[k & 1]:
-//     [after ev_done[k-3]] trace_k  [after ev_done[k-1]] (halo pack_k, post-processing_k)  -> ev_done[k]
-// * stream order puts frame k behind frame k-2; ev_done[j] also stands for every frame before j (each frame waits
-//   for its predecessor before it ends), so after ev_done[k-3] only frame k-1 can still be running;
-// * trace_k may run beside frame k-1: it writes a physical slot retired two frames ago (last read by the passes of
-//   frames <= k-3 and by trace_{k-2}), the raw / hit planes of its parity, and reads the slot's previous record,
-//   which frame k-1 does not write -- unless both frames name the same ring slot, or frame k writes its colour in
-//   place (modes 3/4 without G-buffer) while frame k-1's pass may be reading the ring: then it waits for k-1 first;
+// PIPE (3) frames are in flight: frame k's trace kernel goes on trace stream k mod PIPE, its finishing passes on the
+// post stream (higher priority: short kernels that the frames behind them wait for):
+//     trace stream k % PIPE:   [after ev_done[k-PIPE]]  trace_k  -> ev_trace[k]
+//     post stream:             [after ev_trace[k], ev_done[k-1]]  halo pack_k, post-processing_k  -> ev_done[k]
+// * ev_done[j] also stands for every frame before j (a frame without passes waits for ev_done[k-1] before it records
+//   its own), so after ev_done[k-PIPE] only frames k-PIPE+1 .. k-1 can still be running;
+// * trace_k may run beside those: it writes a physical slot retired PIPE frames ago (last read by the passes of frames
+//   <= k-PIPE-1 and by trace_{k-PIPE}), the raw / hit planes of its number mod PIPE (last read by the passes of frame
+//   k-PIPE), and reads the slot's previous record, which none of them writes -- unless one of them names the same
+//   ring slot, or frame k writes its colour in place (modes 3/4 without G-buffer) while one of their passes may be
+//   reading the ring: then it waits for frame k-1 (hence all of them) first;
 // * the halo pack and the post-processing pass read frame k-1's result (the history, the wrapped row of FLAT32) and
-//   share the halo rows with frame k-1's pass: they follow ev_done[k-1].
+//   share the halo rows with frame k-1's pass: they follow ev_done[k-1] -- the passes of consecutive frames are serial;
+// * why three and not two: with two, trace_{k+2} has to wait for pass_k (it reuses its raw plane), so while pass_k
+//   runs -- a short kernel with its own ramp and tail, and on linked bands a wait for the neighbours' halo rows --
+//   only trace_{k+1}'s remainder can fill the machine; with three there is always a whole trace kernel ready.
+//   Measured on 8 GPUs, config 4 (an eighth of a 4K frame per GPU): DESIGN.md section 6.
 // The context's stream carries no kernels then; entry points that hand results to the caller make it wait for the
-// frame streams (join_frames), entry points through which the caller changes state that later frames depend on
+// internal streams (join_frames), entry points through which the caller changes state that later frames depend on
 // (uploads, resets, fences, a new stream) make the next frames wait for it (mark_fork).
-static inline cudaStream_t cur_stream(rt_ctx *c) { return c->pipeline ? c->fstream[(c->frame_no - 1) & 1] : c->stream; }
+static inline int frame_par(const rt_ctx *c) { return (int)((c->frame_no - 1) % PIPE); }   // of the frame being built
+static inline cudaStream_t trace_stream(rt_ctx *c) { return c->pipeline ? c->fstream[frame_par(c)] : c->stream; }
+static inline cudaStream_t post_stream(rt_ctx *c) { return c->pipeline ? c->fstream[PIPE] : c->stream; }
 static inline void mark_fork(rt_ctx *c) { if (c->pipeline) c->fork_pending = true; }
 
 static cudaError_t join_frames(rt_ctx *c)
 {
     if (!c->pipeline) return cudaSuccess;
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i <= PIPE; i++) {
         cudaError_t e = cudaEventRecord(c->ev_join[i], c->fstream[i]);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, c->ev_join[i], 0);
         if (e != cudaSuccess) return e;
@@ -291,39 +315,77 @@ static cudaError_t join_frames(rt_ctx *c)
     return cudaSuccess;
 }
 
-static cudaError_t sync_fork(rt_ctx *c, int par)
+// internal stream `si` follows what the caller enqueued on the context's stream before the last fork mark
+static cudaError_t sync_fork(rt_ctx *c, int si)
 {
     cudaError_t e = cudaSuccess;
     if (!c->pipeline) return e;
     if (c->fork_pending) {
         e = cudaEventRecord(c->ev_user, c->stream);
-        c->fork_seen[0] = c->fork_seen[1] = false;
+        for (bool &f : c->fork_seen) f = false;
         c->fork_pending = false;
     }
-    if (e == cudaSuccess && !c->fork_seen[par]) {
-        e = cudaStreamWaitEvent(c->fstream[par], c->ev_user, 0);
-        c->fork_seen[par] = true;
+    if (e == cudaSuccess && !c->fork_seen[si]) {
+        e = cudaStreamWaitEvent(c->fstream[si], c->ev_user, 0);
+        c->fork_seen[si] = true;
     }
     return e;
 }
 
-static cudaError_t wait_prev_frame(rt_ctx *c)
+// stream S waits for frame k - back (complete, and every frame before it)
+static cudaError_t wait_frame_done(rt_ctx *c, cudaStream_t S, unsigned back)
 {
     const unsigned long long k = c->frame_no - 1;
-    if (!c->pipeline || k < 1) return cudaSuccess;
-    return cudaStreamWaitEvent(c->fstream[k & 1], c->ev_done[(k - 1) & 3], 0);
+    if (!c->pipeline || k < back) return cudaSuccess;
+    return cudaStreamWaitEvent(S, c->ev_done[(k - back) % EVR], 0);
 }
 
 static cudaError_t begin_frame(rt_ctx *c, int slot, bool inplace)
 {
     const unsigned long long k = c->frame_no++;
     if (!c->pipeline) return cudaSuccess;
-    cudaStream_t S = c->fstream[k & 1];
-    cudaError_t e = sync_fork(c, (int)(k & 1));
-    if (e == cudaSuccess && k >= 3) e = cudaStreamWaitEvent(S, c->ev_done[(k - 3) & 3], 0);
-    const bool serial = c->serialize_next || slot == c->prev_slot || (inplace && c->prev_post);
-    if (e == cudaSuccess && serial) e = wait_prev_frame(c);
-    c->serialize_next = false;
+    cudaStream_t S = c->fstream[k % PIPE];
+    cudaError_t e = sync_fork(c, (int)(k % PIPE));
+    // the planes of this frame number mod PIPE (raw, hit, the object block) and the physical ring slot it takes were
+    // last used by frame k - PIPE, whose finishing passes ran on the post stream
+    if (e == cudaSuccess) e = wait_frame_done(c, S, PIPE);
+    // Beside the PIPE - 1 frames before it this frame may NOT run when one of them names the same ring slot (it
+    // reads that slot's previous record), when it writes its colour in place (modes 3/4 without G-buffer) while one
+    // of their passes may be walking the ring, or around a change of the shared sky constants.
+    bool serial = c->serialize_frames > 0;
+    for (int j = 0; j < PIPE - 1; j++) serial = serial || slot == c->recent_slot[j] || (inplace && c->recent_post[j]);
+    if (e == cudaSuccess && serial) e = wait_frame_done(c, S, 1);
+    if (c->serialize_frames > 0) c->serialize_frames--;
+    return e;
+}
+
+// The trace kernel of the frame being built has been enqueued.  A frame without finishing passes ends here.
+static cudaError_t end_trace(rt_ctx *c, bool post)
+{
+    if (!c->pipeline) return cudaSuccess;
+    const unsigned long long k = c->frame_no - 1;
+    cudaStream_t S = c->fstream[k % PIPE];
+    cudaError_t e = cudaEventRecord(c->ev_trace[k % EVR], S);
+    if (e == cudaSuccess && !post) {
+        e = wait_frame_done(c, S, 1);       // ev_done[k] stands for every frame up to k
+        if (e == cudaSuccess) e = cudaEventRecord(c->ev_done[k % EVR], S);
+    }
+    return e;
+}
+
+// The finishing passes (halo pack, post-processing; or the copy that closes a frame left without them) run on the
+// post stream: behind the frame's trace kernel and behind frame k-1 (whose result they read as history, and whose
+// halo rows they share).
+static cudaError_t begin_post(rt_ctx *c)
+{
+    if (!c->pipeline) return cudaSuccess;
+    const unsigned long long k = c->frame_no - 1;
+    cudaStream_t S = c->fstream[PIPE];
+    cudaError_t e = sync_fork(c, PIPE);     // e.g. the caller's halo-row copies between rt_halo_pack and rt_postprocess
+    if (e != cudaSuccess || c->prev_waited) return e;
+    e = cudaStreamWaitEvent(S, c->ev_trace[k % EVR], 0);
+    if (e == cudaSuccess) e = wait_frame_done(c, S, 1);
+    c->prev_waited = true;
     return e;
 }
 
@@ -331,7 +393,7 @@ static cudaError_t end_frame(rt_ctx *c)
 {
     if (!c->pipeline) return cudaSuccess;
     const unsigned long long k = c->frame_no - 1;
-    return cudaEventRecord(c->ev_done[k & 3], c->fstream[k & 1]);
+    return cudaEventRecord(c->ev_done[k % EVR], c->fstream[PIPE]);
 }
 
 int rt_set_stream(rt_ctx *c, void *cuda_stream)
@@ -362,7 +424,7 @@ int rt_synchronize(rt_ctx *c)
 {
     if (!c) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
-    for (int i = 0; i < 2; i++) if (c->fstream[i]) CU(c, cudaStreamSynchronize(c->fstream[i]));
+    for (int i = 0; i <= PIPE; i++) if (c->fstream[i]) CU(c, cudaStreamSynchronize(c->fstream[i]));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaStreamSynchronize(c->copy_stream)); // outstanding rt_download_rgba8_async read-backs
     CU(c, cudaStreamSynchronize(c->fence_stream));
@@ -582,26 +644,26 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
 
     // a frame left without its second pass is closed as aop_compute alone leaves it: pixels[slot] = the raw colour
     if (c->frame_pending_post) {
-        CU(c, wait_prev_frame(c));
+        CU(c, begin_post(c));
         CU(c, cudaMemcpyAsync(c->ring_color + (size_t)c->phys[c->last_slot] * c->npix, c->raw[c->last_par], c->npix * sizeof(float4),
-                              cudaMemcpyDeviceToDevice, cur_stream(c)));
+                              cudaMemcpyDeviceToDevice, post_stream(c)));
         CU(c, end_frame(c));
         c->frame_pending_post = false;
     }
     const bool sky_changed = !c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0;
-    if (sky_changed) c->serialize_next = true;      // the constants are shared by the frames in flight
+    if (sky_changed) c->serialize_frames = 1;       // the constants are shared by the frames in flight
     // frames that write normals / depth take a fresh physical slot; modes 3/4 without the G-buffer extension leave
     // both as they are (p_compute.glsl:223-246) and write their colour in place
     const bool writes_gbuffer = ao || (c->cfg.flags & RT_FLAG_PHONG_GBUFFER);
     CU(c, begin_frame(c, slot, !writes_gbuffer));
-    const int par = (int)((c->frame_no - 1) & 1);
-    cudaStream_t S = cur_stream(c);
+    const int par = frame_par(c);
+    cudaStream_t S = trace_stream(c);
     const int p_old = c->phys[slot];
     int p_new = p_old;
     if (writes_gbuffer) {
         p_new = c->retired[0];
-        c->retired[0] = c->retired[1];
-        c->retired[1] = p_old;
+        for (int i = 0; i + 1 < PIPE; i++) c->retired[i] = c->retired[i + 1];
+        c->retired[PIPE - 1] = p_old;
         c->phys[slot] = p_new;
     }
 
@@ -613,7 +675,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
         if (!c->big_dev[0]) {
             const size_t bytes = (size_t)big_tables_vec4(RT_MAX_SHAPES_LIMIT, RT_MAX_SHAPES_LIMIT, 0, 0) * sizeof(uint4) * 2;   // any mix of kinds fits
             for (int i = 0; i < 4; i++) { CU(c, cudaMallocHost((void **)&c->big_host[i], bytes)); CU(c, cudaEventCreateWithFlags(&c->ev_big[i], cudaEventDisableTiming)); }
-            for (int i = 0; i < 2; i++) CU(c, cudaMalloc((void **)&c->big_dev[i], bytes));
+            for (int i = 0; i < PIPE; i++) CU(c, cudaMalloc((void **)&c->big_dev[i], bytes));
             c->big_cap_vec4 = (int)(bytes / sizeof(uint4));
         }
         CU(c, cudaEventSynchronize(c->ev_big[k]));
@@ -643,7 +705,7 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
         CU(c, launch_sky_gamma(p.bg, p.AA, c->sky, S));
         c->sky_bg = p.bg;
         c->sky_valid = true;
-        c->serialize_next = true;   // the next frame (other stream) reads them too
+        c->serialize_frames = PIPE - 1;   // the next frames (other streams) read them too
     }
     // a frame that rt_postprocess finishes: the trace output is raw; the post-processing pass writes the frame
     GatherTargets g = band_gather_targets(c), none = {};
@@ -659,12 +721,10 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     c->frame_pending_post = post;
     c->halo_packed = false;
     c->prev_waited = false;
-    c->prev_slot = slot;
-    c->prev_post = post;
-    if (!post) {
-        CU(c, wait_prev_frame(c));   // ev_done[k] stands for every frame up to k
-        CU(c, end_frame(c));
-    }
+    for (int j = PIPE - 2; j > 0; j--) { c->recent_slot[j] = c->recent_slot[j - 1]; c->recent_post[j] = c->recent_post[j - 1]; }
+    c->recent_slot[0] = slot;
+    c->recent_post[0] = post;
+    CU(c, end_trace(c, post));
     return RT_OK;
 }
 
@@ -717,10 +777,8 @@ int rt_halo_pack(rt_ctx *c)
     }
     // the pack reads frame k-1's result (the wrapped row's first element under FLAT32) and, with linked bands or a
     // single band, writes halo rows that frame k-1's pass may still be reading: it follows frame k-1
-    const int fpar = c->last_par;
-    CU(c, sync_fork(c, fpar));
-    if (!c->prev_waited) { CU(c, wait_prev_frame(c)); c->prev_waited = true; }
-    CU(c, launch_halo_pack(q, cur_stream(c)));
+    CU(c, begin_post(c));
+    CU(c, launch_halo_pack(q, post_stream(c)));
     c->halo_packed = true;
     if (c->cfg.band_count > 1 && !c->halo_direct) {
         // the caller moves the rows (rt_get_halo) on the context's stream: behind the pack, ahead of the pass
@@ -744,7 +802,7 @@ int rt_postprocess(rt_ctx *c)
     if (!c) return RT_EINVAL;
     if (!c->frame_pending_post) return fail(c, RT_ESTATE, "rt_postprocess: the last frame was not rendered in mode 1");
     CU(c, cudaSetDevice(c->cfg.device));
-    cudaStream_t S = cur_stream(c);
+    cudaStream_t S = post_stream(c);
     const int fpar = c->last_par;
     if (!c->halo_packed) {
         if (c->cfg.band_count > 1) return fail(c, RT_ESTATE, "rt_postprocess: call rt_halo_pack and exchange the halo rows first");
@@ -755,8 +813,7 @@ int rt_postprocess(rt_ctx *c)
     }
     PostParams q{};
     fill_post(c, q);
-    CU(c, sync_fork(c, fpar));
-    if (!c->prev_waited) { CU(c, wait_prev_frame(c)); c->prev_waited = true; }   // the history is frame k-1's result
+    CU(c, begin_post(c));   // the history is frame k-1's result
     // rt_stats.ms_post_last is the post-processing kernel's own duration: the pack kernel and the wait for the
     // previous frame are before the first event
     if (c->timing) CU(c, cudaEventRecord(c->ev[fpar][2], S));
@@ -859,7 +916,7 @@ int rt_fence_status(rt_ctx *c, int *timed_out)
     if (!c || !timed_out) return RT_EINVAL;
     if (c->link_world < 1) return fail(c, RT_ESTATE, "rt_fence_status: call rt_link_peers first");
     CU(c, cudaSetDevice(c->cfg.device));
-    for (int i = 0; i < 2; i++) if (c->fstream[i]) CU(c, cudaStreamSynchronize(c->fstream[i]));
+    for (int i = 0; i <= PIPE; i++) if (c->fstream[i]) CU(c, cudaStreamSynchronize(c->fstream[i]));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaStreamSynchronize(c->fence_stream));
     unsigned long long st = 0;
@@ -1209,14 +1266,14 @@ int rt_reset_ring(rt_ctx *c)
 {
     if (!c) return RT_EINVAL;
     CU(c, cudaSetDevice(c->cfg.device));
-    const size_t ring = c->npix * (c->cfg.num_frames + 2);
+    const size_t ring = c->npix * (c->cfg.num_frames + PIPE);
     CU(c, join_frames(c));
     mark_fork(c);
     CU(c, cudaMemsetAsync(c->ring_color, 0, ring * sizeof(float4), c->stream));
     CU(c, cudaMemsetAsync(c->ring_normal, 0, ring * sizeof(float4), c->stream));
     CU(c, cudaMemsetAsync(c->ring_depth_xy, 0, ring * sizeof(float2), c->stream));
     CU(c, cudaMemsetAsync(c->ring_depth_w, 0, ring * sizeof(float), c->stream));
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < PIPE; i++) {
         CU(c, cudaMemsetAsync(c->raw[i], 0, c->npix * sizeof(float4), c->stream));
         CU(c, cudaMemsetAsync(c->hit[i], 0, c->npix * sizeof(int), c->stream));
     }

@@ -510,7 +510,7 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
     }
     if (active) {
         const int y = q.y0 + yl;
-        // 32-bit element indices (rt_create: W * H * (NF + 2) < 2^31): half the registers of size_t offsets
+        // 32-bit element indices (rt_create: W * H * (NF + 3) < 2^31): half the registers of size_t offsets
         const unsigned plane = (unsigned)q.rows * (unsigned)q.W;
         const unsigned pix = (unsigned)yl * (unsigned)q.W + (unsigned)x;
         const float4 *nslot = q.ring_normal + (unsigned)q.phys[q.slot] * plane;

@@ -175,8 +175,8 @@ struct PostParams {
     int slot, edge_mode;
     int band_index, band_count;
     const float4 *raw;    // aop_compute output of this frame
-    int phys[RT_MAX_FRAMES]; // ring slot -> physical slot of the planes below (NF + 2 of them; rt_capi.cu)
-    float4 *ring_color;   // [NF + 2][rows*W]
+    int phys[RT_MAX_FRAMES]; // ring slot -> physical slot of the planes below (NF + 3 of them; rt_capi.cu)
+    float4 *ring_color;   // [NF + 3][rows*W]
     const float4 *ring_normal;
     const float2 *ring_depth_xy;
     const float *ring_depth_w;
