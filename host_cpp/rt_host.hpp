@@ -91,6 +91,16 @@ inline scene init_scene5() // src/scene.h:67-109
                  mk_sphere({ 0, -35, 0 }, 33, { 0.8f, 0.6f, 0.2f }) };
     return s;
 }
+// scene5 with the emissive rectangle its source keeps commented out (src/scene.h:79-85) in place of the emissive
+// sphere; rectangles are only intersected under RT_FLAG_RECTANGLES
+inline scene init_scene5_rectangle()
+{
+    scene s;
+    auto r = std::make_shared<rectangle>(vec3{ 4, 6, 4 }, vec3{ 0, 0, -8 }, vec3{ -8, 0, 0 }, vec3{ 1.5f, 1.5f, 1.5f });
+    r->emissive = true;
+    s.shapes = { r, mk_sphere({ 0, 0, 0 }, 2, { 0.2f, 0.6f, 0.8f }, 0.4f), mk_sphere({ 0, -35, 0 }, 33, { 0.8f, 0.6f, 0.2f }) };
+    return s;
+}
 inline scene init_scene6() // src/scene.h:111-167
 {
     scene s;
@@ -143,14 +153,18 @@ public:
     rt_ctx *rt = nullptr;
     int width, height, aa;
 
-    Application(int w, int h, int aa_, int edge_mode = RT_EDGE_FLAT32, int device = 0) : rand_buffer(8 * aa_), width(w), height(h), aa(aa_)
+    // rectangles: RT_FLAG_RECTANGLES, and scene5 is built with its commented-out emissive rectangle
+    Application(int w, int h, int aa_, int edge_mode = RT_EDGE_FLAT32, int device = 0, bool rectangles = false)
+        : rand_buffer(8 * aa_), width(w), height(h), aa(aa_)
     {
+        if (rectangles) scene5 = init_scene5_rectangle();
         mycam.lighting = 1;                                   // initGeom(), src/main.cpp:393
         uniforms.background = { 13 / 255.0f, 153 / 255.0f, 219 / 255.0f, 0 }; // SKY, computeInitGeom()
         uniforms.light_pos = { -12, 8, 7, 0 };                // DEFAULT_LIGHT_POS
         rt_config cfg{};
         cfg.width = w; cfg.height = h; cfg.aa = aa_; cfg.recursion_depth = 20; cfg.num_frames = NUM_FRAMES;
         cfg.edge_mode = edge_mode; cfg.device = device;
+        cfg.flags = rectangles ? RT_FLAG_RECTANGLES : 0;
         if (rt_create(&cfg, &rt) != RT_OK) throw std::runtime_error(rt_last_error(nullptr));
     }
     ~Application() { rt_destroy(rt); }

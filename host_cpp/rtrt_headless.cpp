@@ -2,7 +2,7 @@
 // loop, src/main.cpp:839-847, without the window) and writes frames as binary PPM / raw float32.
 //
 //   rtrt_headless [--size WxH] [--aa N] [--frames N] [--mode 1..4] [--scene 0..2] [--keys wasdqezc..]
-//                 [--light] [--fullscreen] [--out prefix] [--raw] [--every N]
+//                 [--light] [--fullscreen] [--rectangles] [--out prefix] [--raw] [--every N]
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -32,7 +32,7 @@ static void write_ppm(const std::string &path, const std::vector<float> &img, in
 int main(int argc, char **argv)
 {
     int w = 440, h = 330, aa = 4, frames = 8, mode = 1, scene = 0, every = 0;
-    bool light = false, full = false, raw = false;
+    bool light = false, full = false, raw = false, rectangles = false;
     std::string keys, out = "frame";
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
@@ -48,10 +48,11 @@ int main(int argc, char **argv)
         else if (a == "--light") light = true;
         else if (a == "--fullscreen") full = true;
         else if (a == "--raw") raw = true;
+        else if (a == "--rectangles") rectangles = true;
         else { fprintf(stderr, "unknown option %s\n", a.c_str()); return 2; }
     }
     try {
-        rth::Application app(w, h, aa);
+        rth::Application app(w, h, aa, RT_EDGE_FLAT32, 0, rectangles);
         for (int k = 0; k < scene; k++) app.toggle_scene();
         if (light) app.toggle_light_movement();
         if (full) app.toggle_fullscreen_aspect();

@@ -341,9 +341,14 @@ class Application:
     names; the SSBO itself is the device-resident ring owned by ``self.rt``."""
 
     def __init__(self, width: int = host.WIDTH, height: int = host.HEIGHT, aa: int = host.AA,
-                 edge_mode: int = L.EDGE_FLAT32, device: int = 0, rand_seed: int = 0xC0FFEE, tracer=None):
+                 edge_mode: int = L.EDGE_FLAT32, device: int = 0, rand_seed: int = 0xC0FFEE, tracer=None,
+                 rectangles: bool = False):
+        """``rectangles``: the context intersects rectangle records (FLAG_RECTANGLES) and scene5 is built with the
+        emissive rectangle its source keeps commented out instead of the emissive sphere (src/scene.h:79-85)"""
         self.aspect_ratio = host.ASPECT_RATIO
         self.scenes = {k: f() for k, (f, _) in host.SCENES.items()}
+        if rectangles:
+            self.scenes["scene5"] = host.init_scene5_rectangle()
         self.myscene = self.scenes["scene1"]
         self.true_num_scene_objects = len(self.myscene.shapes)
         self.mycam = host.camera()
@@ -356,7 +361,8 @@ class Application:
         self.frames_rendered = 0
         self.rand_seed = rand_seed
         self.horizontal = self.vertical = self.llc_minus_campos = None
-        self.rt = tracer if tracer is not None else RayTracer(width, height, aa, edge_mode=edge_mode, device=device)
+        self.rt = tracer if tracer is not None else RayTracer(width, height, aa, edge_mode=edge_mode, device=device,
+                                                              flags=L.FLAG_RECTANGLES if rectangles else 0)
 
     # key handlers of src/main.cpp:225-283 as methods
     def toggle_scene(self):  # V

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "rt_kernels.cuh"
 
@@ -76,6 +77,12 @@ struct rt_ctx {
     cudaEvent_t ev_big[4]{};
     uint4 *big_dev[PIPE] = {};
     int big_cap_vec4 = 0;
+    // uniform grid over the bounded objects of a scene of >= RT_GRID_MIN_SHAPES objects (rebuilt by rt_upload_scene;
+    // RT_GRID=0 leaves it out for A/B runs: the results are the same bits)
+    bool grid_enabled = true;
+    unsigned *grid_cells = nullptr;
+    unsigned short *grid_items = nullptr;
+    GridView grid{};
     FrameParams fp{};
     int last_mode = 0, last_slot = 0;
     bool frame_pending_post = false, halo_packed = false;
@@ -152,6 +159,7 @@ static void free_all(rt_ctx *c)
     for (cudaEvent_t e : c->ev_trace) if (e) cudaEventDestroy(e);
     if (c->ev_user) cudaEventDestroy(c->ev_user);
     cudaFree(c->rgba8); cudaFree(c->pack_count);
+    cudaFree(c->grid_cells); cudaFree(c->grid_items);
     for (int i = 0; i < 4; i++) { if (c->big_host[i]) cudaFreeHost(c->big_host[i]); if (c->ev_big[i]) cudaEventDestroy(c->ev_big[i]); }
     if (c->ev_fence_in) cudaEventDestroy(c->ev_fence_in);
     if (c->ev_fence_done) cudaEventDestroy(c->ev_fence_done);
@@ -251,6 +259,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     alloc0((void **)&c->stats, STAT_STRIPES * STAT_STRIDE * sizeof(unsigned long long));
     alloc0((void **)&c->sky, 12 * sizeof(float));
     if (const char *k = getenv("RT_AO_CULL")) c->ao_cull = strcmp(k, "0") != 0;
+    if (const char *k = getenv("RT_GRID")) c->grid_enabled = strcmp(k, "0") != 0;
     if (const char *k = getenv("RT_AO_KERNEL")) {
         if (!strcmp(k, "phased")) c->ao_kernel = AO_KERNEL_PHASED;
         else if (strcmp(k, "pulled")) {
@@ -441,6 +450,113 @@ int rt_set_timing(rt_ctx *c, int enabled)
     return RT_OK;
 }
 
+// Uniform grid over the spheres and (under RT_FLAG_RECTANGLES) rectangles of the scene, in the order in which
+// build_big_tables lists them.  Every object goes into each cell its bounding box, grown by `margin`, touches; the
+// walk on the device (rt_trace_common.cuh: closest_hit_grid) relies on exactly that for its early exit.
+static int build_grid(rt_ctx *c)
+{
+    c->grid = GridView{};
+    const int n = c->nshapes;
+    const bool rectangles = (c->cfg.flags & RT_FLAG_RECTANGLES) != 0;
+    if (!c->grid_enabled || n < RT_GRID_MIN_SHAPES) return RT_OK;
+    struct Box { float lo[3], hi[3]; unsigned short item; };
+    std::vector<Box> boxes;
+    int nsph = 0, nrc = 0;
+    for (int i = 0; i < n; i++) {
+        const DevShape &s = c->shapes[i];
+        Box b{};
+        if (s.id == SPHERE_ID) {
+            const float r = fabsf(s.s0.w), ctr[3] = { s.s0.x, s.s0.y, s.s0.z };
+            for (int a = 0; a < 3; a++) { b.lo[a] = ctr[a] - r; b.hi[a] = ctr[a] + r; }
+            b.item = (unsigned short)nsph++;
+        } else if (s.id == RECTANGLE_ID && rectangles) {
+            const float l[3] = { s.s3.x, s.s3.y, s.s3.z };
+            const float u[3] = { c->edges[i][0].x, c->edges[i][0].y, c->edges[i][0].z }, r[3] = { c->edges[i][1].x, c->edges[i][1].y, c->edges[i][1].z };
+            for (int a = 0; a < 3; a++) {
+                const float v[4] = { l[a], l[a] + u[a], l[a] + r[a], l[a] + u[a] + r[a] };
+                b.lo[a] = fminf(fminf(v[0], v[1]), fminf(v[2], v[3]));
+                b.hi[a] = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
+            }
+            b.item = (unsigned short)(0x8000u | (unsigned)nrc++);
+        } else {
+            continue;
+        }
+        bool finite = true;
+        for (int a = 0; a < 3; a++) finite = finite && std::isfinite(b.lo[a]) && std::isfinite(b.hi[a]);
+        if (!finite) return RT_OK;      // a scene with NaN / inf geometry is walked without a grid
+        boxes.push_back(b);
+    }
+    if (boxes.empty()) return RT_OK;
+    float lo[3], hi[3];
+    for (int a = 0; a < 3; a++) { lo[a] = boxes[0].lo[a]; hi[a] = boxes[0].hi[a]; }
+    for (const Box &b : boxes) for (int a = 0; a < 3; a++) { lo[a] = fminf(lo[a], b.lo[a]); hi[a] = fmaxf(hi[a], b.hi[a]); }
+    float ext = 0.0f, amax = 0.0f;
+    for (int a = 0; a < 3; a++) { ext = fmaxf(ext, hi[a] - lo[a]); amax = fmaxf(amax, fmaxf(fabsf(lo[a]), fabsf(hi[a]))); }
+    // far above the rounding of the walk (binary32 at this scene's coordinates: ~1e-7 * amax) and of a hit point
+    const float margin = fmaxf(1e-3f * fmaxf(ext, amax), 1e-4f);
+    for (int a = 0; a < 3; a++) { lo[a] -= 2.0f * margin; hi[a] += 2.0f * margin; }
+    double vol = 1.0;
+    for (int a = 0; a < 3; a++) vol *= (double)(hi[a] - lo[a]);
+    const double per_len = cbrt(4.0 * (double)boxes.size() / vol);   // about four cells per object
+    int dim[3];
+    float cell[3];
+    for (int a = 0; a < 3; a++) {
+        int d = (int)lround((double)(hi[a] - lo[a]) * per_len);
+        dim[a] = d < 1 ? 1 : (d > RT_GRID_MAX_DIM ? RT_GRID_MAX_DIM : d);
+        cell[a] = (hi[a] - lo[a]) / (float)dim[a];
+    }
+    const int ncell = dim[0] * dim[1] * dim[2];
+    auto range = [&](const Box &b, int a, int &i0, int &i1) {
+        i0 = (int)floorf((b.lo[a] - margin - lo[a]) / cell[a]);
+        i1 = (int)floorf((b.hi[a] + margin - lo[a]) / cell[a]);
+        i0 = i0 < 0 ? 0 : (i0 >= dim[a] ? dim[a] - 1 : i0);
+        i1 = i1 < 0 ? 0 : (i1 >= dim[a] ? dim[a] - 1 : i1);
+    };
+    std::vector<unsigned> cells((size_t)ncell + 1, 0u);
+    for (int pass = 0; pass < 2; pass++) {
+        std::vector<unsigned> fill;
+        std::vector<unsigned short> items;
+        if (pass == 1) {
+            unsigned run = 0;
+            for (int k = 0; k < ncell; k++) { const unsigned cnt = cells[k]; cells[k] = run; run += cnt; }
+            cells[ncell] = run;
+            fill.assign(cells.begin(), cells.end() - 1);
+            items.resize(run);
+        }
+        for (const Box &b : boxes) {
+            int x0, x1, y0, y1, z0, z1;
+            range(b, 0, x0, x1); range(b, 1, y0, y1); range(b, 2, z0, z1);
+            for (int z = z0; z <= z1; z++)
+                for (int y = y0; y <= y1; y++)
+                    for (int x = x0; x <= x1; x++) {
+                        const int k = (z * dim[1] + y) * dim[0] + x;
+                        if (pass == 0) cells[k]++;
+                        else items[fill[k]++] = b.item;
+                    }
+        }
+        if (pass == 1) {
+            // scene uploads are rare: finish what is in flight, replace the device copy
+            int rc = rt_synchronize(c);
+            if (rc != RT_OK) return rc;
+            cudaFree(c->grid_cells); cudaFree(c->grid_items);
+            c->grid_cells = nullptr; c->grid_items = nullptr;
+            CU(c, cudaMalloc((void **)&c->grid_cells, cells.size() * sizeof(unsigned)));
+            CU(c, cudaMalloc((void **)&c->grid_items, (items.empty() ? 1 : items.size()) * sizeof(unsigned short)));
+            CU(c, cudaMemcpy(c->grid_cells, cells.data(), cells.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
+            if (!items.empty()) CU(c, cudaMemcpy(c->grid_items, items.data(), items.size() * sizeof(unsigned short), cudaMemcpyHostToDevice));
+        }
+    }
+    GridView g{};
+    g.cells = c->grid_cells; g.items = c->grid_items;
+    g.lo = make_float3(lo[0], lo[1], lo[2]); g.hi = make_float3(hi[0], hi[1], hi[2]);
+    g.cell = make_float3(cell[0], cell[1], cell[2]);
+    g.inv_cell = make_float3(1.0f / cell[0], 1.0f / cell[1], 1.0f / cell[2]);
+    g.dim = make_int3(dim[0], dim[1], dim[2]);
+    g.margin = margin;
+    c->grid = g;
+    return RT_OK;
+}
+
 // loadShapeBuffer's records (src/main.cpp:395-469) -> device table
 int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
 {
@@ -463,7 +579,8 @@ int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
         c->edges[i][1] = v[2];
     }
     c->nshapes = n;
-    return RT_OK;
+    CU(c, cudaSetDevice(c->cfg.device));
+    return build_grid(c);
 }
 
 static inline float3 f3(const rt_vec4 &v) { return make_float3(v.x, v.y, v.z); }
@@ -685,6 +802,8 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
         CU(c, cudaEventRecord(c->ev_big[k], S));
         p.big = c->big_dev[par];
         p.big_vec4 = nv;
+        // the grid covers the scene as uploaded: a frame that draws fewer objects than that walks the lists
+        p.grid = (nobj == c->nshapes) ? c->grid : GridView{};
     }
 
     TraceOut o{};

@@ -67,6 +67,47 @@ __device__ __forceinline__ void shadow_occluder(float t, float3 l, double L2, fl
     }
 }
 
+// the bounded objects of a big scene through the grid: an AND over the objects the ray meets before the light, so
+// the order is free and the walk ends at the first occluder or where the cells begin beyond the light
+__device__ __forceinline__ void shadow_grid(const BigTables &p, float3 new_pos, float3 l, double L2, float len, bool &lit)
+{
+    const GridView &g = p.grid;
+    GridWalk w = grid_enter(g, new_pos, l, len * 1.01f + 0.01f);
+    if (!w.alive) return;
+    unsigned last = 0xffffffffu;
+#pragma unroll 1
+    while (lit) {
+        int axis;
+        const float t_exit = grid_cell_exit(g, w, axis);
+        const int cell = (w.iz * g.dim.y + w.iy) * g.dim.x + w.ix;
+        const unsigned i0 = __ldg(g.cells + cell), i1 = __ldg(g.cells + cell + 1);
+#pragma unroll 1
+        for (unsigned k = i0; k < i1 && lit; k++) {
+            const unsigned it = __ldg(g.items + k);
+            if (it == last) continue;
+            last = it;
+            if (it & 0x8000u) {
+                const int j = (int)(it & 0x7fffu);
+                const float3 n = xyz(p.rc_n[j]);
+                const float denom = dot3(n, l);
+                if (!(denom < 0.001f && denom > -0.001f)) {
+                    const float num = dot3(n, sub3(xyz(p.rc_p[j]), new_pos));
+                    if (num != 0.0f) {
+                        const float t = __fdiv_rn(num, denom);
+                        if (t > 0.0001f && rect_inside(t, new_pos, l, p.rc_p[j], p.rc_r[j], p.rc_u[j])) shadow_occluder(t, l, L2, len, lit);
+                    }
+                }
+            } else {
+                const float4 s = p.sph[it];
+                const float3 pmc = sub3(new_pos, xyz(s));
+                const float b = dot3(l, pmc);
+                shadow_occluder(sphere_roots(b, b * b - dot3(pmc, pmc) + s.w), l, L2, len, lit);
+            }
+        }
+        if (!(t_exit < w.t_end) || !grid_step(g, w, axis)) break;
+    }
+}
+
 template <bool RC, class TAB>
 __device__ __forceinline__ bool shadow_ray(const FrameParams &fp, const TAB &p, float3 pos)
 {
@@ -77,6 +118,19 @@ __device__ __forceinline__ bool shadow_ray(const FrameParams &fp, const TAB &p, 
     const double L2 = __dmul_rn((double)len, (double)len);
     bool lit = true;
     if constexpr (TAB::BIG) {
+        if (p.grid.dim.x > 0) {
+#pragma unroll 1
+            for (int j = 0; j < p.npl; j++) {
+                const float3 n = xyz(p.pl_n[j]);
+                const float denom = dot3(n, l);
+                if (lit && !(denom < 0.001f && denom > -0.001f)) {
+                    const float num = dot3(n, sub3(xyz(p.pl_p0[j]), new_pos));
+                    if (num != 0.0f) shadow_occluder(__fdiv_rn(num, denom), l, L2, len, lit);
+                }
+            }
+            shadow_grid(p, new_pos, l, L2, len, lit);
+            return lit;
+        }
 #pragma unroll 2
         for (int i = 0; i < p.nsph; i++) {
             if (lit) {

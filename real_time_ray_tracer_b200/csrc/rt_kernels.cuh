@@ -24,6 +24,21 @@ struct DevShape {
     int pad;
 };
 
+// Uniform grid over the bounded objects (spheres, rectangles) of a scene of >= RT_GRID_MIN_SHAPES objects, built on
+// the host by rt_upload_scene (rt_capi.cu: build_grid).  cells[c] .. cells[c + 1] delimit the items of cell
+// c = (iz * dim.y + iy) * dim.x + ix; an item is the object's position in the sphere list, or 0x8000 | its
+// position in the rectangle list.  Planes are unbounded and stay outside.  dim.x == 0: no grid.
+constexpr int RT_GRID_MIN_SHAPES = 64;
+constexpr int RT_GRID_MAX_DIM = 24;
+struct GridView {
+    const unsigned *cells;
+    const unsigned short *items;
+    float3 lo, hi;          // the box of the grid
+    float3 cell, inv_cell;  // cell size and its reciprocal per axis
+    int3 dim;
+    float margin;           // a hit this far in front of a cell's exit ends the walk (>> the rounding of the walk)
+};
+
 // Everything a trace dispatch needs besides the output planes; passed by value as a
 // __grid_constant__ kernel parameter (constant bank), so the per-object loop reads it with
 // warp-uniform addresses.  This replaces the per-frame 55.8 MB SSBO upload of
@@ -70,6 +85,7 @@ struct FrameParams {
     const uint4 *big;
     int big_vec4;                  // size of the block in 16-byte units; 0 = small scene
     int pad3;
+    GridView grid;                 // big scenes only
     float4 rand[2 * RT_MAX_AA];
 };
 
@@ -81,6 +97,7 @@ struct BigTables {
     const DevShape *shapes;
     const float4 *sph, *sph_cam, *pl_n, *pl_p0, *rc_n, *rc_p, *rc_r, *rc_u;
     const int *sph_idx, *pl_idx, *rc_idx;
+    GridView grid;
 };
 // sizes in 16-byte units of the sections of the block, in this order: shapes, sph, sph_cam, pl_n, pl_p0, rc_n, rc_p,
 // rc_r, rc_u, sph_idx, pl_idx, rc_idx (the index lists padded to a multiple of four entries)

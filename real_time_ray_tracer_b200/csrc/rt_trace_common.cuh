@@ -128,6 +128,127 @@ __device__ __forceinline__ float div_aa(const FrameParams &p, float x)
     return (p.invAA != 0.0f) ? x * p.invAA : __fdiv_rn(x, (float)p.AA);
 }
 
+// ---------------------------------------------------------------------------------------------
+// uniform grid (scenes of >= RT_GRID_MIN_SHAPES objects)
+// ---------------------------------------------------------------------------------------------
+// The result of a closest hit does not depend on the order in which objects are tested: a candidate replaces the
+// current one when it is nearer, or equally near and earlier in the scene.  A walk over the grid therefore gives
+// the brute-force loop's bits as long as it never stops before the winner has been tested.  The walk visits the
+// cells the ray pierces front to back (one exact-to-rounding exit distance per cell, recomputed from the cell's
+// planes, no accumulated increments), tests every item of a cell with the same *_candidate arithmetic, and stops
+// only when the best hit lies more than `margin` in front of the cell's exit: an untested object's hit point would
+// lie in a later cell, hence at least margin - rounding behind the best one.  Objects are entered into every cell
+// their bounding box, grown by that same margin, touches (host), so a walk that rounds into a neighbouring cell at
+// an edge still meets everything near the ray.
+__device__ __forceinline__ void sphere_candidate_any(float b, float del, int idx, float tmin, Closest &c)
+{
+    if (del >= 0.0f) {
+        float im = sqrt_fast(del);
+        if (!sqrt_fast_ok(del)) im = sqrt_slow(del);
+        const float t1 = -b + im;
+        const float t2 = -b - im;
+        const float res_t = (t2 < 0.0f) ? t1 : t2;
+        const unsigned bits = __float_as_uint(res_t);
+        if (res_t > tmin && (bits < c.tb || (bits == c.tb && idx < c.ind))) {
+            c.tb = bits;
+            c.ind = idx;
+        }
+    }
+}
+
+struct GridWalk {
+    int ix, iy, iz, sx, sy, sz;
+    float ox, oy, oz, ix_inv, iy_inv, iz_inv;   // origin, reciprocal direction (0 marks an axis the ray does not move along)
+    float t_end;                                 // the ray leaves the box here
+    bool alive;
+};
+
+// enter the grid; `t_limit`: nothing beyond it matters (a shadow ray ends at the light)
+__device__ __forceinline__ GridWalk grid_enter(const GridView &g, float3 pos, float3 dir, float t_limit)
+{
+    GridWalk w;
+    w.alive = false;
+    float t0 = 0.0f, t1 = t_limit;
+    const float o[3] = { pos.x, pos.y, pos.z }, d[3] = { dir.x, dir.y, dir.z };
+    const float lo[3] = { g.lo.x, g.lo.y, g.lo.z }, hi[3] = { g.hi.x, g.hi.y, g.hi.z };
+    float inv[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        if (fabsf(d[a]) < 1e-30f) {
+            inv[a] = 0.0f;
+            if (!(o[a] >= lo[a] && o[a] <= hi[a])) return w;   // parallel to the slab and outside it (NaN: outside)
+        } else {
+            inv[a] = 1.0f / d[a];
+            const float ta = (lo[a] - o[a]) * inv[a], tb = (hi[a] - o[a]) * inv[a];
+            t0 = fmaxf(t0, fminf(ta, tb));
+            t1 = fminf(t1, fmaxf(ta, tb));
+        }
+    }
+    if (!(t0 <= t1)) return w;
+    w.t_end = t1;
+    w.ox = o[0]; w.oy = o[1]; w.oz = o[2];
+    w.ix_inv = inv[0]; w.iy_inv = inv[1]; w.iz_inv = inv[2];
+    w.sx = d[0] > 0.0f ? 1 : -1; w.sy = d[1] > 0.0f ? 1 : -1; w.sz = d[2] > 0.0f ? 1 : -1;
+    const float px = o[0] + t0 * d[0], py = o[1] + t0 * d[1], pz = o[2] + t0 * d[2];
+    w.ix = min(max((int)floorf((px - g.lo.x) * g.inv_cell.x), 0), g.dim.x - 1);
+    w.iy = min(max((int)floorf((py - g.lo.y) * g.inv_cell.y), 0), g.dim.y - 1);
+    w.iz = min(max((int)floorf((pz - g.lo.z) * g.inv_cell.z), 0), g.dim.z - 1);
+    w.alive = true;
+    return w;
+}
+
+// exit distance of the current cell; `axis` receives the axis the ray leaves through
+__device__ __forceinline__ float grid_cell_exit(const GridView &g, const GridWalk &w, int &axis)
+{
+    const float inf = __int_as_float(0x7f800000);
+    const float tx = (w.ix_inv != 0.0f) ? (g.lo.x + (float)(w.ix + (w.sx > 0 ? 1 : 0)) * g.cell.x - w.ox) * w.ix_inv : inf;
+    const float ty = (w.iy_inv != 0.0f) ? (g.lo.y + (float)(w.iy + (w.sy > 0 ? 1 : 0)) * g.cell.y - w.oy) * w.iy_inv : inf;
+    const float tz = (w.iz_inv != 0.0f) ? (g.lo.z + (float)(w.iz + (w.sz > 0 ? 1 : 0)) * g.cell.z - w.oz) * w.iz_inv : inf;
+    axis = (tx <= ty) ? ((tx <= tz) ? 0 : 2) : ((ty <= tz) ? 1 : 2);
+    return fminf(tx, fminf(ty, tz));
+}
+
+__device__ __forceinline__ bool grid_step(const GridView &g, GridWalk &w, int axis)
+{
+    if (axis == 0) { w.ix += w.sx; return (unsigned)w.ix < (unsigned)g.dim.x; }
+    if (axis == 1) { w.iy += w.sy; return (unsigned)w.iy < (unsigned)g.dim.y; }
+    w.iz += w.sz;
+    return (unsigned)w.iz < (unsigned)g.dim.z;
+}
+
+// the bounded objects of a big scene through the grid (the planes are walked by the caller)
+__device__ __forceinline__ void closest_hit_grid(const BigTables &p, float3 pos, float3 dir, float tmin, Closest &c)
+{
+    const GridView &g = p.grid;
+    GridWalk w = grid_enter(g, pos, dir, __int_as_float(0x7f800000));
+    if (!w.alive) return;
+    unsigned last = 0xffffffffu;
+#pragma unroll 1
+    for (;;) {
+        int axis;
+        const float t_exit = grid_cell_exit(g, w, axis);
+        const int cell = (w.iz * g.dim.y + w.iy) * g.dim.x + w.ix;
+        const unsigned i0 = __ldg(g.cells + cell), i1 = __ldg(g.cells + cell + 1);
+#pragma unroll 1
+        for (unsigned k = i0; k < i1; k++) {
+            const unsigned it = __ldg(g.items + k);
+            if (it == last) continue;       // the same object in consecutive cells
+            last = it;
+            if (it & 0x8000u) {
+                const int j = (int)(it & 0x7fffu);
+                rect_candidate(p, j, dot3(xyz(p.rc_n[j]), sub3(xyz(p.rc_p[j]), pos)), pos, dir, tmin, c);
+            } else {
+                const float4 s = p.sph[it];
+                const float3 pmc = sub3(pos, xyz(s));
+                const float b = dot3(dir, pmc);
+                sphere_candidate_any(b, b * b - dot3(pmc, pmc) + s.w, p.sph_idx[it], tmin, c);
+            }
+        }
+        if (c.ind >= 0 && __uint_as_float(c.tb) < t_exit - g.margin) break;
+        if (!(t_exit < w.t_end) || !grid_step(g, w, axis)) break;
+    }
+}
+
 // TAB = FrameParams (lists in the constant bank, at most RT_MAX_SHAPES entries, the sphere loop unrolled) or
 // BigTables (lists in shared memory, rolled loops).
 // RC: the rectangle list is walked at all (a kernel instance per case: the headline scenes have none and keep the
@@ -137,6 +258,17 @@ __device__ __forceinline__ int closest_hit(const TAB &p, float3 pos, float3 dir,
 {
     Closest c = { 0xffffffffu, -1 };
     if constexpr (TAB::BIG) {
+        if (p.grid.dim.x > 0) {
+            // planes first (their tie rule carries the scene index), then the bounded objects through the grid
+#pragma unroll 1
+            for (int j = 0; j < p.npl; j++) {
+                const float3 n = xyz(p.pl_n[j]);
+                plane_candidate(dot3(n, sub3(xyz(p.pl_p0[j]), pos)), dot3(n, dir), p.pl_idx[j], tmin, c);
+            }
+            closest_hit_grid(p, pos, dir, tmin, c);
+            t_out = (c.ind < 0) ? -1.0f : __uint_as_float(c.tb);
+            return c.ind;
+        }
 #pragma unroll 2
         for (int i = 0; i < p.nsph; i++) {
             const float4 s = p.sph[i];
@@ -306,6 +438,7 @@ __device__ __forceinline__ BigTables big_tables(const FrameParams &p, const uint
     b.sph_idx = reinterpret_cast<const int *>(q); q += big_idx_vec4(p.nsph);
     b.pl_idx = reinterpret_cast<const int *>(q); q += big_idx_vec4(p.npl);
     b.rc_idx = reinterpret_cast<const int *>(q);
+    b.grid = p.grid;
     return b;
 }
 
@@ -351,6 +484,9 @@ template <> struct SceneSel<SCENE_BIG> {
     __device__ __forceinline__ unsigned candidates(float, float) const { return 0xffffffffu; }   // no tile test
     __device__ __forceinline__ int primary_masked(float3 dir, float tmin, float &t, unsigned) const
     {
+        // through the grid the camera ray is a general ray from the camera: the per-frame camera constants are the
+        // same operations done on the host, so both give the same bits
+        if (bt.grid.dim.x > 0) return closest_hit<true>(bt, cam, dir, tmin, t);
         return closest_hit_primary<true>(bt, cam, dir, tmin, t);
     }
     __device__ __forceinline__ int closest(float3 pos, float3 dir, float tmin, float &t) const

@@ -16,8 +16,9 @@ def test_cpp_host_builds():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode,scene,keys,light", [(1, 0, "d", False), (4, 1, "ws", True), (2, 2, "a", False), (3, 0, "", True)])
-def test_cpp_host_equals_python_application(tmp_path, mode, scene, keys, light):
+@pytest.mark.parametrize("mode,scene,keys,light,rectangles", [(1, 0, "d", False, False), (4, 1, "ws", True, False), (2, 2, "a", False, False),
+                                                              (3, 0, "", True, False), (1, 1, "q", False, True), (4, 1, "", True, True)])
+def test_cpp_host_equals_python_application(tmp_path, mode, scene, keys, light, rectangles):
     import real_time_ray_tracer_b200 as rtb
 
     W, H, AA, frames = 120, 90, 4, 10
@@ -28,11 +29,13 @@ def test_cpp_host_equals_python_application(tmp_path, mode, scene, keys, light):
         cmd += ["--keys", keys]
     if light:
         cmd += ["--light"]
+    if rectangles:
+        cmd += ["--rectangles"]     # scene 1 = scene5 with its commented-out emissive rectangle, RT_FLAG_RECTANGLES
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     got = np.fromfile(f"{out}_{frames - 1:04d}.f32", dtype=np.float32).reshape(H, W, 4)
 
-    app = rtb.Application(W, H, AA)
+    app = rtb.Application(W, H, AA, rectangles=rectangles)
     for _ in range(scene):
         app.toggle_scene()
     if light:

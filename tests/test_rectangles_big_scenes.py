@@ -201,7 +201,7 @@ def test_rectangles_sequence_with_moving_camera(pipeline):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n_shapes,max_shapes", [(11, 11), (60, 64), (256, 256)])
+@pytest.mark.parametrize("n_shapes,max_shapes", [(11, 11), (60, 64), (64, 64), (100, 128), (200, 200), (256, 256)])
 @pytest.mark.parametrize("mode", [2, 3, 4, 1])
 def test_big_scene_single_frame(n_shapes, max_shapes, mode):
     W, H, AA = (200, 150, 4) if n_shapes < 256 else (120, 90, 4)
@@ -286,3 +286,91 @@ def test_upload_respects_max_shapes():
             rt.upload_scene(sc.shapes, sc.n)
     with pytest.raises(rtb.RtError):
         rtb.RayTracer(32, 24, 1, max_shapes=257)
+
+
+def lattice_scene(n_side=5):
+    """spheres on an exact integer lattice (cell faces of a uniform grid pass through centres and tangent points),
+    a floor, two rectangles through lattice planes: the worst case for a walk that rounds at cell edges"""
+    shapes = [host.make_plane((0, 1, 0), -3, (0.4, 0.4, 0.4)),
+              host.make_rectangle((-4, -3, -6), (8, 0, 0), (0, 8, 0), (0.8, 0.8, 0.9), reflectivity=0.05),
+              host.make_rectangle((-2, 3, 2), (4, 0, 0), (0, 0, -4), (2, 2, 2), emissive=True)]
+    k = 0
+    for ix in range(n_side):
+        for iy in range(3):
+            for iz in range(n_side):
+                refl = (1.0, 0.5, 0.0)[k % 3]
+                shapes.append(host.make_sphere((2 * (ix - n_side // 2), 2 * iy - 2, 2 - 2 * iz), 1.0 if k % 2 else 0.5,
+                                               (0.3 + 0.1 * (k % 7), 0.9 - 0.1 * (k % 5), 0.5), reflectivity=refl))
+                k += 1
+    return host.scene(shapes)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [2, 3, 4, 1])
+def test_grid_on_a_lattice_scene(mode):
+    """78 objects (grid on): touching spheres, hits exactly on cell faces, camera rays parallel to grid planes"""
+    W, H, AA = 160, 120, 4
+    sc = Scenario(scene=lattice_scene(), bg=host.SKY, max_shapes=96)
+    assert sc.n >= 64
+    with rtb.RayTracer(W, H, AA, flags=rtb.FLAG_RECTANGLES, max_shapes=96) as rt:
+        o = orc.Oracle(W, H, AA, rectangles=True, max_shapes=96)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        slot, u, rb = sc.next(mode, AA)
+        rt.render_frame(mode, u, rb)
+        o.render(mode, u, rb)
+        if mode == 1:
+            rt.postprocess()
+            o.postprocess()
+        check_frame(rt, o, slot, f"lattice mode {mode}")
+        check_stats(rt, o)
+        o.close()
+
+
+@pytest.mark.gpu
+def test_grid_with_the_camera_moving_through_the_field():
+    """the camera flies forward into the field (origins inside the grid, inside cells that hold objects), turning"""
+    W, H, AA = 128, 96, 4
+    sc = Scenario(scene=host.init_scene_field(150), bg=host.SKY, max_shapes=160, keys=("w", "e"), frametime=0.25, light_movement=True)
+    modes = [2, 4, 1, 1, 3, 2, 4, 1, 1, 2]
+    with rtb.RayTracer(W, H, AA, flags=rtb.FLAG_RECTANGLES, max_shapes=160) as rt:
+        o = orc.Oracle(W, H, AA, rectangles=True, max_shapes=160)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        for k, mode in enumerate(modes):
+            slot, u, rb = sc.next(mode, AA)
+            rt.render_frame(mode, u, rb)
+            o.render(mode, u, rb)
+            if mode == 1:
+                rt.postprocess()
+                o.postprocess()
+            check_frame(rt, o, slot, f"frame {k} mode {mode}")
+        check_stats(rt, o)
+        o.close()
+
+
+@pytest.mark.gpu
+def test_grid_off_and_a_partial_scene_are_the_same_bits(monkeypatch):
+    """RT_GRID=0 walks the lists; a frame that draws fewer objects than were uploaded (mode.z) does too"""
+    W, H, AA = 120, 90, 4
+    sc = Scenario(scene=host.init_scene_field(120), bg=host.SKY, max_shapes=128)
+    slot, u, rb = sc.next(4, AA)
+    imgs = []
+    for grid in ("1", "0"):
+        monkeypatch.setenv("RT_GRID", grid)
+        with rtb.RayTracer(W, H, AA, flags=rtb.FLAG_RECTANGLES, max_shapes=128) as rt:
+            rt.upload_scene(sc.shapes, sc.n)
+            rt.render_frame(4, u, None)
+            imgs.append(rt.download(rtb.BUF_COLOR, slot))
+    assert same_bits(imgs[0], imgs[1])
+    monkeypatch.delenv("RT_GRID")
+    u2 = u.copy()
+    u2[0, 2] = 70       # draw the first 70 objects only
+    with rtb.RayTracer(W, H, AA, flags=rtb.FLAG_RECTANGLES, max_shapes=128) as rt:
+        o = orc.Oracle(W, H, AA, rectangles=True, max_shapes=128)
+        rt.upload_scene(sc.shapes, sc.n)
+        o.set_scene(sc.shapes, sc.n)
+        rt.render_frame(4, u2, None)
+        o.render(4, u2, None)
+        check_frame(rt, o, slot, "partial scene")
+        o.close()
