@@ -286,7 +286,7 @@ class Setup:
                 plan = bands.replan_from_times(plan, [float(x.item()) for x in allt], H)
         self.plan = plan
         y0, rows = plan[rank]
-        # two frames in flight (RT_FLAG_PIPELINE): the tail of a frame's kernels and the short second pass of mode 1
+        # frames in flight (RT_FLAG_PIPELINE): the tail of a frame's kernels and the short second pass of mode 1
         # are filled with the next frame's trace kernel
         self.rt = rtb.RayTracer(W, H, AA, device=local, band_y0=y0, band_rows=rows, band_index=rank, band_count=world,
                                 flags=(rtb.FLAG_PIPELINE if args.pipeline else 0))
