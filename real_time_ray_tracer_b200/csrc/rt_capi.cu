@@ -891,7 +891,14 @@ int rt_halo_pack(rt_ctx *c)
         q.send_lo = c->peer_prev_recv_hi ? (char *)c->peer_prev_recv_hi + par : nullptr; // null on band 0: nobody below
         q.send_hi = (char *)c->peer_next_recv_lo + par;
         q.sig_next_lo = c->peers.box[(r + 1) % n] + MB_HALO_LO;
-        q.sig_prev_hi = (r > 0) ? c->peers.box[r - 1] + MB_HALO_HI : nullptr;
+        // band 0 has nobody below; its second signal goes to the last band, which waits for it before it overwrites
+        // the wrapped row (PostParams::wrap_wait)
+        q.sig_prev_hi = c->peers.box[(r > 0 ? r - 1 : n - 1)] + MB_HALO_HI;
+        if (r == n - 1 && c->halo_seq >= 1) {
+            q.wrap_wait = c->peers.box[r] + MB_HALO_HI;
+            q.wrap_seq = c->halo_seq - 1;
+            q.status = c->peers.box[r] + MB_STATUS;
+        }
         q.pack_count = c->pack_count;
     }
     // the pack reads frame k-1's result (the wrapped row's first element under FLAT32) and, with linked bands or a

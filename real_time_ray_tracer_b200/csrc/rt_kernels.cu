@@ -386,6 +386,7 @@ cudaError_t launch_trace(const FrameParams &p, const TraceOut &o, cudaStream_t s
 // i.e. (x-1, H-1) of the same slot, and for x = 0 the last element of the previous slot / array
 // (aop_postprocessing.glsl:150-159 over the layout of src/main.cpp:79-84).
 __device__ __forceinline__ void halo_pack_rows(const PostParams &q, int x);
+__device__ __forceinline__ void halo_wait(const unsigned long long *flag, unsigned long long seq, unsigned long long *status);
 
 // Linked bands: after the rows, the flags.  Every block fences its stores (system scope: they went to peer
 // memory) and counts itself; the last one publishes the frame's sequence number in the neighbours' flags, which
@@ -393,6 +394,12 @@ __device__ __forceinline__ void halo_pack_rows(const PostParams &q, int x);
 __global__ void rt_halo_pack_kernel(const __grid_constant__ PostParams q)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
+#ifndef RT_EXP_NO_WRAP_WAIT  // (defined only to show that the stalled-band-0 test fails without the wait)
+    if (q.wrap_wait) {      // the last band: band 0 must be done with the previous content of the wrapped row
+        if (threadIdx.x < 32) halo_wait(q.wrap_wait, q.wrap_seq, q.status);
+        __syncthreads();
+    }
+#endif
     if (x < q.W) halo_pack_rows(q, x);
     if (!q.pack_count) return;
     __threadfence_system();
@@ -559,7 +566,10 @@ __global__ void __launch_bounds__(PP_BLOCK_X *PP_BLOCK_Y, PP_MIN_BLOCKS) rt_ao_p
     unsigned n_nonbg = 0, n_eval = 0, n_acc = 0;
     if (q.wait_halo && yl < q.rows) {   // warp-uniform: a warp is 32 consecutive x of one row
         const int y = q.y0 + yl;
-        if (yl == 0 && ((q.edge_mode == RT_EDGE_FLAT32) ? (y != 1) : (y > 0))) halo_wait(q.flag_lo, q.seq, q.status);
+        // a band above band 0 always waits for the band below it, even where FLAT32 does not read that row (y == 1:
+        // band 0 is a single row): the wait is also what keeps neighbours within a frame of each other, which the
+        // double-buffered halo rows rely on
+        if (yl == 0 && ((q.edge_mode == RT_EDGE_FLAT32) ? (y != 1 || q.band_index > 0) : (y > 0))) halo_wait(q.flag_lo, q.seq, q.status);
         if (yl == q.rows - 1 && y + 1 < q.H) halo_wait(q.flag_hi, q.seq, q.status);
     }
     if (active) {

@@ -207,6 +207,13 @@ struct PostParams {
     // flags (sig_*: peer memory; pack_count finds the last block).  The post-processing kernel's edge-row warps
     // wait (wait_halo) until their own flags (flag_*) show `seq` before they read halo_lo / halo_hi.
     unsigned long long *sig_next_lo, *sig_prev_hi;
+    // The wrapped row (last band -> band 0, FLAT32) is the one halo transfer whose receiver does not send anything
+    // back, so nothing would keep the last band from running several frames ahead of band 0 and overwriting a row
+    // band 0 has not read yet.  Band 0 therefore also publishes its sequence number to the LAST band (sig_prev_hi
+    // = that band's MB_HALO_HI flag, which it has no other use for), and the last band's pack kernel waits until
+    // that flag shows wrap_seq (= seq - 1: band 0 has finished the pass that read the row's previous content).
+    const unsigned long long *wrap_wait;
+    unsigned long long wrap_seq;
     unsigned *pack_count;
     const unsigned long long *flag_lo, *flag_hi;
     unsigned long long *status;    // set to 1 when a wait gave up (10 s)

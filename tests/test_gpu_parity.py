@@ -277,13 +277,16 @@ def test_row_bands_on_one_gpu_equal_the_whole_frame(edge_mode, cuts):
 
 
 @pytest.mark.parametrize("edge_mode", [rtb.EDGE_FLAT32, rtb.EDGE_CLEAN])
-@pytest.mark.parametrize("cuts", [[0, 30, 64], [0, 1, 9, 40, 64], [0, 5, 64]])
-def test_linked_bands_exchange_the_halo_inside_the_kernels(edge_mode, cuts):
+@pytest.mark.parametrize("cuts,stalled", [([0, 30, 64], 1), ([0, 1, 9, 40, 64], 2), ([0, 5, 64], 1), ([0, 20, 30, 41, 52, 64], 0),
+                                          ([0, 1, 9, 40, 64], 0)])
+def test_linked_bands_exchange_the_halo_inside_the_kernels(edge_mode, cuts, stalled):
     """rt_link_peers on one device: every band context has its own stream and mailbox, the pack kernel stores the
     edge rows into the neighbours' receive rows (two per side, alternating with the frame) and raises their flags,
     and the edge rows of the post-processing kernels wait for the flags.  No copy, no fence, no synchronisation
-    between the bands for 19 frames (ring wrap, both parities, the wrapped row of FLAT32); a stalled band in the
-    middle (its stream blocked by a sleeping kernel for a while) must not change a bit."""
+    between the bands for 19 frames (ring wrap, both parities, the wrapped row of FLAT32); a stalled band (its stream
+    blocked by a sleeping kernel for a while) must not change a bit.  Band 0 stalled is the hard case: the wrapped
+    row travels from the last band to band 0 only, so without band 0's signal back to the last band the other bands
+    could run one frame ahead per link of the chain and overwrite a row band 0 has not read yet."""
     import torch
 
     W, H, AA = 96, 64, 4
@@ -301,7 +304,7 @@ def test_linked_bands_exchange_the_halo_inside_the_kernels(edge_mode, cuts):
         rt.upload_scene(sc.shapes, sc.n)
     frames = []
     side = torch.cuda.Stream()
-    rts[n // 2].set_stream(side.cuda_stream)       # the band that gets stalled
+    rts[stalled].set_stream(side.cuda_stream)      # the band that gets stalled
     for k in range(19):
         slot, u, rb = sc.next(1, AA)
         frames.append((slot, u, rb))

@@ -27,7 +27,7 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_ou
 rows = list(csv.reader(io.StringIO(out)))
 # a report may hold several kernels: take the section whose kernel name matches
 starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
-sec = next(i for i in starts if pat in rows[i][1])
+sec = next(i for i in starts if os.environ.get("RT_KPAT", pat) in rows[i][1])   # RT_KPAT: the demangled name when it differs (templates)
 hi = sec + 1
 h = rows[hi]
 end = next((i for i in starts if i > sec), len(rows))
