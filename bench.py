@@ -303,6 +303,8 @@ class Setup:
             self.direct.split = False
             if self.direct.halo_direct and not args.mode1_store_gather:
                 self.direct.mode1_gather = args.mode1_gather
+            if self.direct.halo_direct:
+                self.direct.single_pass_gather = args.single_pass_gather
         self.br = bands.BandedRenderer(eng, W, H, plan, rank, world, direct=self.direct)
         # rank 0 assembles frames in two alternating buffers so the gather of frame k overlaps the trace of k+1
         self.fulls = [env.torch.empty(W * H * 4, dtype=env.torch.float32, device=env.dev()) for _ in range(2)] \
@@ -332,9 +334,10 @@ class Setup:
             return "none"
         if d is None:
             return "nccl p2p"
-        if self.fr.mode == 1 and d.mode1_gather in ("copy", "copy8", "none"):
+        kind = self.br._gather_kind(self.fr.mode)
+        if kind != "store":
             what = {"copy": "float4 band copies", "copy8": "8-bit RGBA band copies (quantised on the device)",
-                    "none": "NO gather (diagnostic): nothing"}[d.mode1_gather]
+                    "none": "NO gather (diagnostic): nothing"}[kind]
             g = what + " into rank 0's image under the next frame's trace kernel, closed by one rt_fence at the end"
         else:
             g = "direct NVLink stores into rank 0's image, one rt_fence per frame on the library's fence stream"
@@ -346,9 +349,10 @@ class Setup:
         rt_fence kernel of a frame whose bands the kernels store into the frame image"""
         n = 3 if self.fr.mode == 1 else 1
         d = self.direct
-        if d is not None and d.halo_direct and not (self.fr.mode == 1 and d.mode1_gather in ("copy", "copy8", "none")):
+        kind = self.br._gather_kind(self.fr.mode)
+        if d is not None and d.halo_direct and kind == "store":
             n += 1
-        if d is not None and self.fr.mode == 1 and d.mode1_gather == "copy8":
+        if d is not None and kind == "copy8":
             n += 1      # the quantisation kernel
         return n
 
@@ -615,6 +619,7 @@ def parity_check(env: Env, su: Setup, frames: int = 9) -> dict:
     seq = Frames(fr.name)
     ins = [seq.next() for _ in range(frames)]
     run_gather = su.direct.mode1_gather if su.direct is not None else None
+    run_gather1 = su.direct.single_pass_gather if su.direct is not None else None
     check8 = world > 1 and fr.mode == 1 and run_gather == "copy8"
     extra = seq.next() if check8 else None       # one more frame through the 8-bit gather the timed loop used
     rt.reset_ring()
@@ -623,6 +628,8 @@ def parity_check(env: Env, su: Setup, frames: int = 9) -> dict:
         su.br.frame_fence = "stream"
         if run_gather in ("copy8", "none"):
             su.direct.mode1_gather = "copy"      # the float4 image is the stricter check
+        if run_gather1 == "none":
+            su.direct.single_pass_gather = "copy"
     last_k = None
     for (slot, u, rb) in ins:
         last_k = su.br.frame_k
@@ -640,6 +647,7 @@ def parity_check(env: Env, su: Setup, frames: int = 9) -> dict:
             got = su.fulls[(su.pending["k"] - 1) & 1].cpu().numpy().reshape(H, W, 4)
     if su.direct is not None:
         su.direct.mode1_gather = run_gather
+        su.direct.single_pass_gather = run_gather1
     if check8:
         k8 = su.br.frame_k
         su.step(extra)
@@ -1057,6 +1065,10 @@ def main():
     ap.add_argument("--mode1-gather", default="copy", choices=["copy", "copy8", "none"],
                     help="N > 1, mode 1, device-timed loop: what travels to rank 0 under the next frame's trace kernel: the "
                          "float4 colour bands, the 8-bit displayable image, or nothing (compute only, diagnostic)")
+    ap.add_argument("--single-pass-gather", default="store", choices=["store", "copy", "none"],
+                    help="N > 1, modes 2-4, device-timed loop: the trace kernel stores each pixel into rank 0's image "
+                         "(fused), or the band's colour plane travels as a copy under the next frame's trace kernel, or "
+                         "nothing travels (diagnostic)")
     ap.add_argument("--e2e-own-bands", action="store_true",
                     help="N > 1 e2e: every rank reads back its own (compute-balanced) band instead of a share "
                          "of the frame assembled with rt_set_frame_targets")

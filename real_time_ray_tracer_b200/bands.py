@@ -171,6 +171,10 @@ class DirectGather:
         # "copy8" = the same with the 8-bit displayable image (rt_band_to_frame_rgba8_overlapped: a quarter of the
         # bytes; the image occupies the first quarter of the frame buffer); "none" = the bands stay where they are
         self.mode1_gather = "store"
+        # the same choice for the frames of the single-pass modes (2, 3, 4), whose trace kernel can store into the
+        # image itself: "store" (fused, no extra pass -- but the stores of n - 1 ranks into one GPU hold the kernels
+        # back once rank 0's NVLink ingress is the bound), "copy", "none"
+        self.single_pass_gather = "store"
         if owners == "rows":
             if tracer is None:
                 raise ValueError("owners='rows' needs the band's RayTracer")
@@ -318,7 +322,7 @@ class BandedRenderer:
         self.e, self.W, self.H = engine, width, height
         self.bands, self.rank, self.world, self.group = bands, rank, world, group
         self.direct, self.frame_k = direct, 0
-        self._copy, self._copy_pending = False, False
+        self._copy, self._copy_pending, self._kind = False, False, "store"
         # how gather_start closes a frame whose bands the kernels store into the frame images:
         # "stream" = rt_fence on the rank's stream (the frame is complete when the stream gets there);
         # "background" = rt_fence_async, nothing on the rank's stream waits (a consumer joins the fence);
@@ -329,10 +333,16 @@ class BandedRenderer:
         f = getattr(self.e, "needs_postprocess", None)
         return f(mode) if f is not None else mode == 1
 
-    def _copy_gather(self, mode: int) -> bool:
+    def _gather_kind(self, mode: int) -> str:
+        """how this frame's band reaches the frame image: "store" (from the kernel that produces the final colour),
+        "copy" / "copy8" (band copies behind it), "none" """
         d = self.direct
-        return (self._post(mode) and self.world > 1 and d is not None and d.mode1_gather in ("copy", "copy8", "none")
-                and not (d.owners == "rows" and d.split))
+        if d is None or self.world == 1 or (d.owners == "rows" and d.split):
+            return "store"
+        return d.mode1_gather if self._post(mode) else d.single_pass_gather
+
+    def _copy_gather(self, mode: int) -> bool:
+        return self._gather_kind(mode) != "store"
 
     def exchange_halo(self):
         """send_hi -> recv_lo of band (r+1) % n (the last band's send_hi is the wrapped row image row 0
@@ -352,7 +362,8 @@ class BandedRenderer:
             w.wait()
 
     def render(self, mode: int, uniforms, rand_buffer):
-        self._copy = self._copy_gather(mode)
+        self._kind = self._gather_kind(mode)
+        self._copy = self._kind != "store"
         if self.direct is not None:
             if self._copy:
                 self.e.set_frame_target(None)
@@ -381,9 +392,9 @@ class BandedRenderer:
             if self._copy:
                 # copy engine, behind the post-processing kernel and under the next frame's trace kernel; the
                 # next fence on this stream (a single-pass frame's, or gather_flush) waits for it and closes the frame
-                if self.direct.mode1_gather == "copy8":
+                if self._kind == "copy8":
                     self.e.band_to_frame_rgba8(slot, self.direct.target(self.frame_k))
-                elif self.direct.mode1_gather == "copy":
+                elif self._kind == "copy":
                     self.e.band_to_frame(slot, self.direct.target(self.frame_k))
                 self._copy_pending = True
             else:

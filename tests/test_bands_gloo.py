@@ -198,6 +198,7 @@ class _Recorder:
 class _FakeDirect:
     def __init__(self, log, owners="rank0", halo_direct=True):
         self.log, self.owners, self.split, self.mode1_gather, self._hd = log, owners, owners == "rows", "store", halo_direct
+        self.single_pass_gather = "store"
 
     halo_direct = property(lambda self: self._hd)
 
@@ -253,6 +254,15 @@ def test_banded_renderer_call_sequences():
     br.gather_flush()
     assert [c[0] for c in log] == ["set_frame_target", "render_frame", "fence_bg", "set_frame_target", "render_frame", "fence_bg", "join"]
     br.frame_fence = "stream"
+    # single-pass frames as band copies too (what separates the kernels from rank 0's NVLink ingress at 8 GPUs)
+    del log[:]
+    d.single_pass_gather = "copy"
+    br.render(2, None, None); br.gather_start(0)
+    br.render(4, None, None); br.gather_start(1)
+    br.gather_flush()
+    assert [c[0] for c in log] == ["set_frame_target", "render_frame", "band_to_frame", "set_frame_target", "render_frame", "band_to_frame", "fence"]
+    assert log[0] == ("set_frame_target", None)
+    d.single_pass_gather = "store"
     # split row owners: every pixel goes to its owner's image, post-processed frames included (no copy gather)
     del log[:]
     d2 = _FakeDirect(log, owners="rows")

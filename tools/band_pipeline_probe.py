@@ -43,7 +43,14 @@ def run(name, y0, rows, nb, flags, K=64):
     return loop, float(np.mean(alone))
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "config2":
+    # an eighth of a 1080p frame (config 2 at N = 8): rank 0's band and a sphere band
+    for (y0, rows, nb, tag) in ((0, 1080, 1, "whole frame"), (0, 106, 8, "rows 0-106 (floor)"), (376, 87, 8, "rows 376-463 (spheres)"), (717, 363, 8, "rows 717-1080 (sky)")):
+        a, alone = run("config2_ao_1080p", y0, rows, nb, 0)
+        b, _ = run("config2_ao_1080p", y0, rows, nb, rtb.FLAG_PIPELINE)
+        print(json.dumps({"band": tag, "rows": rows, "kernel_alone_ms": round(alone, 4), "loop_one_at_a_time_ms": round(a, 4),
+                          "loop_in_flight_ms": round(b, 4)}), flush=True)
+elif __name__ == "__main__":
     name = "config4_aopp_4k"
     H = 2160
     for (y0, rows, nb, tag) in ((0, H, 1, "whole frame"), (990, 180, 8, "1/8 band, spheres"), (990, 360, 8, "1/4 band"), (200, 180, 8, "1/8 band, floor"), (1800, 360, 8, "sky band")):
