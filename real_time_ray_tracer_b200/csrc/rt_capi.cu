@@ -358,6 +358,12 @@ static cudaError_t begin_frame(rt_ctx *c, int slot, bool inplace)
     // the planes of this frame number mod PIPE (raw, hit, the object block) and the physical ring slot it takes were
     // last used by frame k - PIPE, whose finishing passes ran on the post stream
     if (e == cudaSuccess) e = wait_frame_done(c, S, PIPE);
+    // Copies of earlier frames' results that run beside the frames on the library's copy stream (band copies to a
+    // frame image, overlapped read-backs) must not fall behind without bound: their source is a ring slot that is
+    // rewritten NF frames later.  A frame waits for the older of the two copies that can be pending.
+#ifndef RT_EXP_NO_COPY_THROTTLE  // (defined only to show that test_band_copies_keep_up_with_the_frames fails without it)
+    if (e == cudaSuccess && c->copy_pending[c->rgba8_flip]) e = cudaStreamWaitEvent(S, c->ev_copy[c->rgba8_flip], 0);
+#endif
     // Beside the PIPE - 1 frames before it this frame may NOT run when one of them names the same ring slot (it
     // reads that slot's previous record), when it writes its colour in place (modes 3/4 without G-buffer) while one
     // of their passes may be walking the ring, or around a change of the shared sky constants.
@@ -1318,6 +1324,9 @@ int rt_band_to_frame_overlapped(rt_ctx *c, int slot, void *frame)
     CU(c, join_frames(c));
     const int h = c->rgba8_flip;
     c->rgba8_flip ^= 1;
+#ifndef RT_EXP_NO_COPY_THROTTLE
+    if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));   // at most two copies in flight
+#endif
     CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
     CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
     // contiguous rows on both sides; `frame` may be an imported mapping: the copy engine moves it over NVLink

@@ -1034,3 +1034,30 @@ def test_pipelined_frames_are_the_same_bits():
         assert st[kk] == v, (kk, st[kk], v)
     rt.close()
     o.close()
+
+
+@pytest.mark.parametrize("pipeline", [0, rtb.FLAG_PIPELINE])
+def test_band_copies_keep_up_with_the_frames(pipeline):
+    """rt_band_to_frame_overlapped when the copies are SLOWER than the frames (here: 4.9 MB per frame into pinned host
+    memory over PCIe against a 12 us kernel; on 8 GPUs: rank 0's NVLink ingress).  The source of a copy is a ring
+    slot that is rewritten 8 frames later, so the frames must not run ahead of the copies without bound: every one
+    of 48 frames, enqueued without a single host wait, must arrive as it was rendered."""
+    import torch
+
+    W, H, AA, K = 640, 480, 4, 48
+    sc = Scenario("scene1", keys=("d",))
+    ins = [sc.next(3, AA) for _ in range(K)]
+    host_frames = [torch.empty(W * H * 4, dtype=torch.float32).pin_memory() for _ in range(K)]
+    with rtb.RayTracer(W, H, AA, flags=pipeline) as rt:
+        rt.upload_scene(sc.shapes, sc.n)
+        for (slot, u, rb), hf in zip(ins, host_frames):
+            rt.render_frame(3, u, None)
+            rt.band_to_frame_overlapped(slot, hf.data_ptr())
+        rt.synchronize()
+        got = [hf.numpy().reshape(H, W, 4).copy() for hf in host_frames]
+    with rtb.RayTracer(W, H, AA) as rt:
+        rt.upload_scene(sc.shapes, sc.n)
+        for k, (slot, u, rb) in enumerate(ins):
+            rt.render_frame(3, u, None)
+            want = rt.download(rtb.BUF_COLOR, slot)
+            assert same_bits(got[k], want), f"frame {k}: the copy shows another frame's pixels ({diff_report(got[k], want)})"
