@@ -104,6 +104,10 @@ struct rt_ctx {
     cudaStream_t copy_stream = nullptr;   // read-backs of rt_download_rgba8_async overlap the next frame
     cudaEvent_t ev_quant[2] = { nullptr, nullptr }, ev_copy[2] = { nullptr, nullptr };
     bool copy_pending[2] = { false, false };
+    // copies whose SOURCE is a ring slot (band copies to a frame image, overlapped colour read-backs): a ring of
+    // events so that the frames can be kept from running more than copy_window() copies ahead of them
+    cudaEvent_t ev_ringcopy[8] = {};
+    unsigned long long ringcopies = 0;
     bool timing = false;
     cudaEvent_t ev[PIPE][4] = {};   // per frame number mod PIPE: trace begin / end, post-processing begin / end
     bool ev_trace_valid = false, ev_post_valid = false;
@@ -172,6 +176,7 @@ static void free_all(rt_ctx *c)
         if (c->ev_quant[i]) cudaEventDestroy(c->ev_quant[i]);
         if (c->ev_copy[i]) cudaEventDestroy(c->ev_copy[i]);
     }
+    for (cudaEvent_t e : c->ev_ringcopy) if (e) cudaEventDestroy(e);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
@@ -250,6 +255,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
             e = cudaStreamCreateWithPriority(&c->fstream[i], cudaStreamNonBlocking, i == PIPE ? prio_greatest : prio_least);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming);
     }
+    for (int i = 0; i < 8 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->ev_ringcopy[i], cudaEventDisableTiming);
     for (int i = 0; i < EVR && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_trace[i], cudaEventDisableTiming);
@@ -349,10 +355,33 @@ static cudaError_t wait_frame_done(rt_ctx *c, cudaStream_t S, unsigned back)
     return cudaStreamWaitEvent(S, c->ev_done[(k - back) % EVR], 0);
 }
 
+static inline unsigned copy_window(const rt_ctx *c)
+{
+    const int nf = c->cfg.num_frames;
+    return (unsigned)(nf - 1 < 4 ? (nf - 1 < 0 ? 0 : nf - 1) : 4);
+}
+static cudaError_t throttle_on_ring_copies(rt_ctx *c, cudaStream_t S)
+{
+#ifdef RT_EXP_NO_COPY_THROTTLE  // (defined only to show that test_band_copies_keep_up_with_the_frames fails without it)
+    (void)c; (void)S;
+    return cudaSuccess;
+#else
+    const unsigned w = copy_window(c);
+    if (c->ringcopies <= w) return cudaSuccess;
+    return cudaStreamWaitEvent(S, c->ev_ringcopy[(c->ringcopies - 1 - w) % 8], 0);
+#endif
+}
+static cudaError_t note_ring_copy(rt_ctx *c)
+{
+    cudaError_t e = cudaEventRecord(c->ev_ringcopy[c->ringcopies % 8], c->copy_stream);
+    c->ringcopies++;
+    return e;
+}
+
 static cudaError_t begin_frame(rt_ctx *c, int slot, bool inplace)
 {
     const unsigned long long k = c->frame_no++;
-    if (!c->pipeline) return cudaSuccess;
+    if (!c->pipeline) return throttle_on_ring_copies(c, c->stream);
     cudaStream_t S = c->fstream[k % PIPE];
     cudaError_t e = sync_fork(c, (int)(k % PIPE));
     // the planes of this frame number mod PIPE (raw, hit, the object block) and the physical ring slot it takes were
@@ -360,10 +389,10 @@ static cudaError_t begin_frame(rt_ctx *c, int slot, bool inplace)
     if (e == cudaSuccess) e = wait_frame_done(c, S, PIPE);
     // Copies of earlier frames' results that run beside the frames on the library's copy stream (band copies to a
     // frame image, overlapped read-backs) must not fall behind without bound: their source is a ring slot that is
-    // rewritten NF frames later.  A frame waits for the older of the two copies that can be pending.
-#ifndef RT_EXP_NO_COPY_THROTTLE  // (defined only to show that test_band_copies_keep_up_with_the_frames fails without it)
-    if (e == cudaSuccess && c->copy_pending[c->rgba8_flip]) e = cudaStreamWaitEvent(S, c->ev_copy[c->rgba8_flip], 0);
-#endif
+    // rewritten NF frames later (a frame that writes its colour in place reuses the very plane).  A frame waits
+    // until at most copy_window() of them are still pending -- enough to keep the copy engines busy when they are
+    // the bound (rank 0's NVLink ingress at 8 GPUs), few enough for the ring.
+    if (e == cudaSuccess) e = throttle_on_ring_copies(c, S);
     // Beside the PIPE - 1 frames before it this frame may NOT run when one of them names the same ring slot (it
     // reads that slot's previous record), when it writes its colour in place (modes 3/4 without G-buffer) while one
     // of their passes may be walking the ring, or around a change of the shared sky constants.
@@ -409,6 +438,13 @@ static cudaError_t end_frame(rt_ctx *c)
     if (!c->pipeline) return cudaSuccess;
     const unsigned long long k = c->frame_no - 1;
     return cudaEventRecord(c->ev_done[k % EVR], c->fstream[PIPE]);
+}
+
+// The last frame issued is complete (no pass pending) and nothing of the caller's on the context's stream has to be
+// respected: its completion event alone orders a consumer behind all frames issued so far.
+static inline bool frames_done_event_usable(const rt_ctx *c)
+{
+    return c->pipeline && c->frame_no > 0 && !c->frame_pending_post && !c->fork_pending;
 }
 
 int rt_set_stream(rt_ctx *c, void *cuda_stream)
@@ -1252,6 +1288,7 @@ int rt_download_rgba8_async(rt_ctx *c, int slot, void *pinned_host, size_t bytes
     CU(c, cudaMemcpyAsync(pinned_host, dst, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
     CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
     c->copy_pending[h] = true;
+    CU(c, note_ring_copy(c));     // its source is a ring slot: the frames stay within copy_window() of it
     return RT_OK;
 }
 
@@ -1260,21 +1297,29 @@ int rt_band_to_frame_rgba8_overlapped(rt_ctx *c, int slot, void *frame8)
     if (!c || !frame8) return RT_EINVAL;
     if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
     CU(c, cudaSetDevice(c->cfg.device));
-    CU(c, join_frames(c));
     const size_t half = (c->npix + 3) & ~(size_t)3;
     if (!c->rgba8) CU(c, cudaMalloc((void **)&c->rgba8, 2 * half * sizeof(uchar4)));
     const int h = c->rgba8_flip;
     c->rgba8_flip ^= 1;
     uchar4 *dst = c->rgba8 + (size_t)h * half;
-    if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));
-    CU(c, launch_quantize_rgba8(c->ring_color + (size_t)c->phys[slot] * c->npix, dst, c->npix, c->stream));
-    CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
-    CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    if (frames_done_event_usable(c)) {
+        // frames in flight: quantisation and copy both on the copy stream, behind the last frame's completion event
+        // (in order there: the buffer's previous copy is over)
+        CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_done[(c->frame_no - 1) % EVR], 0));
+        CU(c, launch_quantize_rgba8(c->ring_color + (size_t)c->phys[slot] * c->npix, dst, c->npix, c->copy_stream));
+    } else {
+        CU(c, join_frames(c));
+        if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));
+        CU(c, launch_quantize_rgba8(c->ring_color + (size_t)c->phys[slot] * c->npix, dst, c->npix, c->stream));
+        CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
+        CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    }
     // contiguous rows on both sides; `frame8` may be an imported mapping: the copy engine moves it over NVLink
     CU(c, cudaMemcpyAsync((uchar4 *)frame8 + (size_t)c->cfg.band_y0 * c->cfg.width, dst, c->npix * sizeof(uchar4),
                           cudaMemcpyDefault, c->copy_stream));
     CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
     c->copy_pending[h] = true;
+    CU(c, note_ring_copy(c));     // its source is a ring slot: the frames stay within copy_window() of it
     return RT_OK;
 }
 
@@ -1292,6 +1337,7 @@ int rt_download_color_overlapped(rt_ctx *c, int slot, void *pinned_host, size_t 
     CU(c, cudaMemcpyAsync(pinned_host, c->ring_color + (size_t)c->phys[slot] * c->npix, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
     CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
     c->copy_pending[h] = true;
+    CU(c, note_ring_copy(c));     // its source is a ring slot: the frames stay within copy_window() of it
     return RT_OK;
 }
 
@@ -1321,19 +1367,23 @@ int rt_band_to_frame_overlapped(rt_ctx *c, int slot, void *frame)
     if (!c || !frame) return RT_EINVAL;
     if (slot < 0 || slot >= c->cfg.num_frames) return fail(c, RT_EINVAL, "slot %d outside the ring", slot);
     CU(c, cudaSetDevice(c->cfg.device));
-    CU(c, join_frames(c));
     const int h = c->rgba8_flip;
     c->rgba8_flip ^= 1;
-#ifndef RT_EXP_NO_COPY_THROTTLE
-    if (c->copy_pending[h]) CU(c, cudaStreamWaitEvent(c->stream, c->ev_copy[h], 0));   // at most two copies in flight
-#endif
-    CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
-    CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    if (frames_done_event_usable(c)) {
+        // frames in flight: the copy follows the last frame's completion event directly (one call instead of a
+        // join of all internal streams; the frames themselves wait for the older pending copy, begin_frame)
+        CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_done[(c->frame_no - 1) % EVR], 0));
+    } else {
+        CU(c, join_frames(c));
+        CU(c, cudaEventRecord(c->ev_quant[h], c->stream));
+        CU(c, cudaStreamWaitEvent(c->copy_stream, c->ev_quant[h], 0));
+    }
     // contiguous rows on both sides; `frame` may be an imported mapping: the copy engine moves it over NVLink
     CU(c, cudaMemcpyAsync((float4 *)frame + (size_t)c->cfg.band_y0 * c->cfg.width, c->ring_color + (size_t)c->phys[slot] * c->npix,
                           c->npix * 16, cudaMemcpyDefault, c->copy_stream));
     CU(c, cudaEventRecord(c->ev_copy[h], c->copy_stream));
     c->copy_pending[h] = true;
+    CU(c, note_ring_copy(c));     // its source is a ring slot: the frames stay within copy_window() of it
     return RT_OK;
 }
 
