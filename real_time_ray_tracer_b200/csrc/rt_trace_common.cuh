@@ -360,29 +360,30 @@ __device__ __forceinline__ unsigned tile_candidates(const FrameParams &p, float 
     sph_mask = (1u << p.nsph) - 1u;
     pl_mask = (1u << (p.npl + (RC ? p.nrc : 0))) - 1u;
     if (!(p.cull_a > 0.0f && s < 0.05f)) return sph_mask | (pl_mask << 16);   // off, degenerate camera, or tiles too wide for the margins
-#pragma unroll 1
-    for (int i = 0; i < p.nsph; i++) {
-        const float m = fabsf(dot3(d0, xyz(p.sph_cam[i]))) + p.sph_len[i] * s;
-        if (m * m < p.sph_gap[i]) sph_mask &= ~(1u << i);
-    }
-#pragma unroll 1
-    for (int j = 0; j < p.npl; j++) {
-        const float4 n = p.pl_n[j];
-        const float dn = dot3(xyz(n), d0);
-        const float q = (n.w < 0.0f) ? dn : -dn;
-        const float len = p.pl_len[j];
-        if (n.w == 0.0f || q * (1.0f - s) - len * s > 1e-3f * len) pl_mask &= ~(1u << j);
-    }
-    if constexpr (RC) {
-#pragma unroll 1
-        for (int j = 0; j < p.nrc; j++) {
-            const float4 n = p.rc_n[j];
+    // One object per lane (the lists hold at most RT_MAX_SHAPES entries between them; the whole warp is here: the
+    // call sits at the top of the kernels): lanes [0, nsph) take the spheres, the next npl the planes, then the
+    // rectangles; a ballot collects the verdicts.  The same tests as a loop over the objects in every lane would
+    // make -- that loop was 5 % of the AO kernel's instructions.
+    const int lane = threadIdx.x & 31;
+    bool ruled_out = false;
+    if (lane < p.nsph) {
+        const float m = fabsf(dot3(d0, xyz(p.sph_cam[lane]))) + p.sph_len[lane] * s;
+        ruled_out = m * m < p.sph_gap[lane];
+    } else {
+        const int j = lane - p.nsph;
+        if (j < p.npl + (RC ? p.nrc : 0)) {
+            float4 n;
+            float len;
+            if (!RC || j < p.npl) { n = p.pl_n[j]; len = p.pl_len[j]; }
+            else { n = p.rc_n[j - p.npl]; len = p.rc_p[j - p.npl].w; }
             const float dn = dot3(xyz(n), d0);
             const float q = (n.w < 0.0f) ? dn : -dn;
-            const float len = p.rc_p[j].w;
-            if (n.w == 0.0f || q * (1.0f - s) - len * s > 1e-3f * len) pl_mask &= ~(1u << (p.npl + j));
+            ruled_out = (n.w == 0.0f || q * (1.0f - s) - len * s > 1e-3f * len);
         }
     }
+    const unsigned verdicts = __ballot_sync(0xffffffffu, ruled_out);
+    sph_mask &= ~verdicts;
+    pl_mask &= ~(verdicts >> p.nsph);
     return sph_mask | (pl_mask << 16);
 }
 
