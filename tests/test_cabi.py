@@ -54,3 +54,32 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dp, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
                 assert "rt_oracle" not in src and "librt_oracle" not in src, f
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/rt.h is what a C or C++ host binds: it must compile as C99 on its own, with the documented constants"""
+    import subprocess
+
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "rt.h"\n'
+                   "int main(void) { rt_config c = {0}; rt_uniforms u; rt_shape s; rt_stats st; (void)u; (void)s; (void)st;\n"
+                   "  c.max_shapes = RT_MAX_SHAPES_LIMIT; c.flags = RT_FLAG_RECTANGLES | RT_FLAG_PIPELINE;\n"
+                   "  return (RT_ABI_VERSION == 2 && RT_MAX_SHAPES == 10 && sizeof(rt_config) == 64 && sizeof(rt_shape) == 80 && c.flags == 12) ? 0 : 1; }\n")
+    exe = tmp_path / "hdr"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                    str(src), "-o", str(exe)], check=True, capture_output=True)
+    assert subprocess.run([str(exe)]).returncode == 0
+
+
+def test_create_validates_before_touching_a_device():
+    """bad arguments are RT_EINVAL with a message, with or without a GPU (the checks come first)"""
+    lib = _lib.load()
+    h = C.c_void_p()
+    for kw, words in ((dict(flags=64), b"unknown flags"), (dict(max_shapes=257), b"max_shapes"), (dict(max_shapes=-1), b"max_shapes"),
+                      (dict(flags=_lib.FLAG_PHONG_POSTPROCESS), b"RT_FLAG_PHONG_GBUFFER"), (dict(aa=0), b"aa"),
+                      (dict(num_frames=17), b"num_frames")):
+        cfg = _lib.rt_config(64, 48, 4, 20, 8, 0, 0, 0, 0, 0, 1)
+        for k, v in kw.items():
+            setattr(cfg, k, v)
+        assert lib.rt_create(C.byref(cfg), C.byref(h)) == _lib.RT_EINVAL, kw
+        assert words in lib.rt_last_error(None), (kw, lib.rt_last_error(None))
