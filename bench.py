@@ -524,9 +524,9 @@ def run_b200(args) -> None:
             "data": "synthetic", "impl": "b200",
             "config": fr.config(),
             "run": {"parallelism": f"row-bands x{world}", "bands": su.plan, "gather": su.gather_description(),
-                    "frames_in_flight": 2 if args.pipeline else 1,
-                    "l2": "no input reuse: ~1.4 KB of kernel parameters in, each frame writes a different "
-                          "ring slot (8 x %.0f MB > 126 MB L2)" % (fr.W * fr.H * 44 / 1e6)},
+                    "frames_in_flight": 3 if args.pipeline else 1,
+                    "l2": "no input reuse: ~3 KB of kernel parameters in, each frame writes a different "
+                          "physical ring slot (11 x %.0f MB > 126 MB L2)" % (fr.W * fr.H * 44 / 1e6)},
             "rays_per_frame": tr["rays"] / K,
             "per_rank": ranks,
             "gpu_launches": K * world * su.launches_per_frame() + (world if world > 1 else 0),
