@@ -68,6 +68,19 @@ def ncu_traffic(kernel: str, workload: str):
     return None
 
 
+def ncu_capture(kernel: str, workload: str):
+    """What the committed `ncu --set full` capture of `kernel` on `workload` says beside the DRAM bytes: issue-slot
+    utilisation, lanes per instruction, warp instructions, duration, and the file it comes from -- or None.  Not a
+    measurement of this run: the evidence behind calling the trace kernels issue-bound."""
+    try:
+        e = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json"))).get(f"{kernel}@{workload}")
+    except (OSError, ValueError):
+        return None
+    if not e:
+        return None
+    return {k: e[k] for k in ("issue_active_pct", "lanes_per_instruction", "warp_instructions", "ncu_duration_us", "source") if k in e}
+
+
 def pp_bytes_from_counters(st: dict) -> float:
     """Algorithmic HBM bytes of the post-processing pass: every pixel reads raw colour 16 + normal 16
     and writes the ring colour 16 (the image IS the ring slot: no second store); a non-background pixel
@@ -452,6 +465,7 @@ def rooflines(env: Env, su: Setup, kl: dict, peak_tf: float) -> dict:
     out = {"roofline": {
         "bound": "fp32", "kernel": kname, "achieved": round(ach, 4), "peak": round(peak_tf, 3), "unit": "TFLOP/s",
         "frac": round(ach / peak_tf, 5), "traffic": ncu_traffic(kname, fr.name) if world == 1 else None,
+        "ncu_capture": ncu_capture(kname, fr.name) if world == 1 else None,
         "algorithmic_bytes_written": int(fr.W * fr.H * (48 if fr.mode in (1, 2) else 20)) if world == 1 else None,
         "peak_source": "FFMA microbenchmark measured in this run (MEASURED_PEAKS.json has no FP32 figure)",
         "kernel_ms": round(t_ms, 5), "kernel_mrays_per_s": round(kr / (t_ms * 1e-3) / 1e6, 1),
@@ -464,6 +478,7 @@ def rooflines(env: Env, su: Setup, kl: dict, peak_tf: float) -> dict:
             "bound": "hbm", "kernel": "rt_ao_postprocess_kernel", "achieved": round(p_b / (p_ms * 1e-3) / 1e9, 1),
             "peak": hbm, "unit": "GB/s", "frac": round(p_b / (p_ms * 1e-3) / 1e9 / hbm, 4),
             "traffic": ncu_traffic("rt_ao_postprocess_kernel", fr.name) if world == 1 else None,
+            "ncu_capture": ncu_capture("rt_ao_postprocess_kernel", fr.name) if world == 1 else None,
             "algorithmic_bytes": p_b,
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (no MEASURED_PEAKS.json)",
             "kernel_ms": round(p_ms, 5), "per_rank_band": world > 1}
