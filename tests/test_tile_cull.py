@@ -16,8 +16,9 @@ from tests.util import Scenario
 f32 = np.float32
 
 
-def cull_bounds(u, shapes, n, W, H):
-    """host side, as build_traversal_tables computes them"""
+def cull_bounds(u, shapes, n, W, H, rectangles=False):
+    """host side, as build_traversal_tables computes them (``rectangles``: RT_FLAG_RECTANGLES -- a rectangle takes
+    the plane test of its own plane, through its lower left vertex)"""
     hz, vt, cam = u[1, :3].astype(f32), u[2, :3].astype(f32), u[4, :3].astype(f32)
     cull_a = f32(1.1) * (f32(3.7) / f32(W) * np.sqrt((hz * hz).sum(dtype=f32)) + f32(1.7) / f32(H) * np.sqrt((vt * vt).sum(dtype=f32)))
     sph, pl = [], []
@@ -29,7 +30,7 @@ def cull_bounds(u, shapes, n, W, H):
             dd = f32((oc * oc).sum(dtype=f32))
             gap = dd - f32(rec[0, 3]) * f32(rec[0, 3])
             sph.append((oc, f32(np.sqrt(dd)) * f32(1.001), gap * f32(0.999) if gap > 0 else f32(-1.0), i))
-        elif kind == host.PLANE_ID:
+        elif kind == host.PLANE_ID or (kind == host.RECTANGLE_ID and rectangles):
             nrm = rec[0, :3].astype(f32)
             num = f32((nrm * (rec[3, :3] - cam)).sum(dtype=f32))
             pl.append((nrm, num, f32(np.sqrt((nrm * nrm).sum(dtype=f32))) * f32(1.001), i))
@@ -208,3 +209,40 @@ def test_tile_test_holds_for_arbitrary_cameras(seed):
                 assert not _exact_hits(sc.shapes[i].astype(np.float64), cam64, d).any(), \
                     f"trial {trial} ({scene}, {W}x{H}, camera {c}, look {look}): object {i} ruled out for tile ({tx}, {ty}) but hit"
     assert ruled_out > 500, ruled_out
+
+
+
+@pytest.mark.parametrize("scene,keys,W,H", [("scene5_rectangle", ("e",), 160, 90), ("mixed", ("d", "w"), 203, 117),
+                                            ("mixed", ("a", "q"), 320, 180), ("mixed", ("s", "e"), 640, 360)])
+def test_rectangles_in_the_tile_test(scene, keys, W, H):
+    """RT_FLAG_RECTANGLES: a rectangle is kept or ruled out by the plane test of its own plane; against the oracle's
+    frames (rectangles intersected) no tile may rule out an object one of its pixels hits, and a tile without
+    candidates must be pure background"""
+    from tests.test_rectangles_big_scenes import rect_scenarios
+
+    AA = 4
+    sc = rect_scenarios(keys=keys, frametime=0.25)[scene]()
+    o = orc.Oracle(W, H, AA, rectangles=True)
+    o.set_scene(sc.shapes, sc.n)
+    rect_ids = {i for i, s in enumerate(sc.scene.shapes) if s.id() == host.RECTANGLE_ID}
+    rect_seen = rect_ruled_out = 0
+    for frame in range(5):
+        slot, u, rb = sc.next(2, AA)
+        o.render(2, u, rb)
+        img, hit = o.get(orc.IMAGE), o.get(orc.HIT_INDEX)
+        sky = sky_colour(u[6], AA)
+        is_sky = (hit == -1) & (img[..., :3].view(np.uint32) == sky.view(np.uint32)).all(axis=2)
+        bounds = cull_bounds(u, sc.shapes, sc.n, W, H, rectangles=True)
+        for ty in range(0, H, 4):
+            for tx in range(0, W, 8):
+                keep = tile_candidates(u, bounds, (f32(tx) + f32(3.5)) / f32(W), (f32(ty) + f32(1.5)) / f32(H))
+                seen = set(np.unique(hit[ty:ty + 4, tx:tx + 8]).tolist()) - {-1}
+                assert seen <= keep, f"{scene} frame {frame}: tile ({tx}, {ty}) rules out {seen - keep} but a camera ray hits it"
+                rect_seen += len(seen & rect_ids)
+                rect_ruled_out += len(rect_ids - keep)
+                if not keep:
+                    assert bool(is_sky[ty:ty + 4, tx:tx + 8].all()), f"{scene} frame {frame}: tile ({tx}, {ty}) would be culled"
+    o.close()
+    assert rect_seen > 0        # the rectangles are in the picture ...
+    if scene == "mixed":
+        assert rect_ruled_out > 0   # ... and the test does rule them out somewhere (tiles that look away from a plane)
