@@ -325,6 +325,44 @@ int rt_reset_ring(rt_ctx *ctx);
 int rt_get_stats(rt_ctx *ctx, rt_stats *out); /* synchronises */
 int rt_reset_stats(rt_ctx *ctx);
 
+/* ---- one AO frame without a context and without a single allocation (no counterpart in the reference, whose
+ * only path creates its SSBO with glBufferData first) ------------------------------------------------------
+ *
+ * Who this is for.  rt_create reserves the G-buffer ring, the statistics stripes and a handful of streams and
+ * events with cudaMalloc / cudaMallocHost / cudaStreamCreate.  Some hosts may not do that at the moment they
+ * want a frame: a plug-in that runs inside another program's frame loop under a "no driver allocation after
+ * start-up" rule (cudaMalloc takes a device-wide lock and can stall every stream of the process), a service
+ * whose whole device budget was handed to an arena at start-up so that a later cudaMalloc simply fails, or code
+ * that is handed a device buffer and a stream by its framework and nothing else.  For them this entry point
+ * traces one lighting-mode-2 frame (ao_compute.glsl: the colour of RT_MODE_AO, the same bits as rt_render_frame
+ * on a new context) with everything the kernel needs besides its inputs and its output -- the normal / depth /
+ * hit-index planes the kernel also writes, the all-zero "previous record" planes it reads behind an emissive
+ * primary hit, the statistics stripes and the sky constants -- in ONE array that is part of the library image:
+ * about 8.7 MiB of device memory on every GPU that loads the library, held until the process exits.
+ *
+ * Limits.  width * height <= RT_STATIC_MAX_PIXELS (anything larger is refused with RT_EINVAL and a message in
+ * rt_last_error(NULL); the reference's own 440 x 330 window fits), n_shapes <= RT_MAX_SHAPES (larger scenes
+ * need an object block in device memory: use a context), flags: 0 or RT_FLAG_RECTANGLES.
+ *
+ * Arguments.  shapes / u / rand_buffer are host memory as for rt_upload_scene / rt_render_frame (u->mode.z =
+ * objects drawn, u->mode.y is ignored: there is no ring).  color_out is DEVICE memory of the caller, float4
+ * [height][width], row-major, y = 0 at the bottom.  stats_out may be NULL; if given, the frame's ray counters
+ * are copied back and the call waits for the stream (ms_* stay 0).  cuda_stream: the caller's cudaStream_t,
+ * NULL = the default stream; without stats_out the call returns as soon as the work is enqueued.
+ *
+ * Sharing.  There is one array per GPU, not per call: it keeps what the previous call left, so every call
+ * first zeroes the statistics stripes (the one part that accumulates) and rewrites the sky constants; the
+ * planes are overwritten pixel by pixel and the "previous record" planes are never written at all.  Two calls
+ * whose work overlaps on the same GPU (two streams, two threads) race on that array -- order them.
+ *
+ * First call.  The first call for a device looks the array's device address up (with that device current)
+ * and remembers it; make that call before any stream capture begins.  No call allocates: no cudaMalloc,
+ * cudaFree, stream, event or host allocation. */
+#define RT_STATIC_MAX_PIXELS 147456 /* 384 x 384; any shape with width * height at or below it */
+int rt_render_ao_static(int device, int width, int height, int aa, int recursion_depth, int flags,
+                        const rt_shape *shapes, int n_shapes, const rt_uniforms *u, const float *rand_buffer,
+                        void *color_out, rt_stats *stats_out, void *cuda_stream);
+
 /* diagnostics used by the parity tests and the benchmark */
 /* element-wise built-ins on the device: kind 0 sin(a), 1 pow(a,b), 2 random(vec2(a,b)),
  * 3 1/sqrt(a) as normalize() forms it, 4 sqrt(a) as the sphere test forms it */

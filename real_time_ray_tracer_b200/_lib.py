@@ -20,6 +20,7 @@ BUF_COLOR, BUF_NORMAL, BUF_DEPTH, BUF_HIT_INDEX, BUF_IMAGE, BUF_RAW_COLOR, BUF_D
 LAYOUT_ROW_MAJOR, LAYOUT_REFERENCE = 0, 1
 MAX_SHAPES, MAX_AA, MAX_FRAMES = 10, 16, 16
 MAX_SHAPES_LIMIT = 256
+STATIC_MAX_PIXELS = 147456   # RT_STATIC_MAX_PIXELS: the largest frame of rt_render_ao_static
 
 
 class rt_config(C.Structure):
@@ -48,6 +49,7 @@ EXPORTS = (
     "rt_reset_stats", "rt_reset_ring", "rt_debug_eval_math", "rt_measure_fp32_peak",
     "rt_set_frame_target", "rt_set_frame_targets", "rt_frame_download_overlapped", "rt_stream_wait_readback", "rt_band_to_frame_overlapped", "rt_band_to_frame_rgba8_overlapped", "rt_frame_create", "rt_frame_destroy", "rt_peer_export", "rt_peer_import",
     "rt_peer_release", "rt_mailbox_create", "rt_mailbox_destroy", "rt_link_peers", "rt_fence", "rt_fence_async", "rt_fence_join", "rt_fence_status",
+    "rt_render_ao_static",
 )
 
 _lib = None
@@ -108,5 +110,6 @@ def load():
     L.rt_fence_async.argtypes = [vp]
     L.rt_fence_join.argtypes = [vp, i32]
     L.rt_fence_status.argtypes = [vp, C.POINTER(i32)]
+    L.rt_render_ao_static.argtypes = [i32, i32, i32, i32, i32, i32, vp, i32, vp, vp, vp, C.POINTER(rt_stats), vp]
     _lib = L
     return L

@@ -334,6 +334,30 @@ def measure_fp32_peak(device: int = 0) -> float:
     return v.value
 
 
+def render_ao_static(width: int, height: int, shapes: np.ndarray, n_shapes: int, uniforms: np.ndarray,
+                     rand_buffer: np.ndarray, color_ptr: int, aa: int = host.AA,
+                     recursion_depth: int = host.RECURSION_DEPTH, flags: int = 0, device: int = 0,
+                     cuda_stream: Optional[int] = None, want_stats: bool = False) -> Optional[dict]:
+    """rt_render_ao_static: one lighting-mode-2 frame into the caller's device buffer at ``color_ptr`` (float4
+    [height][width]) without a context and without any allocation by the library -- for hosts that must not, or
+    cannot, allocate device memory when they need the frame (include/rt.h lists them).  At most
+    ``_lib.STATIC_MAX_PIXELS`` pixels and ``MAX_SHAPES`` objects; calls that overlap on one GPU share the scratch
+    array and race.  ``want_stats``: wait for the frame and return its ray counters."""
+    lib = L.load()
+    s = np.ascontiguousarray(shapes, dtype=np.float32)
+    u = np.ascontiguousarray(uniforms, dtype=np.float32)
+    r = np.ascontiguousarray(rand_buffer, dtype=np.float32)
+    if s.size < n_shapes * 20 or u.size != 28 or r.size != 8 * aa:
+        raise ValueError("shapes / uniforms / rand_buffer do not have the sizes of the frame contract")
+    st = L.rt_stats()
+    rc = lib.rt_render_ao_static(device, width, height, aa, recursion_depth, flags, s.ctypes.data_as(C.c_void_p), n_shapes,
+                                 u.ctypes.data_as(C.c_void_p), r.ctypes.data_as(C.c_void_p), C.c_void_p(color_ptr),
+                                 C.byref(st) if want_stats else None, C.c_void_p(cuda_stream or 0))
+    if rc != L.RT_OK:
+        raise RtError(rc, lib.rt_last_error(None).decode())
+    return {n: int(getattr(st, n)) for n in L.STAT_COUNTERS} if want_stats else None
+
+
 class Application:
     """The hot-path half of the reference's Application (src/main.cpp:135-800), headless.
 

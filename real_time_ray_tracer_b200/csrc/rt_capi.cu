@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -1549,6 +1550,160 @@ int rt_measure_fp32_peak(int device, double *tflops_out)
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return RT_ECUDA;
     *tflops_out = best;
+    return RT_OK;
+}
+
+// ---- rt_render_ao_static: one AO frame for callers that may not allocate -------------------------------------
+// (include/rt.h says who they are: hosts under a no-allocation rule after start-up, hosts whose device memory was
+// all given to an arena, hosts that own nothing but a buffer and a stream.)  rt_render_frame's mode-2 dispatch
+// needs, besides the caller's inputs and the colour plane, memory of its own: the normal / depth.xy / depth.w / hit
+// planes the kernel also writes, the previous record of the slot that it reads behind an emissive primary hit
+// (all zero on a new context, src/main.cpp:810), the statistics stripes and the sky constants.  Here all of that
+// is carved out of ONE file-scope device array, so the frame costs no cudaMalloc -- and no stream, event or
+// pinned buffer either.  Sections (bytes; each a multiple of 256):
+constexpr size_t SX_PX = RT_STATIC_MAX_PIXELS;
+static_assert(SX_PX % 64 == 0, "every section of the static scratch must stay 256-byte aligned");
+constexpr size_t SX_NORMAL = 0;                               // float4[SX_PX], written
+constexpr size_t SX_OLD_NORMAL = SX_NORMAL + SX_PX * 16;      // float4[SX_PX], only ever read: stays zero
+constexpr size_t SX_DEPTH_XY = SX_OLD_NORMAL + SX_PX * 16;    // float2[SX_PX], written
+constexpr size_t SX_OLD_DEPTH_XY = SX_DEPTH_XY + SX_PX * 8;   // float2[SX_PX], only ever read
+constexpr size_t SX_DEPTH_W = SX_OLD_DEPTH_XY + SX_PX * 8;    // float[SX_PX], written
+constexpr size_t SX_OLD_DEPTH_W = SX_DEPTH_W + SX_PX * 4;     // float[SX_PX], only ever read
+constexpr size_t SX_HIT = SX_OLD_DEPTH_W + SX_PX * 4;         // int[SX_PX], written
+constexpr size_t SX_STATS = SX_HIT + SX_PX * 4;               // the statistics stripes: accumulate, so cleared per call
+constexpr size_t SX_STATS_WORDS = (size_t)STAT_STRIPES * STAT_STRIDE;
+constexpr size_t SX_SKY = SX_STATS + SX_STATS_WORDS * 8;      // float[12], rewritten per call (rt_sky_gamma_kernel)
+constexpr size_t SX_BYTES = SX_SKY + 256;                     // 9 109 760 bytes for 147 456 pixels
+
+// Lives in the library image: every GPU that loads librt_b200.so holds these 8.7 MiB until the process exits.  In
+// HOST code this name is only a handle for cudaGetSymbolAddress -- never a pointer a kernel could be given.
+static __device__ __align__(256) unsigned char rt_static_scratch[SX_BYTES];
+
+// device code of this file may name the array directly: the stripes must start every frame at zero
+__global__ void rt_static_clear_stats_kernel()
+{
+    unsigned long long *st = reinterpret_cast<unsigned long long *>(rt_static_scratch + SX_STATS);
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < SX_STATS_WORDS) st[i] = 0ull;
+}
+
+constexpr int SX_MAX_DEVICES = 64;
+static std::mutex g_static_mu;
+static unsigned char *g_static_base[SX_MAX_DEVICES];              // the array's address ON each device; null = not asked yet
+static unsigned long long g_static_stats_host[SX_STATS_WORDS];    // stats_out: where the stripes land (under the mutex)
+
+// Once per device, with that device current: the device address of rt_static_scratch.  (Every device has its own
+// copy of the array at its own address; the look-up also makes the runtime load this file's module on the device,
+// which is why the first call belongs before any stream capture.)
+static int static_scratch_base(int device, unsigned char **out)
+{
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_base[device]) {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, rt_static_scratch);
+        if (e != cudaSuccess || !ptr) {
+            cudaGetLastError();
+            return fail(nullptr, RT_ECUDA, "rt_render_ao_static: cudaGetSymbolAddress on device %d: %s", device, cudaGetErrorString(e));
+        }
+        g_static_base[device] = static_cast<unsigned char *>(ptr);
+    }
+    *out = g_static_base[device];
+    return RT_OK;
+}
+
+int rt_render_ao_static(int device, int width, int height, int aa, int recursion_depth, int flags,
+                        const rt_shape *shapes, int n_shapes, const rt_uniforms *u, const float *rand_buffer,
+                        void *color_out, rt_stats *stats_out, void *cuda_stream)
+{
+    if (!u || !rand_buffer || !color_out) return fail(nullptr, RT_EINVAL, "rt_render_ao_static: null uniforms, rand_buffer or color_out");
+    if (width <= 0 || height <= 0) return fail(nullptr, RT_EINVAL, "rt_render_ao_static: width/height must be > 0");
+    if ((long long)width * height > (long long)RT_STATIC_MAX_PIXELS)
+        return fail(nullptr, RT_EINVAL, "rt_render_ao_static: %d x %d = %lld pixels, the static scratch holds RT_STATIC_MAX_PIXELS = %d (use rt_create for larger frames)",
+                    width, height, (long long)width * height, RT_STATIC_MAX_PIXELS);
+    if (aa < 1 || aa > RT_MAX_AA) return fail(nullptr, RT_EINVAL, "rt_render_ao_static: aa must be 1..%d", RT_MAX_AA);
+    if (recursion_depth < 1 || recursion_depth > 1000) return fail(nullptr, RT_EINVAL, "rt_render_ao_static: bad recursion_depth");
+    if (flags & ~RT_FLAG_RECTANGLES) return fail(nullptr, RT_EINVAL, "rt_render_ao_static: flags 0x%x (only RT_FLAG_RECTANGLES applies)", flags);
+    if (n_shapes < 0 || n_shapes > RT_MAX_SHAPES)
+        return fail(nullptr, RT_EINVAL, "rt_render_ao_static: n_shapes %d outside 0..%d (larger scenes need an object block in device memory: use rt_create)", n_shapes, RT_MAX_SHAPES);
+    if (n_shapes > 0 && !shapes) return fail(nullptr, RT_EINVAL, "rt_render_ao_static: null shapes");
+    const int nobj = (int)u->mode.z;
+    if (nobj < 0 || nobj > n_shapes) return fail(nullptr, RT_EINVAL, "rt_render_ao_static: mode.z = %d but %d shapes given", nobj, n_shapes);
+    const int ndev = rt_device_count();
+    if (ndev <= 0) return fail(nullptr, RT_ENODEVICE, "rt_render_ao_static: no CUDA device (this library has no CPU path)");
+    if (device < 0 || device >= ndev || device >= SX_MAX_DEVICES) return fail(nullptr, RT_ENODEVICE, "rt_render_ao_static: device %d of %d", device, ndev);
+    CU(nullptr, cudaSetDevice(device));
+    unsigned char *base = nullptr;
+    if (int rc = static_scratch_base(device, &base)) return rc;
+    cudaStream_t S = (cudaStream_t)cuda_stream;
+
+    // the scene records and the frame parameters, formed exactly as rt_upload_scene / rt_render_frame form them
+    DevShape dev_shapes[RT_MAX_SHAPES] = {};
+    rt_vec4 edges[RT_MAX_SHAPES][2] = {};
+    for (int i = 0; i < n_shapes; i++) {
+        const rt_vec4 *v = shapes[i].v;
+        DevShape d{};
+        d.s0 = make_float4(v[0].x, v[0].y, v[0].z, v[0].w);
+        d.s3 = make_float4(v[3].x, v[3].y, v[3].z, v[3].w);
+        d.col = make_float4(v[4].x, v[4].y, v[4].z, v[4].w);
+        d.emissive = v[1].w;
+        volatile float r = v[0].w;
+        volatile float r2 = r * r;
+        d.r2 = r2;
+        d.id = (int)v[4].w;
+        dev_shapes[i] = d;
+        edges[i][0] = v[1];
+        edges[i][1] = v[2];
+    }
+    FrameParams p{};
+    p.W = width; p.H = height; p.AA = aa; p.RD = recursion_depth; p.NF = 1;
+    p.y0 = 0; p.rows = height;
+    {
+        volatile float fw = (float)p.W, fh = (float)p.H;
+        volatile float iw = 1.0f / fw, ih = 1.0f / fh;
+        p.fW = fw; p.fH = fh; p.invW = iw; p.invH = ih;
+    }
+    p.invAA = ((p.AA & (p.AA - 1)) == 0) ? 1.0f / (float)p.AA : 0.0f;
+    p.slot = 0; p.nshapes = nobj; p.edge_mode = RT_EDGE_FLAT32; p.mode = RT_MODE_AO;
+    p.band_index = 0; p.band_count = 1;
+    p.pad0 = flags;
+    p.llc = f3(u->llc_minus_campos); p.horiz = f3(u->horizontal); p.vert = f3(u->vertical);
+    p.cam = f3(u->camera_location); p.light = f3(u->light_pos);
+    p.bg = make_float4(u->background.x, u->background.y, u->background.z, u->background.w);
+    memcpy(p.shapes, dev_shapes, sizeof p.shapes);
+    build_traversal_tables(p, dev_shapes, edges, nobj, true, (flags & RT_FLAG_RECTANGLES) != 0);
+    memcpy(p.rand, rand_buffer, (size_t)aa * 2 * sizeof(float4));
+
+    TraceOut o{};
+    o.color = static_cast<float4 *>(color_out);
+    o.normal = reinterpret_cast<float4 *>(base + SX_NORMAL);
+    o.depth_xy = reinterpret_cast<float2 *>(base + SX_DEPTH_XY);
+    o.depth_w = reinterpret_cast<float *>(base + SX_DEPTH_W);
+    o.old_normal = reinterpret_cast<const float4 *>(base + SX_OLD_NORMAL);
+    o.old_depth_xy = reinterpret_cast<const float2 *>(base + SX_OLD_DEPTH_XY);
+    o.old_depth_w = reinterpret_cast<const float *>(base + SX_OLD_DEPTH_W);
+    o.hit = reinterpret_cast<int *>(base + SX_HIT);
+    o.stats = reinterpret_cast<unsigned long long *>(base + SX_STATS);
+    o.ao_kernel = AO_KERNEL_PULLED;
+    o.sky = reinterpret_cast<const float *>(base + SX_SKY);
+
+    // what the last call left behind: the stripes back to zero, the sky constants for this background and AA
+    rt_static_clear_stats_kernel<<<(unsigned)((SX_STATS_WORDS + 255) / 256), 256, 0, S>>>();
+    CU(nullptr, cudaGetLastError());
+    CU(nullptr, launch_sky_gamma(p.bg, p.AA, reinterpret_cast<float *>(base + SX_SKY), S));
+    CU(nullptr, launch_trace(p, o, S));
+    if (stats_out) {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        CU(nullptr, cudaMemcpyAsync(g_static_stats_host, o.stats, SX_STATS_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, S));
+        CU(nullptr, cudaStreamSynchronize(S));
+        uint64_t t[ST_COUNT] = { 0 };
+        for (int s = 0; s < STAT_STRIPES; s++)
+            for (int k = 0; k < ST_COUNT; k++) t[k] += g_static_stats_host[s * STAT_STRIDE + k];
+        memset(stats_out, 0, sizeof *stats_out);
+        stats_out->rays_closest = t[ST_RAYS_CLOSEST]; stats_out->rays_shadow = t[ST_RAYS_SHADOW];
+        stats_out->primary = t[ST_PRIMARY]; stats_out->jittered = t[ST_JITTERED];
+        stats_out->seg_nonterminal = t[ST_SEG_NONTERMINAL]; stats_out->seg_terminal = t[ST_SEG_TERMINAL];
+        stats_out->shaded = t[ST_SHADED]; stats_out->reflective = t[ST_REFLECTIVE]; stats_out->pixels = t[ST_PIXELS];
+    }
     return RT_OK;
 }
 
