@@ -515,10 +515,27 @@ static int build_grid(rt_ctx *c)
         } else if (s.id == RECTANGLE_ID && rectangles) {
             const float l[3] = { s.s3.x, s.s3.y, s.s3.z };
             const float u[3] = { c->edges[i][0].x, c->edges[i][0].y, c->edges[i][0].z }, r[3] = { c->edges[i][1].x, c->edges[i][1].y, c->edges[i][1].z };
+            // The box must hold every point the intersection test ACCEPTS, and that is not the quad of the four
+            // corners unless right, up and the record's normal are mutually perpendicular (neither the reference's
+            // constructor nor the raw record promises it): a hit d = q - llv lies in the plane dot(n, d) = 0 with
+            // dot(d, right) in [0, |right|^2] and dot(d, up) in [0, |up|^2] -- the parallelogram with corners
+            // d(a, b) = (a |right|^2 (up x n) + b |up|^2 (n x right)) / dot(n, right x up), a, b in {0, 1}.
+            // A (nearly) singular triple accepts an unbounded or degenerate region: such a scene gets no grid.
+            const double n3[3] = { s.s0.x, s.s0.y, s.s0.z }, r3[3] = { r[0], r[1], r[2] }, u3[3] = { u[0], u[1], u[2] };
+            auto cross3 = [](const double *p, const double *q, double *o) {
+                o[0] = p[1] * q[2] - p[2] * q[1]; o[1] = p[2] * q[0] - p[0] * q[2]; o[2] = p[0] * q[1] - p[1] * q[0];
+            };
+            auto dot3 = [](const double *p, const double *q) { return p[0] * q[0] + p[1] * q[1] + p[2] * q[2]; };
+            double rxu[3], uxn[3], nxr[3];
+            cross3(r3, u3, rxu); cross3(u3, n3, uxn); cross3(n3, r3, nxr);
+            const double det = dot3(n3, rxu), rr = dot3(r3, r3), uu = dot3(u3, u3);
+            const double scale = sqrt(dot3(n3, n3) * rr * uu);
+            if (!(fabs(det) > 1e-2 * scale)) return RT_OK;      // also catches NaN and zero-length edges
             for (int a = 0; a < 3; a++) {
-                const float v[4] = { l[a], l[a] + u[a], l[a] + r[a], l[a] + u[a] + r[a] };
-                b.lo[a] = fminf(fminf(v[0], v[1]), fminf(v[2], v[3]));
-                b.hi[a] = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
+                const double da = rr * uxn[a] / det, db = uu * nxr[a] / det;
+                const double v[4] = { (double)l[a], l[a] + da, l[a] + db, l[a] + da + db };
+                b.lo[a] = (float)fmin(fmin(v[0], v[1]), fmin(v[2], v[3]));
+                b.hi[a] = (float)fmax(fmax(v[0], v[1]), fmax(v[2], v[3]));
             }
             b.item = (unsigned short)(0x8000u | (unsigned)nrc++);
         } else {

@@ -374,3 +374,43 @@ def test_grid_off_and_a_partial_scene_are_the_same_bits(monkeypatch):
         o.render(4, u2, None)
         check_frame(rt, o, slot, "partial scene")
         o.close()
+
+
+def skewed_rectangles():
+    """Records whose accept region (0 <= dot(d, e) / dot(e, e) <= 1 on both edges, in the plane of the record's normal)
+    is NOT the quad of their four corners: `up` leaning along `right` (the region reaches 4 units below and 3.2 above
+    the corners), a normal that is not perpendicular to the edges, and both at once"""
+    lean = host.make_rectangle((-9, 0, 2), (5, 0, 0), (4, 5, 0), (0.9, 0.3, 0.2), reflectivity=0.3)
+    tilt = host.make_rectangle((3, -3, 4), (4, 0, 0), (0, 4, 0), (0.2, 0.4, 0.9), reflectivity=0.6)
+    tilt.normal = host.normalize(host.vec3(0.5, 0.3, 1.0))
+    both = host.make_rectangle((-3, 1, -6), (6, 0, 1), (3, 4, 0), (0.3, 0.9, 0.4), reflectivity=0.0)
+    both.normal = host.normalize(host.vec3(0.2, -0.4, 1.0))
+    return [lean, tilt, both]
+
+
+@pytest.mark.gpu
+def test_grid_boxes_hold_the_accept_region_of_skewed_rectangles(monkeypatch):
+    """The grid lists a rectangle in every cell its ACCEPT region touches, not just the cells of its four corners
+    (they differ for skewed edges or a tilted normal): grid on = grid off = the oracle, camera still and moving"""
+    W, H, AA = 160, 120, 4
+    shapes = host.init_scene_field(100).shapes + skewed_rectangles()
+    for keys, frames, ft in (((), 1, 1 / 60), (("a", "q"), 4, 0.02), (("w",), 4, 0.2)):
+        imgs = []
+        for grid in ("1", "0"):
+            monkeypatch.setenv("RT_GRID", grid)
+            sc = Scenario(scene=host.scene(list(shapes)), bg=host.SKY, max_shapes=128, keys=keys, frametime=ft)
+            with rtb.RayTracer(W, H, AA, flags=rtb.FLAG_RECTANGLES, max_shapes=128) as rt:
+                o = orc.Oracle(W, H, AA, rectangles=True, max_shapes=128)
+                rt.upload_scene(sc.shapes, sc.n)
+                o.set_scene(sc.shapes, sc.n)
+                for k in range(frames):
+                    mode = (4, 2)[k & 1]
+                    slot, u, rb = sc.next(mode, AA)
+                    rt.render_frame(mode, u, rb)
+                    o.render(mode, u, rb)
+                    check_frame(rt, o, slot, f"skewed rectangles, RT_GRID={grid}, frame {k} mode {mode}")
+                imgs.append(rt.download(rtb.BUF_COLOR, slot))
+                hit = rt.download(rtb.BUF_HIT_INDEX)
+                o.close()
+            assert sum(int((hit == 100 + j).sum()) for j in range(3)) > 500     # the three records are in view
+        assert same_bits(imgs[0], imgs[1])
