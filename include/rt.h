@@ -132,7 +132,9 @@ typedef struct rt_uniforms {
 /* one record of simple_shapes[NUM_SHAPES][5] (src/main.cpp:59-77):
  *   sphere: v[0]=(center,radius) v[1].w=emissive v[3].w=reflectivity v[4]=(color,1)
  *   plane:  v[0]=(normal,dist)   v[1].w=emissive v[3]=(p0,reflectivity) v[4]=(color,5)
- *   rectangle (id 3) is accepted and, like in the shaders, never intersected. */
+ *   rectangle (id 3): v[0]=(normal,0) v[1]=(up,emissive) v[2]=(right,0) v[3]=(lower left vertex,reflectivity)
+ *     v[4]=(color,3) -- accepted and, like in the shaders, never intersected unless the context was created with
+ *     RT_FLAG_RECTANGLES. */
 typedef struct rt_shape { rt_vec4 v[5]; } rt_shape;
 
 /* the reference's #defines (src/main.cpp:29-36, every shader :7-13) made run-time */
@@ -191,6 +193,9 @@ typedef struct rt_ctx rt_ctx;
 int rt_abi_version(void);
 int rt_device_count(void);
 
+/* Arguments are checked before any device is touched.  One of the checks is a size bound on 32-bit element indices:
+ * width * height * (num_frames + 3) < 2^31 -- on the WHOLE image, also for a context that owns only a band of it
+ * (conservative: the planes hold band_rows * width elements per slot). */
 int rt_create(const rt_config *cfg, rt_ctx **out);
 void rt_destroy(rt_ctx *ctx);
 const char *rt_last_error(const rt_ctx *ctx); /* ctx may be NULL: last error of rt_create */
@@ -238,7 +243,10 @@ int rt_download_color_overlapped(rt_ctx *ctx, int slot, void *pinned_host, size_
 /* blocks the host until the read-backs issued so far have landed, except the newest `keep_in_flight` (0 or 1)
  * -- the consumer of a double-buffered pinned ring calls it with 1 before it reuses the older buffer */
 int rt_readback_wait(rt_ctx *ctx, int keep_in_flight);
-/* raw device pointer of a row-major plane of this band (for NCCL / framework interop) */
+/* raw device pointer of a row-major plane of this band (for NCCL / framework interop).  NOT a stable address: in EVERY
+ * context (with or without RT_FLAG_PIPELINE) a frame that writes normals / depth moves its ring slot to another
+ * physical plane, so a pointer is valid until the next rt_render_frame only -- ask again after each frame instead of
+ * caching per-slot pointers (a cached one silently reads a retired plane). */
 int rt_device_ptr(rt_ctx *ctx, int buffer, int slot, void **out_ptr, size_t *out_bytes);
 
 /* ---- row bands across the GPUs of one box, over peer memory (no reference counterpart: the reference

@@ -202,6 +202,7 @@ int rt_create(const rt_config *cfg, rt_ctx **out)
     int bcount = cfg->band_count ? cfg->band_count : 1;
     if (cfg->band_index < 0 || cfg->band_index >= bcount) return fail(nullptr, RT_EINVAL, "rt_create: bad band_index");
     if (bcount == 1 && rows != cfg->height) return fail(nullptr, RT_EINVAL, "rt_create: a partial band needs band_count > 1");
+    // 32-bit element indices in the kernels; checked on the whole image, which is conservative for a band
     if ((long long)cfg->width * cfg->height * (cfg->num_frames + PIPE) >= (1ll << 31)) return fail(nullptr, RT_EINVAL, "rt_create: W*H*(num_frames+%d) must fit 31 bits", PIPE);
 
     int ndev = rt_device_count();
@@ -829,6 +830,24 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     }
     const bool sky_changed = !c->sky_valid || memcmp(&c->sky_bg, &p.bg, sizeof(float4)) != 0;
     if (sky_changed) c->serialize_frames = 1;       // the constants are shared by the frames in flight
+    // Everything that can fail for a reason of this frame's own (the lazy allocation of the big-scene blocks, the
+    // wait for the staging buffer, the size check) happens BEFORE the frame takes its number and its physical slot:
+    // a frame that returns an error from here leaves the ring, the frame counter and the per-frame events untouched.
+    int big_k = 0, big_nv = 0;
+    if (big) {
+        // the lists of this frame: staged in the next pinned buffer of the ring (free once the copy that last read
+        // it is over)
+        big_k = (int)((c->frame_no + 1) & 3);
+        if (!c->big_dev[0]) {
+            const size_t bytes = (size_t)big_tables_vec4(RT_MAX_SHAPES_LIMIT, RT_MAX_SHAPES_LIMIT, 0, 0) * sizeof(uint4) * 2;   // any mix of kinds fits
+            for (int i = 0; i < 4; i++) { CU(c, cudaMallocHost((void **)&c->big_host[i], bytes)); CU(c, cudaEventCreateWithFlags(&c->ev_big[i], cudaEventDisableTiming)); }
+            for (int i = 0; i < PIPE; i++) CU(c, cudaMalloc((void **)&c->big_dev[i], bytes));
+            c->big_cap_vec4 = (int)(bytes / sizeof(uint4));
+        }
+        CU(c, cudaEventSynchronize(c->ev_big[big_k]));
+        big_nv = build_big_tables(p, c->big_host[big_k], c->shapes, c->edges, nobj, rectangles);
+        if (big_nv > c->big_cap_vec4) return fail(c, RT_EINVAL, "rt_render_frame: object lists of %d bytes", big_nv * 16);
+    }
     // frames that write normals / depth take a fresh physical slot; modes 3/4 without the G-buffer extension leave
     // both as they are (p_compute.glsl:223-246) and write their colour in place
     const bool writes_gbuffer = ao || (c->cfg.flags & RT_FLAG_PHONG_GBUFFER);
@@ -845,23 +864,12 @@ int rt_render_frame(rt_ctx *c, int mode, const rt_uniforms *u, const float *rand
     }
 
     if (big) {
-        // the lists of this frame: staged in the next pinned buffer of the ring (free once the copy that last read
-        // it is over), copied on the frame's stream into the block of the frame's parity -- whose last reader, the
-        // frame before the previous one, ran on this same stream
-        const int k = (int)(c->frame_no & 3);
-        if (!c->big_dev[0]) {
-            const size_t bytes = (size_t)big_tables_vec4(RT_MAX_SHAPES_LIMIT, RT_MAX_SHAPES_LIMIT, 0, 0) * sizeof(uint4) * 2;   // any mix of kinds fits
-            for (int i = 0; i < 4; i++) { CU(c, cudaMallocHost((void **)&c->big_host[i], bytes)); CU(c, cudaEventCreateWithFlags(&c->ev_big[i], cudaEventDisableTiming)); }
-            for (int i = 0; i < PIPE; i++) CU(c, cudaMalloc((void **)&c->big_dev[i], bytes));
-            c->big_cap_vec4 = (int)(bytes / sizeof(uint4));
-        }
-        CU(c, cudaEventSynchronize(c->ev_big[k]));
-        const int nv = build_big_tables(p, c->big_host[k], c->shapes, c->edges, nobj, rectangles);
-        if (nv > c->big_cap_vec4) return fail(c, RT_EINVAL, "rt_render_frame: object lists of %d bytes", nv * 16);
-        CU(c, cudaMemcpyAsync(c->big_dev[par], c->big_host[k], (size_t)nv * sizeof(uint4), cudaMemcpyHostToDevice, S));
-        CU(c, cudaEventRecord(c->ev_big[k], S));
+        // the staged lists are copied on the frame's stream into the block of the frame's parity -- whose last
+        // reader, the frame PIPE frames back, ran on this same stream
+        CU(c, cudaMemcpyAsync(c->big_dev[par], c->big_host[big_k], (size_t)big_nv * sizeof(uint4), cudaMemcpyHostToDevice, S));
+        CU(c, cudaEventRecord(c->ev_big[big_k], S));
         p.big = c->big_dev[par];
-        p.big_vec4 = nv;
+        p.big_vec4 = big_nv;
         // the grid covers the scene as uploaded: a frame that draws fewer objects than that walks the lists
         p.grid = (nobj == c->nshapes) ? c->grid : GridView{};
     }

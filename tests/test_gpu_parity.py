@@ -990,7 +990,7 @@ def test_full_size_properties_1080p():
 
 
 def test_pipelined_frames_are_the_same_bits():
-    """RT_FLAG_PIPELINE: two frames in flight on two internal streams.  A sequence built to hit every ordering rule
+    """RT_FLAG_PIPELINE: three frames in flight on four internal streams (three trace streams, one post stream).  A sequence built to hit every ordering rule
     -- mode-1 runs (the pass of frame k beside the trace of frame k+1), the same ring slot twice in a row, modes 3/4
     writing their colour in place right after a mode-1 frame, a background change (scene toggle) in the middle, a
     frame whose second pass is never called -- is rendered WITHOUT any synchronisation in between and every ring
