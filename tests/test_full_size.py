@@ -3,7 +3,7 @@
 sin() arguments grow with x and y (resources/ao_compute.glsl:63-73: up to 4.4e5 at 7680x4320) and the margins
 of the tile test depend on a tile's angular size, so small-frame parity does not imply large-frame parity.
 GPU tests: the CUDA path against the oracle, every buffer bit for bit.  CPU tests: the oracle against the
-reference's shader text compiled at 1920x1080 and 3840x2160 (oracle/_ref, prebuilt in the build container)."""
+reference's shader text compiled at 1920x1080, 3840x2160 and 7680x4320 / AA 16 (oracle/_ref, prebuilt in the build container)."""
 import os
 
 import numpy as np
@@ -59,6 +59,37 @@ def test_oracle_equals_shader_text_config4_4k_bands():
             g.dispatch("aop_compute", rows=(a, b))
         # rows whose neighbours were traced: everything but the inner edges of the bands
         pp = [(0, 11), (1075, 1085), (H - 11, H)]
+        for (a, b) in pp:
+            o.postprocess(rows=(a, b))
+            g.dispatch("aop_postprocessing", rows=(a, b))
+        for which, name in ((orc.PIXELS, "pixels"), (orc.NORMALS, "normals"), (orc.DEPTH, "depth")):
+            x, y = o.get(which, slot), g.get(which, slot)
+            for (a, b) in pp:
+                assert same_bits(x[a:b], y[a:b]), f"frame {k} rows {a}:{b} {name}: {diff_report(x[a:b], y[a:b])}"
+    o.close(); g.close()
+
+
+@pytest.mark.skipif(not _have_ref(7680, 4320, 16), reason="oracle/_ref 7680x4320 AA 16 library neither prebuilt nor buildable")
+def test_oracle_equals_shader_text_config5_8k_bands():
+    """config 5 (mode 1, 7680x4320, AA 16: rand_buffer has its full 32 entries only here, sin() arguments reach 4.4e5,
+    the FLAT32 aliases move with W and H), two frames of the camera path on three 12-row bands -- bottom (row 0 wraps
+    into row H-1), middle, top: trace + post-processing of the restatement == the shader text, bit for bit"""
+    fr = bench.Frames("config5_aopp_8k_aa16")
+    W, H = fr.W, fr.H
+    assert (W, H, fr.AA) == (7680, 4320, 16)
+    o, g = orc.Oracle(W, H, fr.AA), orc.GlslRef(W, H, fr.AA)
+    o.set_scene(fr.shapes, fr.n)
+    g.set_scene(fr.shapes, fr.n)
+    mid = H // 2 - 6
+    bands = [(0, 12), (mid, mid + 12), (H - 12, H)]
+    pp = [(0, 11), (mid + 1, mid + 11), (H - 11, H)]    # rows whose neighbours were traced
+    for k in range(2):
+        slot, u, rb = fr.next()
+        assert rb.size == 8 * 16
+        g.set_uniforms(u, rb)
+        for (a, b) in bands:
+            o.render(1, u, rb, rows=(a, b))
+            g.dispatch("aop_compute", rows=(a, b))
         for (a, b) in pp:
             o.postprocess(rows=(a, b))
             g.dispatch("aop_postprocessing", rows=(a, b))
