@@ -84,6 +84,7 @@ struct rt_ctx {
     unsigned *grid_cells = nullptr;
     unsigned short *grid_items = nullptr;
     GridView grid{};
+    std::vector<rt_shape> uploaded;   // the records of the last rt_upload_scene, as given: an identical upload keeps the grid
     FrameParams fp{};
     int last_mode = 0, last_slot = 0;
     bool frame_pending_post = false, halo_packed = false;
@@ -624,6 +625,12 @@ int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
     if (!c) return RT_EINVAL;
     if (n < 0 || n > c->max_shapes) return fail(c, RT_EINVAL, "rt_upload_scene: n_shapes %d outside 0..%d (rt_config.max_shapes)", n, c->max_shapes);
     if (n > 0 && !shapes) return fail(c, RT_EINVAL, "rt_upload_scene: null shapes");
+    // The frame contract uploads the scene every frame (src/main.cpp:768) although it rarely changes.  The same
+    // records again change nothing here -- and for a scene with a grid that matters: rebuilding it waits for the
+    // frames in flight and replaces two device allocations.
+    if ((size_t)n == c->uploaded.size() && n == c->nshapes && (n == 0 || memcmp(c->uploaded.data(), shapes, (size_t)n * sizeof(rt_shape)) == 0))
+        return RT_OK;
+    c->uploaded.clear();     // stays empty if the grid build below fails: the next upload tries again
     for (int i = 0; i < n; i++) {
         const rt_vec4 *v = shapes[i].v;
         DevShape d{};
@@ -641,7 +648,9 @@ int rt_upload_scene(rt_ctx *c, const rt_shape *shapes, int n)
     }
     c->nshapes = n;
     CU(c, cudaSetDevice(c->cfg.device));
-    return build_grid(c);
+    const int rc = build_grid(c);
+    if (rc == RT_OK) c->uploaded.assign(shapes, shapes + n);
+    return rc;
 }
 
 static inline float3 f3(const rt_vec4 &v) { return make_float3(v.x, v.y, v.z); }

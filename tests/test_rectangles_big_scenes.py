@@ -414,3 +414,40 @@ def test_grid_boxes_hold_the_accept_region_of_skewed_rectangles(monkeypatch):
                 o.close()
             assert sum(int((hit == 100 + j).sum()) for j in range(3)) > 500     # the three records are in view
         assert same_bits(imgs[0], imgs[1])
+
+
+@pytest.mark.gpu
+def test_scene_uploaded_every_frame_keeps_its_grid_until_it_changes():
+    """The frame contract uploads the scene before every frame (src/main.cpp:768).  The same records again must not
+    rebuild the grid (that waits for the frames in flight and replaces device allocations); changed records must.
+    A 150-object scene, uploaded before each of 8 pipelined frames; one sphere jumps after frame 3 and back after
+    frame 5: every frame equals the oracle given the same uploads, and the unchanged uploads cost microseconds."""
+    import time
+
+    W, H, AA = 128, 96, 4
+    sc = Scenario(scene=host.init_scene_field(150), bg=host.SKY, max_shapes=160, keys=("w",), frametime=0.1)
+    moved = sc.shapes.copy()
+    moved[40, 0, :3] += np.float32(1.5)         # record 40 is a sphere of the field: centre + 1.5 on every axis
+    assert int(moved[40, 4, 3]) == host.SPHERE_ID
+    modes = [2, 4, 1, 1, 4, 2, 1, 3]
+    with rtb.RayTracer(W, H, AA, flags=rtb.FLAG_RECTANGLES | rtb.FLAG_PIPELINE, max_shapes=160) as rt:
+        o = orc.Oracle(W, H, AA, rectangles=True, max_shapes=160)
+        for k, mode in enumerate(modes):
+            shapes = moved if k in (4, 5) else sc.shapes
+            rt.upload_scene(shapes, sc.n)
+            o.set_scene(shapes, sc.n)
+            slot, u, rb = sc.next(mode, AA)
+            rt.render_frame(mode, u, rb)
+            o.render(mode, u, rb)
+            if mode == 1:
+                rt.postprocess()
+                o.postprocess()
+            check_frame(rt, o, slot, f"upload per frame, frame {k} mode {mode}")
+        check_stats(rt, o)
+        rt.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(200):
+            rt.upload_scene(sc.shapes, sc.n)
+        per_call = (time.perf_counter() - t0) / 200
+        assert per_call < 50e-6, f"an unchanged upload took {per_call * 1e6:.1f} us: the grid is being rebuilt"
+        o.close()
