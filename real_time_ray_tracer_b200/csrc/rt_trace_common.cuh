@@ -3,6 +3,15 @@
 // cited beside it operation for operation (see rt_math.cuh for the built-ins).
 #pragma once
 
+// tuning switches (defaults = the measured best; profiles/r3_unroll_ab.txt)
+#ifndef RT_PLANE_UNROLL
+#define RT_PLANE_UNROLL 1
+#endif
+#ifndef RT_MASKED_UNROLL
+#define RT_MASKED_UNROLL 0
+#endif
+
+
 #include "rt_kernels.cuh"
 #include "rt_math.cuh"
 
@@ -286,8 +295,21 @@ __device__ __forceinline__ int closest_hit(const TAB &p, float3 pos, float3 dir,
             sphere_candidate(b, b * b - dot3(pmc, pmc) + s.w, p.sph_idx[i], tmin, c);
         }
     }
+    // The first RT_PLANE_UNROLL planes of a small scene are tested straight-line, so that their records are read
+    // with immediate constant-bank addresses instead of a register-indexed load per component (the address
+    // divergence unit was 27 % busy in round 2's capture of the AO kernel); the reference's scenes have 1 to 5.
+    int j0 = 0;
+    if constexpr (!TAB::BIG && RT_PLANE_UNROLL > 0) {
+#pragma unroll
+        for (int j = 0; j < RT_PLANE_UNROLL; j++) {
+            if (j >= p.npl) break;
+            const float3 n = xyz(p.pl_n[j]);
+            plane_candidate(dot3(n, sub3(xyz(p.pl_p0[j]), pos)), dot3(n, dir), p.pl_idx[j], tmin, c);
+        }
+        j0 = RT_PLANE_UNROLL;
+    }
 #pragma unroll 1
-    for (int j = 0; j < p.npl; j++) {
+    for (int j = j0; j < p.npl; j++) {
         const float3 n = xyz(p.pl_n[j]);
         plane_candidate(dot3(n, sub3(xyz(p.pl_p0[j]), pos)), dot3(n, dir), p.pl_idx[j], tmin, c);
     }
@@ -398,6 +420,27 @@ __device__ __forceinline__ int closest_hit_primary_masked(const FrameParams &p, 
         rc_cand = (cand >> 16) >> p.npl;
         cand &= ~(0xffff0000u << p.npl);
     }
+#if RT_MASKED_UNROLL
+    // straight-line over the list positions, each guarded by its candidate bit: immediate constant-bank addresses
+    // instead of __ffs + register-indexed loads
+#pragma unroll
+    for (int i = 0; i < RT_MAX_SHAPES; i++) {
+        if (i >= p.nsph) break;
+        if ((cand >> i) & 1u) {
+            const float4 k = p.sph_cam[i];
+            const float b = dot3(dir, xyz(k));
+            sphere_candidate(b, b * b - k.w + p.sph[i].w, p.sph_idx[i], tmin, c);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < RT_MAX_SHAPES; j++) {
+        if (j >= p.npl) break;
+        if ((cand >> (16 + j)) & 1u) {
+            const float4 n = p.pl_n[j];
+            plane_candidate(n.w, dot3(xyz(n), dir), p.pl_idx[j], tmin, c);
+        }
+    }
+#else
 #pragma unroll 1
     for (unsigned m = cand & 0xffffu; m; m &= m - 1u) {
         const int i = __ffs((int)m) - 1;
@@ -411,6 +454,7 @@ __device__ __forceinline__ int closest_hit_primary_masked(const FrameParams &p, 
         const float4 n = p.pl_n[j];
         plane_candidate(n.w, dot3(xyz(n), dir), p.pl_idx[j], tmin, c);
     }
+#endif
     if constexpr (RC) {
 #pragma unroll 1
         for (unsigned m = rc_cand; m; m &= m - 1u) {
