@@ -54,6 +54,8 @@ def lib():
         L.rto_set_threads.argtypes = [C.c_void_p, C.c_int]
         L.rto_set_phong_gbuffer.argtypes = [C.c_void_p, C.c_int]
         L.rto_set_rectangles.argtypes = [C.c_void_p, C.c_int]
+        L.rto_debug_pow_binary64.argtypes = [C.c_int]
+        L.rto_debug_pow_binary64.restype = None
         L.rto_set_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.rto_render.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.rto_render_rows.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]

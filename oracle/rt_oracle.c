@@ -337,10 +337,21 @@ static rtr_v4 ambient_occlusion(rto_ctx *c, rtr_v3 dir, int aa, unsigned x, unsi
     return result;
 }
 
+/* TEST-ONLY switch (tests/test_oracle_math.py): with on != 0 the two pow() call sites below use binary64 libm pow,
+ * rounded to binary32 -- an implementation that shares nothing with rtr_pow.  The oracle, the CUDA kernels and the
+ * shader-text shim all state the SAME binary32 hi/lo pow, so bit-parity between them cannot catch a mistake they
+ * share; rendering both ways and comparing the displayable 8-bit image can.  Process-wide; default off. */
+static int g_pow_binary64 = 0;
+void rto_debug_pow_binary64(int on) { g_pow_binary64 = on; }
+static inline float ora_pow(float x, float y)
+{
+    return g_pow_binary64 ? (float)pow((double)x, (double)y) : rtr_pow(x, y);
+}
+
 static inline rtr_v4 gamma_correct(rtr_v4 c)
 {
     float g = 1.0f / 2.2f;
-    return rtr_mk4(rtr_pow(c.x, g), rtr_pow(c.y, g), rtr_pow(c.z, g), 0.0f);
+    return rtr_mk4(ora_pow(c.x, g), ora_pow(c.y, g), ora_pow(c.z, g), 0.0f);
 }
 
 /* ao_compute.glsl:285-340 */
@@ -413,7 +424,7 @@ static inline rtr_v4 phong_shade(const rto_ctx *c, rtr_v4 att, rtr_v3 curr_pos, 
 {
     if (lit) {
         rtr_v3 l = rtr_normalize3(rtr_sub3(rtr_xyz(U_LIGHT(c)), curr_pos));
-        float spec = rtr_pow(rtr_clamp(rtr_dot3(rtr_normalize3(rtr_sub3(l, dir)), normal), 0.0f, 1.0f), 500.0f);
+        float spec = ora_pow(rtr_clamp(rtr_dot3(rtr_normalize3(rtr_sub3(l, dir)), normal), 0.0f, 1.0f), 500.0f);
         rtr_v4 r = rtr_scale4(rtr_clamp(rtr_dot3(normal, l), PHONG_SHADOW_MIN, 1.0f), att);
         spec = spec * 1.0f;
         return rtr_mk4(r.x + spec, r.y + spec, r.z + spec, r.w + spec);

@@ -154,3 +154,42 @@ def test_phong_gbuffer_extension_is_off_by_default_and_consistent_when_on():
     assert same_bits(d4[..., 0], d_ao[..., 0]) and (d4[..., 1][hit] >= 0).all() and d4[..., 1].max() >= 1
     for o in (ref, off, on):
         o.close()
+
+
+def test_pow_definition_does_not_move_the_displayed_image():
+    """The oracle, the CUDA kernels and the shader-text shim all state the same binary32 pow, so bit-parity between
+    them cannot see a mistake they share.  Metric-level check with an implementation that shares nothing with it:
+    the same frames rendered with binary64 libm pow at the two call sites (gamma, specular exponent) give the same
+    displayable image -- 8-bit quantisation as include/rt.h defines it -- to within 1 LSB, on all but a sliver of
+    the samples exactly."""
+    from real_time_ray_tracer_b200 import host  # noqa: F401
+    from tests.util import Scenario
+
+    def quantise(c):
+        with np.errstate(invalid="ignore"):
+            q = np.floor(np.clip(np.nan_to_num(c[..., :3], nan=0.0), 0.0, 1.0) * 255.0 + 0.5)
+        return q.astype(np.int32)
+
+    W, H, AA = 160, 120, 4
+    L = orc.lib()
+    total = differing = 0
+    try:
+        for scene, mode in (("scene1", 2), ("scene1", 3), ("scene5", 4), ("scene6", 4), ("scene5", 2)):
+            imgs = []
+            for libm in (0, 1):
+                L.rto_debug_pow_binary64(libm)
+                sc = Scenario(scene, keys=("d",), light_movement=True)
+                o = orc.Oracle(W, H, AA)
+                o.set_scene(sc.shapes, sc.n)
+                for _ in range(2):
+                    slot, u, rb = sc.next(mode, AA)
+                    o.render(mode, u, rb)
+                imgs.append(quantise(o.get(orc.PIXELS, slot)))
+                o.close()
+            d = np.abs(imgs[0] - imgs[1])
+            assert d.max() <= 1, (scene, mode, int(d.max()))
+            total += d.size
+            differing += int((d != 0).sum())
+    finally:
+        L.rto_debug_pow_binary64(0)
+    assert differing <= total * 1e-3, (differing, total)
